@@ -1,0 +1,251 @@
+/* b200sd — C ABI of the B200-native Stable-Diffusion-class batch text-to-image hot path.
+ *
+ * The reference (christianshub/k8s-nvidia-gpus) defines no C ABI / FFI: its compute is the un-vendored
+ * diffusers/transformers/torch stack called from cluster-config/apps/sd15-api/configmap.yaml:105-112
+ * (`pipe(prompt, num_inference_steps, guidance_scale, width, height, generator)`), reached over HTTP from
+ * scripts/batch_generate.py:20-26.  Each entry point below therefore cites the *operation inside that call*
+ * which it replaces (SURVEY.md §8(a) row numbers, upstream module names).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; the CALLER owns every buffer (inputs, outputs, scratch).
+ *   - all pointers are device pointers unless a field says "host".
+ *   - activations are NHWC ("channels-last") bf16; token tensors [B, HW, C] alias the same memory.
+ *   - every call is asynchronous on `stream`, performs no allocation and no synchronisation, and can be
+ *     captured into a CUDA graph (exception: b200sd_device_info, which only queries).
+ *   - return value 0 = ok, negative = b200sd_status; b200sd_last_error() (thread-local) has the detail.
+ *   - sm_100a only.  There is no CPU path and no other backend.
+ */
+#ifndef B200SD_H_
+#define B200SD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200sd_stream; /* cudaStream_t */
+
+enum b200sd_status {
+  B200SD_OK = 0,
+  B200SD_ERR_BAD_SHAPE = -1,
+  B200SD_ERR_BAD_ALIGNMENT = -2,
+  B200SD_ERR_UNSUPPORTED_ARCH = -3,
+  B200SD_ERR_CUDA = -4,
+  B200SD_ERR_BAD_ARGUMENT = -5,
+  B200SD_ERR_TOO_LARGE = -6
+};
+
+enum b200sd_act { B200SD_ACT_NONE = 0, B200SD_ACT_SILU = 1, B200SD_ACT_QUICK_GELU = 2, B200SD_ACT_GEGLU = 3 };
+enum b200sd_dtype { B200SD_BF16 = 0, B200SD_F32 = 1 };
+
+int b200sd_version(void);
+const char* b200sd_last_error(void);
+/* out[0]=SM count, out[1]=cc major, out[2]=cc minor, out[3]=max dynamic smem per block. */
+int b200sd_device_info(int32_t* out4);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Implicit-GEMM convolution / linear layer on tcgen05 (TMA-fed, fp32 accumulation in TMEM).
+ * Replaces: torch conv2d 3x3 s1 p1 / 1x1 (ResnetBlock2D.conv1/conv2/conv_shortcut, Transformer2DModel.proj_in/out,
+ * Upsample2D.conv, conv_in/conv_out, VAE decoder convs) and nn.Linear (attention projections, GEGLU, time MLP,
+ * CLIP MLP) inside UNet2DConditionModel.forward / AutoencoderKL.decode / CLIPTextModel — SURVEY §8(a) a7,a10,a13;
+ * call site configmap.yaml:105.
+ *
+ *   out[m, n] = act( alpha * sum_{tap,c} A[pixel(m)+tap, c] * W[n, tap, c] + bias[n] + rowbias[img(m), n] )
+ *               + residual[m, n]
+ * A is the virtual channel-concatenation of up to two NHWC sources (a0: c0 channels, a1: c1 channels; a1 may be
+ * NULL with c1 = 0) — the UNet up-path skip concat is never materialised.  ksize = 1 or 3 (stride 1, zero padding
+ * ksize/2).  A linear layer over M rows is nimg = 1, h = 1, w = M, ksize = 1.
+ * W is bf16 [n, ksize*ksize, c0p + c1p] with c0p/c1p = c0/c1 rounded up to 64 (zero padded), K contiguous.
+ * GEGLU: W rows/bias packed in 64-row groups [32 value rows | 32 gate rows]; out has n/2 columns.
+ * Requirements: c0, c1, ld0, ld1 multiples of 8; pointers 16-byte aligned.
+ */
+typedef struct {
+  const void* a0;       /* bf16 NHWC source 0, pixel stride ld0 elements */
+  const void* a1;       /* bf16 NHWC source 1 or NULL */
+  const void* w;        /* bf16 packed weights */
+  void* out;            /* bf16 or f32 [M, ldc] */
+  const float* bias;    /* f32 [n] or NULL */
+  const float* rowbias; /* f32 [nimg, ld_rowbias] or NULL (time-embedding projection) */
+  const void* residual; /* bf16 [M, ldr] or NULL */
+  int32_t nimg, h, w_, c0, c1, ld0, ld1;
+  int32_t n;      /* GEMM N (weight rows) */
+  int32_t ksize;  /* 1 or 3 */
+  int32_t ldc, ldr, ld_rowbias;
+  int32_t act;       /* b200sd_act */
+  int32_t out_dtype; /* b200sd_dtype */
+  int32_t bn_hint;   /* 0 = auto; else tile N (multiple of 32, <= 256) */
+  float alpha;       /* accumulator scale (1.0 for plain layers) */
+} b200sd_gemm_params;
+int b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Flash attention on tcgen05: out = softmax(Q K^T * scale [+ causal mask]) V, per (batch, head).
+ * Replaces: Attention / SlicedAttnProcessor (configmap.yaml:42 enables slicing — identity up to rounding) in
+ * BasicTransformerBlock.attn1/attn2 and CLIPAttention — SURVEY §8(a) a7, a10.3.
+ * Q: [batch, nq, ldq] bf16, head h at columns [h*d, (h+1)*d); K, V likewise with nk rows.  out: [batch, nq, ldo].
+ * d (head dim) multiple of 8, <= 160.  ld* multiples of 8.
+ */
+typedef struct {
+  const void* q;
+  const void* k;
+  const void* v;
+  void* out;
+  int32_t batch, heads, nq, nk, d;
+  int32_t ldq, ldk, ldv, ldo;
+  int32_t causal;
+  float scale;
+} b200sd_attn_params;
+int b200sd_attention(const b200sd_attn_params* p, b200sd_stream stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * GroupNorm (+ optional SiLU) over the virtual concat of two NHWC sources; two passes.
+ * Replaces: torch group_norm + silu in ResnetBlock2D.norm1/norm2, Transformer2DModel.norm, conv_norm_out, VAE
+ * norms — SURVEY §8(a) a10.2/a10.3/a13 (K7/K8/K14).
+ * stats: f32 [nimg, groups, 2] scratch; b200sd_groupnorm_stats ACCUMULATES into it (caller zeroes it first).
+ */
+typedef struct {
+  const void* x0;
+  const void* x1; /* or NULL */
+  float* stats;
+  const float* gamma; /* f32 [c0+c1] */
+  const float* beta;  /* f32 [c0+c1] */
+  void* out;          /* bf16 [nimg, hw, c0+c1] */
+  int32_t nimg, hw, c0, c1, groups;
+  int32_t silu;
+  float eps;
+} b200sd_groupnorm_params;
+int b200sd_groupnorm_stats(const b200sd_groupnorm_params* p, b200sd_stream stream);
+int b200sd_groupnorm_apply(const b200sd_groupnorm_params* p, b200sd_stream stream);
+
+/* LayerNorm over the last dim. Replaces nn.LayerNorm in BasicTransformerBlock.norm1-3 / CLIPEncoderLayer (K9). */
+typedef struct {
+  const void* x; /* bf16 [rows, c] */
+  const float* gamma;
+  const float* beta;
+  void* out; /* bf16 [rows, c] */
+  int32_t rows, c;
+  float eps;
+} b200sd_layernorm_params;
+int b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_stream stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Denoise-loop glue (bandwidth-bound, fused).  A device-resident step table drives them so one captured
+ * CUDA graph can be replayed for every step with no host interaction:
+ *   step_table: f32 [nsteps, 16]  (see B200SD_ST_* indices), step_counter: int32 [1] on device.
+ */
+enum {
+  B200SD_ST_TIMESTEP = 0,  /* timestep fed to the UNet */
+  B200SD_ST_IN_SCALE = 1,  /* scale_model_input factor */
+  B200SD_ST_KIND = 2,      /* 0 DDIM, 1 Euler, 2 PNDM/PLMS */
+  B200SD_ST_C0 = 3,        /* DDIM: sqrt(1-a_t)   Euler: sigma_next - sigma    PNDM: sample coeff */
+  B200SD_ST_C1 = 4,        /* DDIM: sqrt(a_t)                                  PNDM: -model-output coeff */
+  B200SD_ST_C2 = 5,        /* DDIM: sqrt(a_prev) */
+  B200SD_ST_C3 = 6,        /* DDIM: sqrt(1-a_prev) */
+  B200SD_ST_W0 = 7,        /* PNDM: weights on eps history [newest .. oldest], 4 entries (7..10) */
+  B200SD_ST_PNDM_MODE = 11,/* PNDM: 0 normal, 1 first step (store cur_sample), 2 second step (average, restore) */
+  B200SD_ST_PUSH = 12,     /* PNDM: 1 = push eps into history ring */
+  B200SD_ST_WIDTH = 16
+};
+
+/* latents f32 NHWC [b, hw, 4] -> UNet input bf16 [2b (or b), hw, 8] (channels 4..7 zero), scaled by IN_SCALE.
+ * Replaces torch.cat([latents]*2) + scheduler.scale_model_input (pipeline loop). */
+typedef struct {
+  const float* latents;
+  void* out;
+  const float* step_table;
+  const int32_t* step_counter;
+  int32_t b, hw, cfg; /* cfg=1: duplicate batch [uncond; cond] */
+} b200sd_prep_params;
+int b200sd_prep_unet_input(const b200sd_prep_params* p, b200sd_stream stream);
+
+/* Sinusoidal timestep embedding (flip_sin_to_cos, shift 0): out bf16 [rows, dim] = [cos | sin]. (a10.1, K10) */
+typedef struct {
+  void* out;
+  const float* step_table;
+  const int32_t* step_counter;
+  int32_t rows, dim;
+} b200sd_temb_params;
+int b200sd_timestep_embedding(const b200sd_temb_params* p, b200sd_stream stream);
+
+/* Classifier-free-guidance combine + scheduler step, in place on latents; increments *step_counter.
+ * Replaces eps.chunk(2) / e_u + gs*(e_c-e_u) and scheduler.step (DDIM / Euler / PNDM-PLMS) — a11, a12 (K11/K12).
+ * eps f32 [2b (or b), hw, ld_eps] (first 4 columns used).  history: f32 [4, b, hw, 4] ring (PNDM), cur_sample
+ * f32 [b, hw, 4] (PNDM). */
+typedef struct {
+  const float* eps;
+  float* latents;
+  float* history;
+  float* cur_sample;
+  const float* step_table;
+  int32_t* step_counter;
+  int32_t b, hw, ld_eps, cfg;
+  float guidance_scale;
+} b200sd_sched_params;
+int b200sd_cfg_scheduler_step(const b200sd_sched_params* p, b200sd_stream stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Layout / gather helpers (bandwidth-bound).
+ */
+/* nearest-neighbour 2x upsample, NHWC bf16 (Upsample2D; K13). */
+typedef struct {
+  const void* x;
+  void* out;
+  int32_t nimg, h, w_, c;
+} b200sd_upsample_params;
+int b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream stream);
+
+/* 3x3 stride-2 pad-1 patch gather: out bf16 [nimg, h/2, w/2, 9*cp] (cp = c rounded up to 64, pad zeroed), feeding
+ * b200sd_gemm as a linear layer (Downsample2D; K2).  `out` is caller-provided scratch. */
+typedef struct {
+  const void* x;
+  void* out;
+  int32_t nimg, h, w_, c;
+} b200sd_im2col_s2_params;
+int b200sd_im2col_s2(const b200sd_im2col_s2_params* p, b200sd_stream stream);
+size_t b200sd_im2col_s2_bytes(const b200sd_im2col_s2_params* p);
+
+/* CLIP token + position embedding: out bf16 [rows, c] = tok[ids[r]] + pos[r % seq]. (CLIPTextEmbeddings; a7) */
+typedef struct {
+  const int32_t* ids;
+  const void* tok; /* bf16 [vocab, c] */
+  const void* pos; /* bf16 [seq, c] */
+  void* out;
+  int32_t rows, seq, c, vocab;
+} b200sd_embed_params;
+int b200sd_clip_embed(const b200sd_embed_params* p, b200sd_stream stream);
+
+/* VAE output -> uint8 image: clamp(x/2+0.5, 0, 1)*255, round-half-even. x f32 [npix, ldx] (3 used) -> u8 [npix, 3].
+ * Replaces VaeImageProcessor.postprocess + numpy round/astype (a15, K17). */
+typedef struct {
+  const float* x;
+  uint8_t* out;
+  int64_t npix;
+  int32_t ldx;
+} b200sd_denorm_params;
+int b200sd_denorm_u8(const b200sd_denorm_params* p, b200sd_stream stream);
+
+/* latents f32 NHWC [b, hw, 4] * scale -> bf16 [b, hw, 8] zero padded (VAE input: latents / scaling_factor). */
+typedef struct {
+  const float* latents;
+  void* out;
+  int32_t b, hw;
+  float scale;
+} b200sd_latent_cast_params;
+int b200sd_latent_to_bf16(const b200sd_latent_cast_params* p, b200sd_stream stream);
+
+/* Row softmax in place over bf16 [rows, cols] scaled logits (VAE mid-block attention d=512 unfused path). */
+typedef struct {
+  void* x;
+  int32_t rows, cols;
+} b200sd_softmax_params;
+int b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_stream stream);
+
+/* sizeof() of every params struct, in declaration order above (host bindings check their mirrors against it). */
+int b200sd_struct_sizes(int32_t* out, int32_t max_entries);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SD_H_ */

@@ -1,0 +1,10 @@
+"""b200sd — B200-native Stable-Diffusion-class batch text-to-image hot path.
+
+Drop-in for the compute behind christianshub/k8s-nvidia-gpus' sd15-api (`pipe(...)` in
+cluster-config/apps/sd15-api/configmap.yaml:105-112) and its scripts/batch_generate.py client.
+The directory name contains '-' so import it with importlib (see `b200sd.py` at the repo root).
+"""
+from . import lib  # noqa: F401
+from . import ops  # noqa: F401
+
+__version__ = "0.1.0"

@@ -1,0 +1,51 @@
+// Host-side helpers shared by the C-ABI entry points: error reporting, device checks, TMA descriptor encoding.
+#pragma once
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/b200sd.h"
+
+namespace b200sd {
+
+char* last_error_buf();  // thread-local, defined in capi.cu
+int set_error(int code, const char* fmt, ...);
+
+#define B200SD_CUDA_CHECK(expr)                                                                     \
+  do {                                                                                              \
+    cudaError_t _e = (expr);                                                                        \
+    if (_e != cudaSuccess)                                                                          \
+      return b200sd::set_error(B200SD_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                               __LINE__);                                                           \
+  } while (0)
+
+#define B200SD_REQUIRE(cond, code, ...)                        \
+  do {                                                         \
+    if (!(cond)) return b200sd::set_error(code, __VA_ARGS__); \
+  } while (0)
+
+struct DeviceInfo {
+  int sm_count;
+  int cc_major, cc_minor;
+  int max_smem_optin;
+};
+// Cached per current device; returns error if not sm_100.
+int get_device_info(DeviceInfo* out);
+
+// cuTensorMapEncodeTiled via the runtime's driver entry point (no -lcuda link dependency).
+// dims/strides innermost first; strides[i] = byte stride of dim i+1 (rank-1 entries); bf16 elements; 128B swizzle.
+int encode_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const uint32_t* box);
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+}  // namespace b200sd

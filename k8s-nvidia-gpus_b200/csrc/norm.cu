@@ -1,0 +1,349 @@
+// Bandwidth-bound normalisation kernels: GroupNorm(+SiLU) over a virtual two-source concat, LayerNorm, row softmax.
+// All statistics are fp32; inputs/outputs bf16, 16-byte vectorised, coalesced along the NHWC channel axis.
+// SURVEY §2.1 K7, K8, K9, K14.
+#include "common.cuh"
+#include "host.cuh"
+
+namespace b200sd {
+
+static constexpr int kNormThreads = 256;
+
+__device__ __forceinline__ void load8(const bf16* p, float (&f)[8]) {
+  const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
+  const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ void store8(bf16* p, const float (&f)[8]) {
+  uint4 u;
+  u.x = pack_bf16x2(f[0], f[1]);
+  u.y = pack_bf16x2(f[2], f[3]);
+  u.z = pack_bf16x2(f[4], f[5]);
+  u.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+// ---------------------------------------------------------------------------------------------- GroupNorm: stats
+// grid (chunks, nimg).  Each thread owns one 8-channel vector column ("octet") and walks pixels, keeping 8 sums and
+// 8 sums of squares in registers; one shared-memory atomic pass per CTA, then one global atomic per (group, CTA).
+__global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const bf16* __restrict__ x0,
+                                                                const bf16* __restrict__ x1, float* __restrict__ stats,
+                                                                int hw, int c0, int c1, int groups, int pix_per_cta) {
+  extern __shared__ float gacc[];  // [groups][2]
+  const int n = blockIdx.y;
+  const int C = c0 + c1;
+  const int octs = C >> 3;
+  const int cpg = C / groups;
+  const int p_begin = blockIdx.x * pix_per_cta;
+  const int p_end = min(hw, p_begin + pix_per_cta);
+  for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) gacc[i] = 0.f;
+  __syncthreads();
+  const int Wd = min(octs, kNormThreads);
+  const int S = kNormThreads / Wd;
+  const int stream = threadIdx.x / Wd;
+  if (stream < S) {
+    for (int oct = threadIdx.x % Wd; oct < octs; oct += Wd) {
+      const int ch0 = oct * 8;
+      const bf16* src;
+      int ld;
+      if (ch0 < c0) {
+        src = x0 + static_cast<size_t>(n) * hw * c0 + ch0;
+        ld = c0;
+      } else {
+        src = x1 + static_cast<size_t>(n) * hw * c1 + (ch0 - c0);
+        ld = c1;
+      }
+      float s[8], q[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s[e] = q[e] = 0.f;
+      int p = p_begin + stream;
+      for (; p + 3 * S < p_end; p += 4 * S) {
+        float f[4][8];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) load8(src + static_cast<size_t>(p + u * S) * ld, f[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            s[e] += f[u][e];
+            q[e] = fmaf(f[u][e], f[u][e], q[e]);
+          }
+      }
+      for (; p < p_end; p += S) {
+        float f[8];
+        load8(src + static_cast<size_t>(p) * ld, f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          s[e] += f[e];
+          q[e] = fmaf(f[e], f[e], q[e]);
+        }
+      }
+      // merge runs of equal group before touching shared memory
+      int g_cur = ch0 / cpg;
+      float rs = 0.f, rq = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int g = (ch0 + e) / cpg;
+        if (g != g_cur) {
+          atomicAdd(&gacc[2 * g_cur], rs);
+          atomicAdd(&gacc[2 * g_cur + 1], rq);
+          rs = rq = 0.f;
+          g_cur = g;
+        }
+        rs += s[e];
+        rq += q[e];
+      }
+      atomicAdd(&gacc[2 * g_cur], rs);
+      atomicAdd(&gacc[2 * g_cur + 1], rq);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < groups * 2; i += blockDim.x)
+    atomicAdd(&stats[static_cast<size_t>(n) * groups * 2 + i], gacc[i]);
+}
+
+// ---------------------------------------------------------------------------------------------- GroupNorm: apply
+__global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const bf16* __restrict__ x0,
+                                                                const bf16* __restrict__ x1,
+                                                                const float* __restrict__ stats,
+                                                                const float* __restrict__ gamma,
+                                                                const float* __restrict__ beta, bf16* __restrict__ out,
+                                                                int hw, int c0, int c1, int groups, int pix_per_cta,
+                                                                int silu, float eps) {
+  extern __shared__ float ss[];  // scale[C], shift[C]
+  const int n = blockIdx.y;
+  const int C = c0 + c1;
+  const int octs = C >> 3;
+  const int cpg = C / groups;
+  float* scale = ss;
+  float* shift = ss + C;
+  const float inv_cnt = 1.f / (static_cast<float>(hw) * static_cast<float>(cpg));
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    const float sum = stats[(static_cast<size_t>(n) * groups + g) * 2];
+    const float sq = stats[(static_cast<size_t>(n) * groups + g) * 2 + 1];
+    const float mean = sum * inv_cnt;
+    const float var = fmaxf(sq * inv_cnt - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * rstd;
+    scale[c] = sc;
+    shift[c] = beta[c] - mean * sc;
+  }
+  __syncthreads();
+  const int p_begin = blockIdx.x * pix_per_cta;
+  const int p_end = min(hw, p_begin + pix_per_cta);
+  const int total = (p_end - p_begin) * octs;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int p = p_begin + idx / octs;
+    const int oct = idx - (idx / octs) * octs;
+    const int ch0 = oct * 8;
+    const bf16* src = (ch0 < c0) ? x0 + (static_cast<size_t>(n) * hw + p) * c0 + ch0
+                                 : x1 + (static_cast<size_t>(n) * hw + p) * c1 + (ch0 - c0);
+    float f[8];
+    load8(src, f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float y = fmaf(f[e], scale[ch0 + e], shift[ch0 + e]);
+      f[e] = silu ? silu_f(y) : y;
+    }
+    store8(out + (static_cast<size_t>(n) * hw + p) * C + ch0, f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- LayerNorm
+// one warp per row; the row lives in registers (two-pass mean / variance like the fp32 reference).
+template <int kVecs>
+__global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const bf16* __restrict__ x,
+                                                                 const float* __restrict__ gamma,
+                                                                 const float* __restrict__ beta, bf16* __restrict__ out,
+                                                                 int rows, int c, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (kNormThreads / 32) + warp;
+  if (row >= rows) return;
+  const int octs = c >> 3;
+  const bf16* xr = x + static_cast<size_t>(row) * c;
+  float f[kVecs][8];
+  float sum = 0.f;
+#pragma unroll
+  for (int v = 0; v < kVecs; ++v) {
+    const int oct = lane + 32 * v;
+    if (oct < octs) {
+      load8(xr + oct * 8, f[v]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) sum += f[v][e];
+    }
+  }
+  const float mean = warp_sum(sum) / static_cast<float>(c);
+  float sq = 0.f;
+#pragma unroll
+  for (int v = 0; v < kVecs; ++v) {
+    const int oct = lane + 32 * v;
+    if (oct < octs) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float d = f[v][e] - mean;
+        sq = fmaf(d, d, sq);
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / static_cast<float>(c) + eps);
+  bf16* orow = out + static_cast<size_t>(row) * c;
+#pragma unroll
+  for (int v = 0; v < kVecs; ++v) {
+    const int oct = lane + 32 * v;
+    if (oct < octs) {
+      float y[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int ch = oct * 8 + e;
+        y[e] = (f[v][e] - mean) * rstd * __ldg(gamma + ch) + __ldg(beta + ch);
+      }
+      store8(orow + oct * 8, y);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- row softmax (in place)
+// one CTA per row, row held in registers (cols <= 256 * 8 * kVecs).
+template <int kVecs>
+__global__ void __launch_bounds__(kNormThreads) softmax_rows_kernel(bf16* __restrict__ x, int cols) {
+  __shared__ float red[kNormThreads / 32];
+  bf16* xr = x + static_cast<size_t>(blockIdx.x) * cols;
+  const int octs = cols >> 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float f[kVecs][8];
+  float mx = -INFINITY;
+#pragma unroll
+  for (int v = 0; v < kVecs; ++v) {
+    const int oct = threadIdx.x + kNormThreads * v;
+    if (oct < octs) {
+      load8(xr + oct * 8, f[v]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) mx = fmaxf(mx, f[v][e]);
+    }
+  }
+  mx = warp_max(mx);
+  if (lane == 0) red[warp] = mx;
+  __syncthreads();
+  mx = red[0];
+#pragma unroll
+  for (int i = 1; i < kNormThreads / 32; ++i) mx = fmaxf(mx, red[i]);
+  __syncthreads();
+  float sum = 0.f;
+#pragma unroll
+  for (int v = 0; v < kVecs; ++v) {
+    const int oct = threadIdx.x + kNormThreads * v;
+    if (oct < octs) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        f[v][e] = __expf(f[v][e] - mx);
+        sum += f[v][e];
+      }
+    }
+  }
+  sum = warp_sum(sum);
+  if (lane == 0) red[warp] = sum;
+  __syncthreads();
+  sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormThreads / 32; ++i) sum += red[i];
+  const float inv = 1.f / sum;
+#pragma unroll
+  for (int v = 0; v < kVecs; ++v) {
+    const int oct = threadIdx.x + kNormThreads * v;
+    if (oct < octs) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[v][e] *= inv;
+      store8(xr + oct * 8, f[v]);
+    }
+  }
+}
+
+static int gn_check(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chunks) {
+  B200SD_REQUIRE(h.x0 && h.stats && h.nimg > 0 && h.hw > 0 && h.c0 > 0 && h.c1 >= 0 && h.groups > 0,
+                 B200SD_ERR_BAD_ARGUMENT, "groupnorm: bad arguments");
+  const int C = h.c0 + h.c1;
+  B200SD_REQUIRE((h.c0 % 8) == 0 && (h.c1 % 8) == 0, B200SD_ERR_BAD_SHAPE, "groupnorm: channels must be multiples of 8");
+  B200SD_REQUIRE((C % h.groups) == 0, B200SD_ERR_BAD_SHAPE, "groupnorm: %d channels not divisible by %d groups", C,
+                 h.groups);
+  B200SD_REQUIRE(h.groups <= 1024 && C <= 8192, B200SD_ERR_TOO_LARGE, "groupnorm: too many groups/channels");
+  B200SD_REQUIRE((h.c1 == 0) == (h.x1 == nullptr), B200SD_ERR_BAD_ARGUMENT, "groupnorm: x1 and c1 must agree");
+  B200SD_REQUIRE(aligned16(h.x0) && aligned16(h.x1) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
+                 "groupnorm: pointers must be 16-byte aligned");
+  // aim for ~4 CTAs per SM over the whole launch, at least 8 pixels per CTA
+  int want = (4 * 148 + h.nimg - 1) / h.nimg;
+  int ppc = (h.hw + want - 1) / want;
+  if (ppc < 8) ppc = 8;
+  if (ppc > h.hw) ppc = h.hw;
+  *pix_per_cta = ppc;
+  *chunks = (h.hw + ppc - 1) / ppc;
+  return B200SD_OK;
+}
+
+}  // namespace b200sd
+
+using namespace b200sd;
+
+extern "C" int b200sd_groupnorm_stats(const b200sd_groupnorm_params* hp, b200sd_stream stream_) {
+  B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "groupnorm_stats: params is NULL");
+  int ppc, chunks;
+  if (int e = gn_check(*hp, &ppc, &chunks)) return e;
+  const b200sd_groupnorm_params& h = *hp;
+  dim3 grid(chunks, h.nimg);
+  gn_stats_kernel<<<grid, kNormThreads, h.groups * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const bf16*>(h.x0), static_cast<const bf16*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}
+
+extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_stream stream_) {
+  B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "groupnorm_apply: params is NULL");
+  int ppc, chunks;
+  if (int e = gn_check(*hp, &ppc, &chunks)) return e;
+  const b200sd_groupnorm_params& h = *hp;
+  B200SD_REQUIRE(h.out && h.gamma && h.beta, B200SD_ERR_BAD_ARGUMENT, "groupnorm_apply: out/gamma/beta required");
+  const int C = h.c0 + h.c1;
+  B200SD_REQUIRE(C * 2 * sizeof(float) <= 48 * 1024, B200SD_ERR_TOO_LARGE, "groupnorm_apply: C too large");
+  dim3 grid(chunks, h.nimg);
+  gn_apply_kernel<<<grid, kNormThreads, C * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const bf16*>(h.x0), static_cast<const bf16*>(h.x1), h.stats, h.gamma, h.beta,
+      static_cast<bf16*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}
+
+extern "C" int b200sd_layernorm(const b200sd_layernorm_params* hp, b200sd_stream stream_) {
+  B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "layernorm: params is NULL");
+  const b200sd_layernorm_params& h = *hp;
+  B200SD_REQUIRE(h.x && h.out && h.gamma && h.beta && h.rows > 0 && h.c > 0, B200SD_ERR_BAD_ARGUMENT,
+                 "layernorm: bad arguments");
+  B200SD_REQUIRE((h.c % 8) == 0 && h.c <= 4096, B200SD_ERR_BAD_SHAPE, "layernorm: c must be a multiple of 8, <= 4096");
+  B200SD_REQUIRE(aligned16(h.x) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT, "layernorm: 16-byte alignment");
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  const int grid = ceil_div(h.rows, kNormThreads / 32);
+  const bf16* x = static_cast<const bf16*>(h.x);
+  bf16* o = static_cast<bf16*>(h.out);
+  if (h.c <= 512)
+    layernorm_kernel<2><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+  else if (h.c <= 1280)
+    layernorm_kernel<5><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+  else
+    layernorm_kernel<16><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}
+
+extern "C" int b200sd_softmax_rows(const b200sd_softmax_params* hp, b200sd_stream stream_) {
+  B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "softmax_rows: params is NULL");
+  const b200sd_softmax_params& h = *hp;
+  B200SD_REQUIRE(h.x && h.rows > 0 && h.cols > 0, B200SD_ERR_BAD_ARGUMENT, "softmax_rows: bad arguments");
+  B200SD_REQUIRE((h.cols % 8) == 0 && h.cols <= kNormThreads * 8 * 8, B200SD_ERR_BAD_SHAPE,
+                 "softmax_rows: cols must be a multiple of 8, <= %d", kNormThreads * 8 * 8);
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  bf16* x = static_cast<bf16*>(h.x);
+  if (h.cols <= kNormThreads * 8 * 2)
+    softmax_rows_kernel<2><<<h.rows, kNormThreads, 0, s>>>(x, h.cols);
+  else
+    softmax_rows_kernel<8><<<h.rows, kNormThreads, 0, s>>>(x, h.cols);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}

@@ -1,0 +1,180 @@
+"""ctypes binding of libb200sd.so (the C ABI in include/b200sd.h).
+
+This is the only way the Python host reaches the GPU kernels.  There is deliberately no fallback: if the shared
+library is missing or a call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+_LIB_PATH = Path(__file__).resolve().parent / "libb200sd.so"
+_lib = None
+
+ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU = 0, 1, 2, 3
+BF16, F32 = 0, 1
+ST_TIMESTEP, ST_IN_SCALE, ST_KIND, ST_C0, ST_C1, ST_C2, ST_C3, ST_W0, ST_PNDM_MODE, ST_PUSH, ST_WIDTH = (
+    0, 1, 2, 3, 4, 5, 6, 7, 11, 12, 16)
+
+vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+
+
+class GemmParams(C.Structure):
+    _fields_ = [("a0", vp), ("a1", vp), ("w", vp), ("out", vp), ("bias", vp), ("rowbias", vp), ("residual", vp),
+                ("nimg", i32), ("h", i32), ("w_", i32), ("c0", i32), ("c1", i32), ("ld0", i32), ("ld1", i32),
+                ("n", i32), ("ksize", i32), ("ldc", i32), ("ldr", i32), ("ld_rowbias", i32), ("act", i32),
+                ("out_dtype", i32), ("bn_hint", i32), ("alpha", f32)]
+
+
+class AttnParams(C.Structure):
+    _fields_ = [("q", vp), ("k", vp), ("v", vp), ("out", vp),
+                ("batch", i32), ("heads", i32), ("nq", i32), ("nk", i32), ("d", i32),
+                ("ldq", i32), ("ldk", i32), ("ldv", i32), ("ldo", i32), ("causal", i32), ("scale", f32)]
+
+
+class GroupNormParams(C.Structure):
+    _fields_ = [("x0", vp), ("x1", vp), ("stats", vp), ("gamma", vp), ("beta", vp), ("out", vp),
+                ("nimg", i32), ("hw", i32), ("c0", i32), ("c1", i32), ("groups", i32), ("silu", i32), ("eps", f32)]
+
+
+class LayerNormParams(C.Structure):
+    _fields_ = [("x", vp), ("gamma", vp), ("beta", vp), ("out", vp), ("rows", i32), ("c", i32), ("eps", f32)]
+
+
+class PrepParams(C.Structure):
+    _fields_ = [("latents", vp), ("out", vp), ("step_table", vp), ("step_counter", vp),
+                ("b", i32), ("hw", i32), ("cfg", i32)]
+
+
+class TembParams(C.Structure):
+    _fields_ = [("out", vp), ("step_table", vp), ("step_counter", vp), ("rows", i32), ("dim", i32)]
+
+
+class SchedParams(C.Structure):
+    _fields_ = [("eps", vp), ("latents", vp), ("history", vp), ("cur_sample", vp), ("step_table", vp),
+                ("step_counter", vp), ("b", i32), ("hw", i32), ("ld_eps", i32), ("cfg", i32),
+                ("guidance_scale", f32)]
+
+
+class UpsampleParams(C.Structure):
+    _fields_ = [("x", vp), ("out", vp), ("nimg", i32), ("h", i32), ("w_", i32), ("c", i32)]
+
+
+class Im2colS2Params(C.Structure):
+    _fields_ = [("x", vp), ("out", vp), ("nimg", i32), ("h", i32), ("w_", i32), ("c", i32)]
+
+
+class EmbedParams(C.Structure):
+    _fields_ = [("ids", vp), ("tok", vp), ("pos", vp), ("out", vp),
+                ("rows", i32), ("seq", i32), ("c", i32), ("vocab", i32)]
+
+
+class DenormParams(C.Structure):
+    _fields_ = [("x", vp), ("out", vp), ("npix", i64), ("ldx", i32)]
+
+
+class LatentCastParams(C.Structure):
+    _fields_ = [("latents", vp), ("out", vp), ("b", i32), ("hw", i32), ("scale", f32)]
+
+
+class SoftmaxParams(C.Structure):
+    _fields_ = [("x", vp), ("rows", i32), ("cols", i32)]
+
+
+# declaration order of include/b200sd.h (b200sd_struct_sizes reports sizeof() in this order)
+STRUCTS = [GemmParams, AttnParams, GroupNormParams, LayerNormParams, PrepParams, TembParams, SchedParams,
+           UpsampleParams, Im2colS2Params, EmbedParams, DenormParams, LatentCastParams, SoftmaxParams]
+
+# entry point -> params struct (None = special signature); must list every symbol include/b200sd.h declares
+ENTRY_POINTS = {
+    "b200sd_version": None,
+    "b200sd_last_error": None,
+    "b200sd_device_info": None,
+    "b200sd_struct_sizes": None,
+    "b200sd_gemm": GemmParams,
+    "b200sd_attention": AttnParams,
+    "b200sd_groupnorm_stats": GroupNormParams,
+    "b200sd_groupnorm_apply": GroupNormParams,
+    "b200sd_layernorm": LayerNormParams,
+    "b200sd_prep_unet_input": PrepParams,
+    "b200sd_timestep_embedding": TembParams,
+    "b200sd_cfg_scheduler_step": SchedParams,
+    "b200sd_upsample2x": UpsampleParams,
+    "b200sd_im2col_s2": Im2colS2Params,
+    "b200sd_im2col_s2_bytes": None,
+    "b200sd_clip_embed": EmbedParams,
+    "b200sd_denorm_u8": DenormParams,
+    "b200sd_latent_to_bf16": LatentCastParams,
+    "b200sd_softmax_rows": SoftmaxParams,
+}
+
+
+class B200SDError(RuntimeError):
+    pass
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def load():
+    """Load libb200sd.so (once).  Raises if it has not been built — there is no other execution path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise B200SDError(
+            f"{_LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). b200sd has no CPU or library fallback.")
+    lib = C.CDLL(str(_LIB_PATH))
+    lib.b200sd_version.restype = C.c_int
+    lib.b200sd_last_error.restype = C.c_char_p
+    lib.b200sd_device_info.argtypes = [C.POINTER(i32)]
+    lib.b200sd_struct_sizes.argtypes = [C.POINTER(i32), i32]
+    for name, st in ENTRY_POINTS.items():
+        if st is None:
+            continue
+        fn = getattr(lib, name)
+        fn.argtypes = [C.POINTER(st), vp]
+        fn.restype = C.c_int
+    lib.b200sd_im2col_s2_bytes.argtypes = [C.POINTER(Im2colS2Params)]
+    lib.b200sd_im2col_s2_bytes.restype = C.c_size_t
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str = "") -> None:
+    if code != 0:
+        msg = load().b200sd_last_error().decode(errors="replace")
+        raise B200SDError(f"{what or 'b200sd call'} failed ({code}): {msg}")
+
+
+def struct_sizes():
+    lib = load()
+    buf = (i32 * 32)()
+    n = lib.b200sd_struct_sizes(buf, 32)
+    return [buf[i] for i in range(n)]
+
+
+def device_info():
+    lib = load()
+    buf = (i32 * 4)()
+    check(lib.b200sd_device_info(buf), "device_info")
+    return {"sm_count": buf[0], "cc": (buf[1], buf[2]), "max_smem_optin": buf[3]}
+
+
+class Call:
+    """One prepared kernel invocation: (entry point, params struct).  Calling it enqueues the kernel on `stream`."""
+
+    __slots__ = ("fn", "params", "name", "keep")
+
+    def __init__(self, name: str, params, keep=()):
+        self.fn = getattr(load(), name)
+        self.params = params
+        self.name = name
+        self.keep = keep  # tensors referenced by raw pointer — keep them alive
+
+    def __call__(self, stream: int) -> None:
+        rc = self.fn(C.byref(self.params), stream)
+        if rc != 0:
+            check(rc, self.name)

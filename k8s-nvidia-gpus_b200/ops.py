@@ -1,0 +1,166 @@
+"""Tensor-level wrappers over the C ABI: weight packing + `Call` builders.
+
+Every function here returns a prepared `lib.Call` (or runs it immediately when `stream` is given); device memory is
+owned by torch tensors passed in by the caller — the library never allocates.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import lib as L
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def ceil_to(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+# ------------------------------------------------------------------------------------------------ weight packing
+def pack_conv_weight(w: torch.Tensor, split=None) -> torch.Tensor:
+    """[Cout, Cin, kh, kw] (upstream layout) -> bf16 [Cout, kh*kw, c0p + c1p], channels zero-padded to 64
+    per source so each 64-wide K block of the implicit GEMM belongs to exactly one source / filter tap."""
+    cout, cin, kh, kw = w.shape
+    split = split or (cin,)
+    assert sum(split) == cin
+    wt = w.permute(0, 2, 3, 1).reshape(cout, kh * kw, cin)
+    parts, off = [], 0
+    for c in split:
+        cp = ceil_to(c, 64)
+        blk = torch.zeros(cout, kh * kw, cp, dtype=torch.float32)
+        blk[:, :, :c] = wt[:, :, off:off + c]
+        parts.append(blk)
+        off += c
+    return torch.cat(parts, dim=2).to(torch.bfloat16).contiguous()
+
+
+def pack_linear_weight(w: torch.Tensor, split=None) -> torch.Tensor:
+    """[N, K] -> bf16 [N, 1, Kp]."""
+    return pack_conv_weight(w[:, :, None, None], split)
+
+
+def geglu_perm(n2: int) -> torch.Tensor:
+    """Row permutation for the GEGLU input projection [2F, K]: packed 64-row groups = [32 value rows | 32 gate rows]."""
+    f = n2 // 2
+    assert f % 32 == 0
+    idx = torch.arange(f).view(-1, 32)
+    return torch.cat([idx, idx + f], dim=1).reshape(-1)
+
+
+# ------------------------------------------------------------------------------------------------ call builders
+def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld1=None, bias=None, rowbias=None,
+         ld_rowbias=0, residual=None, ldr=0, ldc=None, act=L.ACT_NONE, out_dtype=None, alpha=1.0, bn_hint=0):
+    p = L.GemmParams()
+    p.a0, p.a1, p.w, p.out = _ptr(a0), _ptr(a1), _ptr(w), _ptr(out)
+    p.bias, p.rowbias, p.residual = _ptr(bias), _ptr(rowbias), _ptr(residual)
+    p.nimg, p.h, p.w_, p.c0, p.c1 = nimg, h, w_, c0, c1
+    p.ld0 = ld0 if ld0 is not None else c0
+    p.ld1 = ld1 if ld1 is not None else c1
+    p.n, p.ksize = n, ksize
+    n_out = n // 2 if act == L.ACT_GEGLU else n
+    p.ldc = ldc if ldc is not None else n_out
+    p.ldr = ldr if ldr else n_out
+    p.ld_rowbias = ld_rowbias
+    p.act = act
+    if out_dtype is None:
+        out_dtype = L.F32 if out.dtype == torch.float32 else L.BF16
+    p.out_dtype = out_dtype
+    p.bn_hint = bn_hint
+    p.alpha = alpha
+    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual))
+
+
+def attention(q, k, v, out, *, batch, heads, nq, nk, d, ldq, ldk, ldv, ldo, scale, causal=False):
+    p = L.AttnParams()
+    p.q, p.k, p.v, p.out = _ptr(q), _ptr(k), _ptr(v), _ptr(out)
+    p.batch, p.heads, p.nq, p.nk, p.d = batch, heads, nq, nk, d
+    p.ldq, p.ldk, p.ldv, p.ldo = ldq, ldk, ldv, ldo
+    p.causal = int(causal)
+    p.scale = scale
+    return L.Call("b200sd_attention", p, keep=(q, k, v, out))
+
+
+def groupnorm(x0, out, stats, gamma, beta, *, nimg, hw, c0, groups, eps, silu, x1=None, c1=0):
+    p = L.GroupNormParams()
+    p.x0, p.x1, p.stats, p.gamma, p.beta, p.out = _ptr(x0), _ptr(x1), _ptr(stats), _ptr(gamma), _ptr(beta), _ptr(out)
+    p.nimg, p.hw, p.c0, p.c1, p.groups, p.silu, p.eps = nimg, hw, c0, c1, groups, int(silu), eps
+    keep = (x0, x1, stats, gamma, beta, out)
+    return (L.Call("b200sd_groupnorm_stats", p, keep=keep), L.Call("b200sd_groupnorm_apply", p, keep=keep))
+
+
+def layernorm(x, out, gamma, beta, *, rows, c, eps):
+    p = L.LayerNormParams()
+    p.x, p.gamma, p.beta, p.out, p.rows, p.c, p.eps = _ptr(x), _ptr(gamma), _ptr(beta), _ptr(out), rows, c, eps
+    return L.Call("b200sd_layernorm", p, keep=(x, gamma, beta, out))
+
+
+def prep_unet_input(latents, out, step_table, step_counter, *, b, hw, cfg):
+    p = L.PrepParams()
+    p.latents, p.out, p.step_table, p.step_counter = _ptr(latents), _ptr(out), _ptr(step_table), _ptr(step_counter)
+    p.b, p.hw, p.cfg = b, hw, int(cfg)
+    return L.Call("b200sd_prep_unet_input", p, keep=(latents, out, step_table, step_counter))
+
+
+def timestep_embedding(out, step_table, step_counter, *, rows, dim):
+    p = L.TembParams()
+    p.out, p.step_table, p.step_counter, p.rows, p.dim = _ptr(out), _ptr(step_table), _ptr(step_counter), rows, dim
+    return L.Call("b200sd_timestep_embedding", p, keep=(out, step_table, step_counter))
+
+
+def cfg_scheduler_step(eps, latents, history, cur_sample, step_table, step_counter, *, b, hw, ld_eps, cfg,
+                       guidance_scale):
+    p = L.SchedParams()
+    p.eps, p.latents, p.history, p.cur_sample = _ptr(eps), _ptr(latents), _ptr(history), _ptr(cur_sample)
+    p.step_table, p.step_counter = _ptr(step_table), _ptr(step_counter)
+    p.b, p.hw, p.ld_eps, p.cfg, p.guidance_scale = b, hw, ld_eps, int(cfg), guidance_scale
+    return L.Call("b200sd_cfg_scheduler_step", p, keep=(eps, latents, history, cur_sample, step_table, step_counter))
+
+
+def upsample2x(x, out, *, nimg, h, w_, c):
+    p = L.UpsampleParams()
+    p.x, p.out, p.nimg, p.h, p.w_, p.c = _ptr(x), _ptr(out), nimg, h, w_, c
+    return L.Call("b200sd_upsample2x", p, keep=(x, out))
+
+
+def im2col_s2(x, out, *, nimg, h, w_, c):
+    p = L.Im2colS2Params()
+    p.x, p.out, p.nimg, p.h, p.w_, p.c = _ptr(x), _ptr(out), nimg, h, w_, c
+    return L.Call("b200sd_im2col_s2", p, keep=(x, out))
+
+
+def im2col_s2_bytes(*, nimg, h, w_, c) -> int:
+    p = L.Im2colS2Params()
+    p.nimg, p.h, p.w_, p.c = nimg, h, w_, c
+    return int(L.load().b200sd_im2col_s2_bytes(C.byref(p)))
+
+
+def clip_embed(ids, tok, pos, out, *, rows, seq, c, vocab):
+    p = L.EmbedParams()
+    p.ids, p.tok, p.pos, p.out, p.rows, p.seq, p.c, p.vocab = _ptr(ids), _ptr(tok), _ptr(pos), _ptr(out), rows, seq, c, vocab
+    return L.Call("b200sd_clip_embed", p, keep=(ids, tok, pos, out))
+
+
+def denorm_u8(x, out, *, npix, ldx):
+    p = L.DenormParams()
+    p.x, p.out, p.npix, p.ldx = _ptr(x), _ptr(out), npix, ldx
+    return L.Call("b200sd_denorm_u8", p, keep=(x, out))
+
+
+def latent_to_bf16(latents, out, *, b, hw, scale):
+    p = L.LatentCastParams()
+    p.latents, p.out, p.b, p.hw, p.scale = _ptr(latents), _ptr(out), b, hw, scale
+    return L.Call("b200sd_latent_to_bf16", p, keep=(latents, out))
+
+
+def softmax_rows(x, *, rows, cols):
+    p = L.SoftmaxParams()
+    p.x, p.rows, p.cols = _ptr(x), rows, cols
+    return L.Call("b200sd_softmax_rows", p, keep=(x,))
+
+
+def current_stream() -> int:
+    return torch.cuda.current_stream().cuda_stream

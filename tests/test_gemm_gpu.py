@@ -1,0 +1,142 @@
+"""GPU parity: tcgen05 implicit-GEMM conv / linear kernel (through the C ABI) vs an fp32 torch restatement of the
+same op on identical bf16-rounded inputs.  Tolerance: bf16 output rounding (2^-8 relative) + fp32 accumulation order,
+i.e. |err| <= 1e-2 * max|ref| elementwise-max — stated per test."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _report(name, got, ref, tol):
+    got = got.float()
+    ref = ref.float()
+    err = (got - ref).abs()
+    scale = ref.abs().max().item() + 1e-12
+    mx = err.max().item()
+    if not (mx <= tol * scale) or torch.isnan(got).any():
+        idx = torch.nonzero(err > tol * scale)
+        print(f"\n[{name}] FAIL max_err={mx:.4g} scale={scale:.4g} bad={idx.shape[0]}/{err.numel()} nan={torch.isnan(got).sum().item()}")
+        print("  first bad idx:", idx[:8].tolist())
+        flat = err.reshape(-1, err.shape[-1])
+        print("  bad rows (first 16):", torch.nonzero(flat.max(dim=1).values > tol * scale)[:16].flatten().tolist())
+        print("  bad cols (first 16):", torch.nonzero(flat.max(dim=0).values > tol * scale)[:16].flatten().tolist())
+        print("  got[0,:8]", got.reshape(-1, got.shape[-1])[0, :8].tolist())
+        print("  ref[0,:8]", ref.reshape(-1, ref.shape[-1])[0, :8].tolist())
+    assert mx <= tol * scale, f"{name}: max err {mx} > {tol} * {scale}"
+    assert not torch.isnan(got).any()
+
+
+def _rand(*shape, scale=1.0):
+    return (torch.randn(*shape, device="cuda") * scale).to(torch.bfloat16)
+
+
+@pytest.mark.parametrize("M,K,N,bn", [(128, 64, 128, 128), (300, 320, 200, 0), (16, 1280, 1280, 0),
+                                      (1232, 768, 640, 0), (4096, 320, 960, 0), (513, 72, 40, 32)])
+def test_linear(cuda_lib, b200sd, M, K, N, bn):
+    torch.manual_seed(0)
+    ops = b200sd.ops
+    x = _rand(M, K)
+    w = _rand(N, K, scale=K ** -0.5)
+    bias = torch.randn(N, device="cuda")
+    wp = ops.pack_linear_weight(w.float().cpu()).cuda()
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.gemm(x, wp, out, nimg=1, h=1, w_=M, c0=K, n=N, bias=bias, bn_hint=bn)(ops.current_stream())
+    torch.cuda.synchronize()
+    ref = x.float() @ w.float().t() + bias
+    _report(f"linear {M}x{K}x{N}", out, ref, 1e-2)
+
+
+def test_linear_epilogues(cuda_lib, b200sd):
+    torch.manual_seed(1)
+    ops, L = b200sd.ops, b200sd.lib
+    M, K, N = 520, 256, 384
+    x = _rand(M, K)
+    w = _rand(N, K, scale=K ** -0.5)
+    bias = torch.randn(N, device="cuda")
+    res = _rand(M, N)
+    wp = ops.pack_linear_weight(w.float().cpu()).cuda()
+    acc = x.float() @ w.float().t()
+    s = ops.current_stream()
+    # residual + bias, bf16 out
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(x, wp, out, nimg=1, h=1, w_=M, c0=K, n=N, bias=bias, residual=res)(s)
+    torch.cuda.synchronize()
+    _report("bias+residual", out, acc + bias + res.float(), 1e-2)
+    # silu, fp32 out, alpha
+    out32 = torch.empty(M, N, device="cuda", dtype=torch.float32)
+    ops.gemm(x, wp, out32, nimg=1, h=1, w_=M, c0=K, n=N, bias=bias, act=L.ACT_SILU, alpha=0.5)(s)
+    torch.cuda.synchronize()
+    _report("silu fp32", out32, F.silu(0.5 * acc + bias), 2e-5 * 50)
+    # quick gelu
+    ops.gemm(x, wp, out, nimg=1, h=1, w_=M, c0=K, n=N, bias=bias, act=L.ACT_QUICK_GELU)(s)
+    torch.cuda.synchronize()
+    z = acc + bias
+    _report("quick_gelu", out, z * torch.sigmoid(1.702 * z), 1e-2)
+    # GEGLU: weight [2F, K] -> packed; out [M, F]
+    Fh = 256
+    w2 = _rand(2 * Fh, K, scale=K ** -0.5)
+    b2 = torch.randn(2 * Fh, device="cuda")
+    perm = ops.geglu_perm(2 * Fh)
+    wp2 = ops.pack_linear_weight(w2.float().cpu()[perm]).cuda()
+    b2p = b2[perm.cuda()].contiguous()
+    outg = torch.empty(M, Fh, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(x, wp2, outg, nimg=1, h=1, w_=M, c0=K, n=2 * Fh, bias=b2p, act=L.ACT_GEGLU)(s)
+    torch.cuda.synchronize()
+    z = x.float() @ w2.float().t() + b2
+    _report("geglu", outg, z[:, :Fh] * F.gelu(z[:, Fh:]), 1e-2)
+
+
+@pytest.mark.parametrize("nimg,H,W,cin,cout", [(2, 16, 16, 64, 128), (3, 8, 8, 128, 64), (1, 64, 64, 320, 320),
+                                               (2, 32, 32, 8, 320), (2, 64, 64, 320, 4), (1, 24, 20, 32, 96),
+                                               (1, 256, 256, 128, 128)])
+def test_conv3x3(cuda_lib, b200sd, nimg, H, W, cin, cout):
+    torch.manual_seed(2)
+    ops = b200sd.ops
+    x = _rand(nimg, H, W, cin)                       # NHWC
+    w = _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+    bias = torch.randn(cout, device="cuda")
+    wp = ops.pack_conv_weight(w.float().cpu()).cuda()
+    out = torch.full((nimg, H, W, cout), float("nan"), device="cuda", dtype=torch.float32)
+    ops.gemm(x, wp, out, nimg=nimg, h=H, w_=W, c0=cin, n=cout, ksize=3, bias=bias)(ops.current_stream())
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=1).permute(0, 2, 3, 1)
+    _report(f"conv3x3 {nimg}x{H}x{W} {cin}->{cout}", out, ref, 2e-3)
+
+
+def test_conv3x3_concat_temb_residual(cuda_lib, b200sd):
+    """ResnetBlock2D pieces in one call: two-source (skip concat) conv + bias + per-image time-embedding row bias,
+    and the 1x1 shortcut over the same virtual concat feeding a residual epilogue."""
+    torch.manual_seed(3)
+    ops = b200sd.ops
+    nimg, H, W, c0, c1, cout = 4, 8, 8, 128, 64, 128
+    a0, a1 = _rand(nimg, H, W, c0), _rand(nimg, H, W, c1)
+    cin = c0 + c1
+    w = _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+    wsc = _rand(cout, cin, 1, 1, scale=cin ** -0.5)
+    bias = torch.randn(cout, device="cuda")
+    temb = torch.randn(nimg, 512, device="cuda")     # row-bias slice at column offset 128, ld 512
+    s = ops.current_stream()
+    sc = torch.empty(nimg, H, W, cout, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a0, ops.pack_conv_weight(wsc.float().cpu(), (c0, c1)).cuda(), sc, nimg=nimg, h=H, w_=W, c0=c0, a1=a1,
+             c1=c1, n=cout, ksize=1)(s)
+    out = torch.empty(nimg, H, W, cout, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a0, ops.pack_conv_weight(w.float().cpu(), (c0, c1)).cuda(), out, nimg=nimg, h=H, w_=W, c0=c0, a1=a1,
+             c1=c1, n=cout, ksize=3, bias=bias, rowbias=temb[:, 128:], ld_rowbias=512, residual=sc)(s)
+    torch.cuda.synchronize()
+    xin = torch.cat([a0, a1], dim=-1).float().permute(0, 3, 1, 2)
+    ref_sc = F.conv2d(xin, wsc.float()).permute(0, 2, 3, 1)
+    _report("shortcut 1x1 concat", sc, ref_sc, 1e-2)
+    ref = F.conv2d(xin, w.float(), bias, padding=1).permute(0, 2, 3, 1) + temb[:, None, None, 128:256] + sc.float()
+    _report("conv3x3 concat+temb+residual", out, ref, 1e-2)
+
+
+def test_gemm_rejects_bad_arguments(cuda_lib, b200sd):
+    ops = b200sd.ops
+    x = _rand(64, 60)
+    w = _rand(64, 64)
+    out = torch.empty(64, 64, device="cuda", dtype=torch.bfloat16)
+    with pytest.raises(b200sd.lib.B200SDError, match="multiples of 8"):
+        ops.gemm(x, w, out, nimg=1, h=1, w_=64, c0=60, n=64)(ops.current_stream())
+    with pytest.raises(b200sd.lib.B200SDError, match="ksize"):
+        ops.gemm(x, w, out, nimg=1, h=1, w_=64, c0=64, n=64, ksize=5)(ops.current_stream())

@@ -1,0 +1,190 @@
+"""GPU parity for the bandwidth-bound kernels and flash attention (C ABI) vs fp32 torch restatements."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from test_gemm_gpu import _rand, _report
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("nimg,hw,c0,c1,groups,silu", [(2, 64, 320, 0, 32, True), (3, 256, 1280, 640, 32, True),
+                                                       (2, 1024, 640, 320, 32, False), (1, 4096, 128, 0, 32, True),
+                                                       (2, 64, 1280, 1280, 32, True), (2, 100, 32, 0, 8, True)])
+def test_groupnorm(cuda_lib, b200sd, nimg, hw, c0, c1, groups, silu):
+    torch.manual_seed(0)
+    ops = b200sd.ops
+    C = c0 + c1
+    x0 = (_rand(nimg, hw, c0).float() * 2 + 0.7).to(torch.bfloat16)
+    x1 = (_rand(nimg, hw, c1).float() * 0.5 - 1.1).to(torch.bfloat16) if c1 else None
+    gamma = torch.randn(C, device="cuda")
+    beta = torch.randn(C, device="cuda")
+    stats = torch.zeros(nimg, groups, 2, device="cuda")
+    out = torch.empty(nimg, hw, C, device="cuda", dtype=torch.bfloat16)
+    st, ap = ops.groupnorm(x0, out, stats, gamma, beta, nimg=nimg, hw=hw, c0=c0, groups=groups, eps=1e-5, silu=silu,
+                           x1=x1, c1=c1)
+    s = ops.current_stream()
+    st(s)
+    ap(s)
+    torch.cuda.synchronize()
+    x = x0.float() if x1 is None else torch.cat([x0.float(), x1.float()], dim=-1)
+    ref = F.group_norm(x.permute(0, 2, 1), groups, gamma, beta, 1e-5).permute(0, 2, 1)
+    if silu:
+        ref = F.silu(ref)
+    _report(f"groupnorm {nimg}x{hw}x{C}", out, ref, 1e-2)
+
+
+@pytest.mark.parametrize("rows,c", [(77, 768), (4096, 320), (1000, 640), (300, 1280), (64, 32), (10, 2048)])
+def test_layernorm(cuda_lib, b200sd, rows, c):
+    torch.manual_seed(0)
+    ops = b200sd.ops
+    x = (_rand(rows, c).float() * 3 + 1).to(torch.bfloat16)
+    g, b = torch.randn(c, device="cuda"), torch.randn(c, device="cuda")
+    out = torch.empty_like(x)
+    ops.layernorm(x, out, g, b, rows=rows, c=c, eps=1e-5)(ops.current_stream())
+    torch.cuda.synchronize()
+    _report(f"layernorm {rows}x{c}", out, F.layer_norm(x.float(), (c,), g, b, 1e-5), 1e-2)
+
+
+def test_softmax_rows(cuda_lib, b200sd):
+    ops = b200sd.ops
+    x = (_rand(50, 4096).float() * 4).to(torch.bfloat16)
+    ref = torch.softmax(x.float(), dim=-1)
+    ops.softmax_rows(x, rows=50, cols=4096)(ops.current_stream())
+    torch.cuda.synchronize()
+    _report("softmax_rows", x, ref, 1e-2)
+
+
+@pytest.mark.parametrize("batch,heads,nq,nk,d,causal", [
+    (1, 1, 128, 128, 64, False),     # single tile, aligned head dim
+    (2, 3, 256, 384, 64, False),     # multiple kv tiles (online softmax + O rescale)
+    (2, 8, 200, 77, 40, False),      # cross-attention shape: ragged nq/nk, d=40
+    (2, 8, 1024, 1024, 80, False),   # two d atoms
+    (1, 8, 256, 256, 160, False),    # three d atoms
+    (2, 8, 64, 64, 160, False),      # 8x8 level
+    (3, 12, 77, 77, 64, True),       # CLIP causal
+    (1, 2, 300, 300, 64, True),      # causal across tiles
+    (1, 8, 4096, 4096, 40, False),   # SD1.5 64x64 level
+])
+def test_attention(cuda_lib, b200sd, batch, heads, nq, nk, d, causal):
+    torch.manual_seed(0)
+    ops = b200sd.ops
+    C = heads * d
+    # q from a fused QKV-like buffer (ld = 3C), k/v from a KV buffer (ld = 2C)
+    qkv = _rand(batch, nq, 3 * C)
+    kv = _rand(batch, nk, 2 * C)
+    q = qkv[..., :C]
+    k, v = kv[..., :C], kv[..., C:]
+    out = torch.full((batch, nq, C), float("nan"), device="cuda", dtype=torch.bfloat16)
+    scale = d ** -0.5
+    ops.attention(q, k, v, out, batch=batch, heads=heads, nq=nq, nk=nk, d=d, ldq=3 * C, ldk=2 * C, ldv=2 * C, ldo=C,
+                  scale=scale, causal=causal)(ops.current_stream())
+    torch.cuda.synchronize()
+    qf = q.float().view(batch, nq, heads, d).transpose(1, 2)
+    kf = k.float().view(batch, nk, heads, d).transpose(1, 2)
+    vf = v.float().view(batch, nk, heads, d).transpose(1, 2)
+    s = qf @ kf.transpose(-1, -2) * scale
+    if causal:
+        mask = torch.ones(nq, nk, device="cuda", dtype=torch.bool).tril()
+        s = s.masked_fill(~mask, float("-inf"))
+    ref = (torch.softmax(s, dim=-1) @ vf).transpose(1, 2).reshape(batch, nq, C)
+    _report(f"attention b{batch} h{heads} {nq}x{nk} d{d} causal={causal}", out, ref, 2e-2)
+
+
+def _table(rows):
+    t = torch.zeros(len(rows), 16)
+    for i, r in enumerate(rows):
+        for k, v in r.items():
+            t[i, k] = v
+    return t.cuda()
+
+
+def test_prep_temb_sched_ddim_euler(cuda_lib, b200sd):
+    torch.manual_seed(0)
+    ops, L = b200sd.ops, b200sd.lib
+    b, hw = 3, 64
+    lat = torch.randn(b, hw, 4, device="cuda")
+    table = _table([
+        {L.ST_TIMESTEP: 961.0, L.ST_IN_SCALE: 0.5, L.ST_KIND: 0, L.ST_C0: 0.9, L.ST_C1: 0.4, L.ST_C2: 0.6, L.ST_C3: 0.8},
+        {L.ST_TIMESTEP: 41.0, L.ST_IN_SCALE: 1.0, L.ST_KIND: 1, L.ST_C0: -0.7, L.ST_C1: 3.0},
+    ])
+    counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+    s = ops.current_stream()
+    xin = torch.empty(2 * b, hw, 8, device="cuda", dtype=torch.bfloat16)
+    ops.prep_unet_input(lat, xin, table, counter, b=b, hw=hw, cfg=True)(s)
+    temb = torch.empty(2 * b, 320, device="cuda", dtype=torch.bfloat16)
+    ops.timestep_embedding(temb, table, counter, rows=2 * b, dim=320)(s)
+    torch.cuda.synchronize()
+    ref_in = torch.cat([lat * 0.5, torch.zeros_like(lat)], dim=-1)
+    _report("prep", xin, torch.cat([ref_in, ref_in]), 1e-2)
+    i = torch.arange(160, device="cuda", dtype=torch.float32)
+    ang = 961.0 * torch.exp(-math.log(10000.0) * i / 160)
+    ref_t = torch.cat([torch.cos(ang), torch.sin(ang)]).expand(2 * b, 320)
+    _report("temb", temb, ref_t, 1e-2)
+    # SURVEY App. C anchors (t=961, dim 320)
+    assert abs(temb[0, 0].item() - 0.94689709) < 4e-3 and abs(temb[0, 160].item() + 0.32153678) < 4e-3
+
+    eps = torch.randn(2 * b, hw, 4, device="cuda")
+    gs = 7.5
+    e = eps[:b] + gs * (eps[b:] - eps[:b])
+    lat0 = lat.clone()
+    ops.cfg_scheduler_step(eps, lat, None, None, table, counter, b=b, hw=hw, ld_eps=4, cfg=True, guidance_scale=gs)(s)
+    torch.cuda.synchronize()
+    x0 = (lat0 - 0.9 * e) / 0.4
+    _report("ddim", lat, 0.6 * x0 + 0.8 * e, 1e-5)
+    assert counter.tolist() == [1, 0]
+    lat1 = lat.clone()
+    ops.cfg_scheduler_step(eps, lat, None, None, table, counter, b=b, hw=hw, ld_eps=4, cfg=True, guidance_scale=gs)(s)
+    torch.cuda.synchronize()
+    _report("euler", lat, lat1 + e * -0.7, 1e-5)
+    assert counter.tolist() == [2, 0]
+
+
+def test_layout_kernels(cuda_lib, b200sd):
+    torch.manual_seed(0)
+    ops = b200sd.ops
+    s = ops.current_stream()
+    x = _rand(2, 6, 10, 64)
+    up = torch.empty(2, 12, 20, 64, device="cuda", dtype=torch.bfloat16)
+    ops.upsample2x(x, up, nimg=2, h=6, w_=10, c=64)(s)
+    ref = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest").permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert torch.equal(up.float(), ref)
+
+    # stride-2 3x3 conv through im2col + linear gemm
+    nimg, H, W, c, cout = 2, 16, 16, 32, 64
+    x = _rand(nimg, H, W, c)
+    w = _rand(cout, c, 3, 3, scale=(9 * c) ** -0.5)
+    nbytes = ops.im2col_s2_bytes(nimg=nimg, h=H, w_=W, c=c)
+    assert nbytes == nimg * 8 * 8 * 9 * 64 * 2
+    col = torch.empty(nbytes // 2, device="cuda", dtype=torch.bfloat16)
+    ops.im2col_s2(x, col, nimg=nimg, h=H, w_=W, c=c)(s)
+    out = torch.empty(nimg, 8, 8, cout, device="cuda", dtype=torch.float32)
+    ops.gemm(col, ops.pack_conv_weight(w.float().cpu()).cuda().view(cout, 1, -1), out, nimg=1, h=1, w_=nimg * 64,
+             c0=9 * 64, n=cout)(s)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), stride=2, padding=1).permute(0, 2, 3, 1)
+    _report("conv s2 via im2col", out, ref, 2e-3)
+
+    ids = torch.randint(0, 1000, (2 * 77,), device="cuda", dtype=torch.int32)
+    tok, pos = _rand(1000, 64), _rand(77, 64)
+    emb = torch.empty(2 * 77, 64, device="cuda", dtype=torch.bfloat16)
+    ops.clip_embed(ids, tok, pos, emb, rows=2 * 77, seq=77, c=64, vocab=1000)(s)
+    torch.cuda.synchronize()
+    ref = tok.float()[ids.long()] + pos.float().repeat(2, 1)
+    _report("clip_embed", emb, ref, 1e-2)
+
+    img = torch.randn(1000, 4, device="cuda") * 1.5
+    u8 = torch.empty(1000, 3, device="cuda", dtype=torch.uint8)
+    ops.denorm_u8(img, u8, npix=1000, ldx=4)(s)
+    torch.cuda.synchronize()
+    ref = ((img[:, :3] / 2 + 0.5).clamp(0, 1) * 255).round().to(torch.uint8)
+    assert torch.equal(u8, ref)
+
+    lat = torch.randn(2, 64, 4, device="cuda")
+    o = torch.empty(2, 64, 8, device="cuda", dtype=torch.bfloat16)
+    ops.latent_to_bf16(lat, o, b=2, hw=64, scale=1 / 0.18215)(s)
+    torch.cuda.synchronize()
+    _report("latent_to_bf16", o, torch.cat([lat / 0.18215, torch.zeros_like(lat)], -1), 1e-2)
