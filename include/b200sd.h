@@ -9,7 +9,10 @@
  * Conventions
  *   - extern "C", plain pointers and sizes; the CALLER owns every buffer (inputs, outputs, scratch).
  *   - all pointers are device pointers unless a field says "host".
- *   - activations are NHWC ("channels-last") bf16; token tensors [B, HW, C] alias the same memory.
+ *   - activations and weights are 16-bit floats, written "act16" below: IEEE fp16 by default — the reference's own
+ *     CUDA dtype (TORCH_DTYPE = float16, configmap.yaml:31) — or bfloat16 when the library is built with
+ *     -DB200SD_ACT_BF16; b200sd_act_dtype() tells which.  Accumulation, statistics and the latents are fp32.
+ *   - activations are NHWC ("channels-last"); token tensors [B, HW, C] alias the same memory.
  *   - every call is asynchronous on `stream`, performs no allocation and no synchronisation, and can be
  *     captured into a CUDA graph (exception: b200sd_device_info, which only queries).
  *   - return value 0 = ok, negative = b200sd_status; b200sd_last_error() (thread-local) has the detail.
@@ -38,9 +41,11 @@ enum b200sd_status {
 };
 
 enum b200sd_act { B200SD_ACT_NONE = 0, B200SD_ACT_SILU = 1, B200SD_ACT_QUICK_GELU = 2, B200SD_ACT_GEGLU = 3 };
-enum b200sd_dtype { B200SD_BF16 = 0, B200SD_F32 = 1 };
+enum b200sd_dtype { B200SD_ACT16 = 0, B200SD_F32 = 1 }; /* output type selector: act16 (see above) or f32 */
 
 int b200sd_version(void);
+/* 16-bit element type this build computes in: 0 = bfloat16, 1 = IEEE fp16. */
+int b200sd_act_dtype(void);
 const char* b200sd_last_error(void);
 /* out[0]=SM count, out[1]=cc major, out[2]=cc minor, out[3]=max dynamic smem per block. */
 int b200sd_device_info(int32_t* out4);
@@ -57,18 +62,18 @@ int b200sd_device_info(int32_t* out4);
  * A is the virtual channel-concatenation of up to two NHWC sources (a0: c0 channels, a1: c1 channels; a1 may be
  * NULL with c1 = 0) — the UNet up-path skip concat is never materialised.  ksize = 1 or 3 (stride 1, zero padding
  * ksize/2).  A linear layer over M rows is nimg = 1, h = 1, w = M, ksize = 1.
- * W is bf16 [n, ksize*ksize, c0p + c1p] with c0p/c1p = c0/c1 rounded up to 64 (zero padded), K contiguous.
+ * W is act16 [n, ksize*ksize, c0p + c1p] with c0p/c1p = c0/c1 rounded up to 64 (zero padded), K contiguous.
  * GEGLU: W rows/bias packed in 64-row groups [32 value rows | 32 gate rows]; out has n/2 columns.
  * Requirements: c0, c1, ld0, ld1 multiples of 8; pointers 16-byte aligned.
  */
 typedef struct {
-  const void* a0;       /* bf16 NHWC source 0, pixel stride ld0 elements */
-  const void* a1;       /* bf16 NHWC source 1 or NULL */
-  const void* w;        /* bf16 packed weights */
-  void* out;            /* bf16 or f32 [M, ldc] */
+  const void* a0;       /* act16 NHWC source 0, pixel stride ld0 elements */
+  const void* a1;       /* act16 NHWC source 1 or NULL */
+  const void* w;        /* act16 packed weights */
+  void* out;            /* act16 or f32 [M, ldc] */
   const float* bias;    /* f32 [n] or NULL */
   const float* rowbias; /* f32 [nimg, ld_rowbias] or NULL (time-embedding projection) */
-  const void* residual; /* bf16 [M, ldr] or NULL */
+  const void* residual; /* act16 [M, ldr] or NULL */
   int32_t nimg, h, w_, c0, c1, ld0, ld1;
   int32_t n;      /* GEMM N (weight rows) */
   int32_t ksize;  /* 1 or 3 */
@@ -111,7 +116,7 @@ typedef struct {
   float* stats;
   const float* gamma; /* f32 [c0+c1] */
   const float* beta;  /* f32 [c0+c1] */
-  void* out;          /* bf16 [nimg, hw, c0+c1] */
+  void* out;          /* act16 [nimg, hw, c0+c1] */
   int32_t nimg, hw, c0, c1, groups;
   int32_t silu;
   float eps;
@@ -121,10 +126,10 @@ int b200sd_groupnorm_apply(const b200sd_groupnorm_params* p, b200sd_stream strea
 
 /* LayerNorm over the last dim. Replaces nn.LayerNorm in BasicTransformerBlock.norm1-3 / CLIPEncoderLayer (K9). */
 typedef struct {
-  const void* x; /* bf16 [rows, c] */
+  const void* x; /* act16 [rows, c] */
   const float* gamma;
   const float* beta;
-  void* out; /* bf16 [rows, c] */
+  void* out; /* act16 [rows, c] */
   int32_t rows, c;
   float eps;
 } b200sd_layernorm_params;
@@ -133,7 +138,8 @@ int b200sd_layernorm(const b200sd_layernorm_params* p, b200sd_stream stream);
 /* ---------------------------------------------------------------------------------------------------------
  * Denoise-loop glue (bandwidth-bound, fused).  A device-resident step table drives them so one captured
  * CUDA graph can be replayed for every step with no host interaction:
- *   step_table: f32 [nsteps, 16]  (see B200SD_ST_* indices), step_counter: int32 [1] on device.
+ *   step_table: f32 [nsteps, 16]  (see B200SD_ST_* indices), step_counter: int32 [2] on device
+ *   ([0] = current step, [1] = internal CTA ticket, both zero-initialised by the caller).
  */
 enum {
   B200SD_ST_TIMESTEP = 0,  /* timestep fed to the UNet */
@@ -149,7 +155,7 @@ enum {
   B200SD_ST_WIDTH = 16
 };
 
-/* latents f32 NHWC [b, hw, 4] -> UNet input bf16 [2b (or b), hw, 8] (channels 4..7 zero), scaled by IN_SCALE.
+/* latents f32 NHWC [b, hw, 4] -> UNet input act16 [2b (or b), hw, 8] (channels 4..7 zero), scaled by IN_SCALE.
  * Replaces torch.cat([latents]*2) + scheduler.scale_model_input (pipeline loop). */
 typedef struct {
   const float* latents;
@@ -160,7 +166,7 @@ typedef struct {
 } b200sd_prep_params;
 int b200sd_prep_unet_input(const b200sd_prep_params* p, b200sd_stream stream);
 
-/* Sinusoidal timestep embedding (flip_sin_to_cos, shift 0): out bf16 [rows, dim] = [cos | sin]. (a10.1, K10) */
+/* Sinusoidal timestep embedding (flip_sin_to_cos, shift 0): out act16 [rows, dim] = [cos | sin]. (a10.1, K10) */
 typedef struct {
   void* out;
   const float* step_table;
@@ -188,7 +194,7 @@ int b200sd_cfg_scheduler_step(const b200sd_sched_params* p, b200sd_stream stream
 /* ---------------------------------------------------------------------------------------------------------
  * Layout / gather helpers (bandwidth-bound).
  */
-/* nearest-neighbour 2x upsample, NHWC bf16 (Upsample2D; K13). */
+/* nearest-neighbour 2x upsample, NHWC act16 (Upsample2D; K13). */
 typedef struct {
   const void* x;
   void* out;
@@ -196,7 +202,7 @@ typedef struct {
 } b200sd_upsample_params;
 int b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream stream);
 
-/* 3x3 stride-2 pad-1 patch gather: out bf16 [nimg, h/2, w/2, 9*cp] (cp = c rounded up to 64, pad zeroed), feeding
+/* 3x3 stride-2 pad-1 patch gather: out act16 [nimg, h/2, w/2, 9*cp] (cp = c rounded up to 64, pad zeroed), feeding
  * b200sd_gemm as a linear layer (Downsample2D; K2).  `out` is caller-provided scratch. */
 typedef struct {
   const void* x;
@@ -206,11 +212,11 @@ typedef struct {
 int b200sd_im2col_s2(const b200sd_im2col_s2_params* p, b200sd_stream stream);
 size_t b200sd_im2col_s2_bytes(const b200sd_im2col_s2_params* p);
 
-/* CLIP token + position embedding: out bf16 [rows, c] = tok[ids[r]] + pos[r % seq]. (CLIPTextEmbeddings; a7) */
+/* CLIP token + position embedding: out act16 [rows, c] = tok[ids[r]] + pos[r % seq]. (CLIPTextEmbeddings; a7) */
 typedef struct {
   const int32_t* ids;
-  const void* tok; /* bf16 [vocab, c] */
-  const void* pos; /* bf16 [seq, c] */
+  const void* tok; /* act16 [vocab, c] */
+  const void* pos; /* act16 [seq, c] */
   void* out;
   int32_t rows, seq, c, vocab;
 } b200sd_embed_params;
@@ -226,21 +232,31 @@ typedef struct {
 } b200sd_denorm_params;
 int b200sd_denorm_u8(const b200sd_denorm_params* p, b200sd_stream stream);
 
-/* latents f32 NHWC [b, hw, 4] * scale -> bf16 [b, hw, 8] zero padded (VAE input: latents / scaling_factor). */
+/* latents f32 NHWC [b, hw, 4] * scale -> act16 [b, hw, 8] zero padded (VAE input: latents / scaling_factor). */
 typedef struct {
   const float* latents;
   void* out;
   int32_t b, hw;
   float scale;
 } b200sd_latent_cast_params;
-int b200sd_latent_to_bf16(const b200sd_latent_cast_params* p, b200sd_stream stream);
+int b200sd_latent_to_act(const b200sd_latent_cast_params* p, b200sd_stream stream);
 
-/* Row softmax in place over bf16 [rows, cols] scaled logits (VAE mid-block attention d=512 unfused path). */
+/* Row softmax: f32 logits [rows, cols] -> act16 probabilities [rows, cols] (VAE mid-block attention, head dim 512,
+ * unfused path: the logits stay fp32 until after the exponent). */
 typedef struct {
-  void* x;
+  const float* x;
+  void* out;
   int32_t rows, cols;
 } b200sd_softmax_params;
 int b200sd_softmax_rows(const b200sd_softmax_params* p, b200sd_stream stream);
+
+/* cudaMemsetAsync(ptr, 0, bytes) on `stream` — zeroes caller-owned scratch (GroupNorm statistics) inside a
+ * captured step without leaving the C ABI. */
+typedef struct {
+  void* ptr;
+  int64_t bytes;
+} b200sd_memset_params;
+int b200sd_memset_zero(const b200sd_memset_params* p, b200sd_stream stream);
 
 /* sizeof() of every params struct, in declaration order above (host bindings check their mirrors against it). */
 int b200sd_struct_sizes(int32_t* out, int32_t max_entries);

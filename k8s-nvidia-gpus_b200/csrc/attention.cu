@@ -7,12 +7,12 @@
 //                       multiple of 64 (40, 80, 160) and ragged token counts are zero-filled by the TMA unit —
 //                       no padded copies of Q/K/V exist in HBM.
 //   warp 1 (1 thread) : tcgen05.mma issuer.  S = Q K^T (K-major A and B) into TMEM columns [0,128);
-//                       O += P V with P (bf16, written by the softmax warps) as the K-major A operand in shared
+//                       O += P V with P (act_t, written by the softmax warps) as the K-major A operand in shared
 //                       memory and V consumed in place as an MN-major B operand; O lives in TMEM columns [128, ...).
 //   warp 2            : TMEM allocator.
 //   warps 4..7        : online softmax (thread = query row): tcgen05.ld S, running max / sum in fp32 registers,
 //                       exp2 with the scale folded in, P -> swizzled shared memory, lazy rescale of O in TMEM,
-//                       final normalisation and bf16 store.
+//                       final normalisation and act_t store.
 // S_{j+1} is issued before P_j V_j so the tensor pipe computes the next scores while the softmax warps work.
 #include "common.cuh"
 #include "host.cuh"
@@ -22,11 +22,11 @@ namespace b200sd {
 static constexpr int kAttThreads = 256;
 static constexpr int kBQ = 128;   // query rows per CTA (UMMA M)
 static constexpr int kBKV = 128;  // keys per tile
-static constexpr uint32_t kAtomBytes = 128 * 128;  // 128 rows x 64 bf16, one swizzle-128B atom column
+static constexpr uint32_t kAtomBytes = 128 * 128;  // 128 rows x 64 act_t, one swizzle-128B atom column
 
 struct alignas(64) AttnDev {
   CUtensorMap tmQ, tmK, tmV;
-  bf16* out;
+  act_t* out;
   int batch, heads, nq, nk, d;
   int ldo;
   int nd;      // 64-wide d atoms
@@ -110,8 +110,8 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
   } else if (warp == 1) {
     if (lane == 0) {
       // ---------------------------------------------------------------- MMA issuer
-      const uint32_t idesc_s = make_idesc_bf16(kBQ, kBKV, 0, 0);  // S[128 x 128] = Q (K-major) x K (K-major)
-      const uint32_t idesc_o = make_idesc_bf16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
+      const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 128] = Q (K-major) x K (K-major)
+      const uint32_t idesc_o = make_idesc_f16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
       const int ksteps_s = p.dN / 16;
       auto issue_s = [&](int j) {
         const int st = j % p.stages;
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
           const uint32_t off = (s >> 2) * kAtomBytes + (s & 3) * 32;
           const uint64_t adesc = make_smem_desc_sw128(sQ + off, 16, 1024);
           const uint64_t bdesc = make_smem_desc_sw128(sK + st * tile_bytes + off, 16, 1024);
-          umma_bf16_ss(tS, adesc, bdesc, idesc_s, s != 0);
+          umma_f16_ss(tS, adesc, bdesc, idesc_s, s != 0);
         }
         umma_commit(smem_u32(&k_empty[st]));
         umma_commit(smem_u32(&s_full));
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
           const uint64_t adesc = make_smem_desc_sw128(sP + (s >> 2) * kAtomBytes + (s & 3) * 32, 16, 1024);
           // V tile: [kv rows at 128 B pitch][64 d per atom]; 16 kv rows per step = 2048 B; atoms kAtomBytes apart
           const uint64_t bdesc = make_smem_desc_sw128(sV + st * tile_bytes + s * 2048, kAtomBytes, 1024);
-          umma_bf16_ss(tO, adesc, bdesc, idesc_o, (j | s) != 0);
+          umma_f16_ss(tO, adesc, bdesc, idesc_o, (j | s) != 0);
         }
         umma_commit(smem_u32(&v_empty[st]));
         umma_commit(smem_u32(&pv_done));
@@ -195,8 +195,8 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
           psum += pv[e];
         }
         const uint32_t addr = sP + (c16 >> 3) * kAtomBytes + r * 128 + (((c16 & 7) ^ (r & 7)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_bf16x2(pv[0], pv[1])),
-                     "r"(pack_bf16x2(pv[2], pv[3])), "r"(pack_bf16x2(pv[4], pv[5])), "r"(pack_bf16x2(pv[6], pv[7]))
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_act2(pv[0], pv[1])),
+                     "r"(pack_act2(pv[2], pv[3])), "r"(pack_act2(pv[4], pv[5])), "r"(pack_act2(pv[6], pv[7]))
                      : "memory");
       }
       l_run = l_run * alpha + psum;
@@ -216,11 +216,11 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
       tc_fence_before();
       mbar_arrive(smem_u32(&p_full));
     }
-    // final: O / l -> bf16 -> global
+    // final: O / l -> act_t -> global
     mbar_wait(smem_u32(&pv_done), (T - 1) & 1);
     tc_fence_after();
     const float inv_l = 1.f / l_run;
-    bf16* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
+    act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
     for (int c = 0; c < p.dN; c += 16) {
       uint32_t o[16];
       tmem_ld16(tO + lane_off + c, o);
@@ -230,10 +230,10 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
         for (int h8 = 0; h8 < 2; ++h8) {
           if (c + h8 * 8 < p.d) {  // d is a multiple of 8
             uint4 u;
-            u.x = pack_bf16x2(__uint_as_float(o[h8 * 8 + 0]) * inv_l, __uint_as_float(o[h8 * 8 + 1]) * inv_l);
-            u.y = pack_bf16x2(__uint_as_float(o[h8 * 8 + 2]) * inv_l, __uint_as_float(o[h8 * 8 + 3]) * inv_l);
-            u.z = pack_bf16x2(__uint_as_float(o[h8 * 8 + 4]) * inv_l, __uint_as_float(o[h8 * 8 + 5]) * inv_l);
-            u.w = pack_bf16x2(__uint_as_float(o[h8 * 8 + 6]) * inv_l, __uint_as_float(o[h8 * 8 + 7]) * inv_l);
+            u.x = pack_act2(__uint_as_float(o[h8 * 8 + 0]) * inv_l, __uint_as_float(o[h8 * 8 + 1]) * inv_l);
+            u.y = pack_act2(__uint_as_float(o[h8 * 8 + 2]) * inv_l, __uint_as_float(o[h8 * 8 + 3]) * inv_l);
+            u.z = pack_act2(__uint_as_float(o[h8 * 8 + 4]) * inv_l, __uint_as_float(o[h8 * 8 + 5]) * inv_l);
+            u.w = pack_act2(__uint_as_float(o[h8 * 8 + 6]) * inv_l, __uint_as_float(o[h8 * 8 + 7]) * inv_l);
             *reinterpret_cast<uint4*>(orow + c + h8 * 8) = u;
           }
         }
@@ -275,7 +275,7 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
 
   AttnDev d;
   memset(&d, 0, sizeof(d));
-  d.out = static_cast<bf16*>(h.out);
+  d.out = static_cast<act_t*>(h.out);
   d.batch = h.batch;
   d.heads = h.heads;
   d.nq = h.nq;
@@ -295,7 +295,7 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
     const uint64_t st[3] = {static_cast<uint64_t>(h.d) * 2, static_cast<uint64_t>(ld) * 2,
                             static_cast<uint64_t>(ld) * 2 * rows};
     const uint32_t box[4] = {64, 1, 128, 1};
-    return encode_tmap_bf16(tm, ptr, 4, dims, st, box);
+    return encode_tmap_act(tm, ptr, 4, dims, st, box);
   };
   if (int e = enc(&d.tmQ, h.q, h.nq, h.ldq)) return e;
   if (int e = enc(&d.tmK, h.k, h.nk, h.ldk)) return e;

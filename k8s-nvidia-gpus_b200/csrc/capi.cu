@@ -46,8 +46,15 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
+#ifdef B200SD_ACT_BF16
+static const CUtensorMapDataType kTmaDtype = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+static const int kActCode = 0;
+#else
+static const CUtensorMapDataType kTmaDtype = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+static const int kActCode = 1;
+#endif
 
-int encode_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const uint32_t* box) {
   if (g_encode == nullptr) {
     std::lock_guard<std::mutex> lk(g_mu);
@@ -73,7 +80,7 @@ int encode_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const uint64_t
   for (int i = 0; i + 1 < rank; ++i)
     B200SD_REQUIRE((gstr[i] % 16) == 0, B200SD_ERR_BAD_ALIGNMENT, "TMA stride %d (%llu B) not a multiple of 16", i,
                    (unsigned long long)gstr[i]);
-  CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank), const_cast<void*>(base),
+  CUresult r = g_encode(tm, kTmaDtype, static_cast<cuuint32_t>(rank), const_cast<void*>(base),
                         gdims, gstr, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200SD_REQUIRE(r == CUDA_SUCCESS, B200SD_ERR_CUDA,
@@ -89,6 +96,8 @@ int encode_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const uint64_t
 using namespace b200sd;
 
 extern "C" int b200sd_version(void) { return 100; }
+
+extern "C" int b200sd_act_dtype(void) { return kActCode; }
 
 extern "C" const char* b200sd_last_error(void) { return last_error_buf(); }
 
@@ -111,7 +120,7 @@ extern "C" int b200sd_struct_sizes(int32_t* out, int32_t max_entries) {
       (int32_t)sizeof(b200sd_sched_params),      (int32_t)sizeof(b200sd_upsample_params),
       (int32_t)sizeof(b200sd_im2col_s2_params),  (int32_t)sizeof(b200sd_embed_params),
       (int32_t)sizeof(b200sd_denorm_params),     (int32_t)sizeof(b200sd_latent_cast_params),
-      (int32_t)sizeof(b200sd_softmax_params),
+      (int32_t)sizeof(b200sd_softmax_params),     (int32_t)sizeof(b200sd_memset_params),
   };
   const int n = (int)(sizeof(sizes) / sizeof(sizes[0]));
   for (int i = 0; i < n && i < max_entries; ++i) out[i] = sizes[i];

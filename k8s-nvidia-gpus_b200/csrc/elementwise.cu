@@ -19,15 +19,15 @@ __global__ void prep_unet_input_kernel(const float4* __restrict__ latents, uint4
   const float s = table[counter[0] * B200SD_ST_WIDTH + B200SD_ST_IN_SCALE];
   const float4 v = latents[i];
   uint4 u;
-  u.x = pack_bf16x2(v.x * s, v.y * s);
-  u.y = pack_bf16x2(v.z * s, v.w * s);
+  u.x = pack_act2(v.x * s, v.y * s);
+  u.y = pack_act2(v.z * s, v.w * s);
   u.z = 0u;
   u.w = 0u;
   out[i] = u;
   if (cfg) out[npix + i] = u;
 }
 
-__global__ void timestep_embedding_kernel(bf16* __restrict__ out, const float* __restrict__ table,
+__global__ void timestep_embedding_kernel(act_t* __restrict__ out, const float* __restrict__ table,
                                           const int* __restrict__ counter, int rows, int dim) {
   const int half = dim >> 1;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -37,8 +37,8 @@ __global__ void timestep_embedding_kernel(bf16* __restrict__ out, const float* _
   // diffusers get_timestep_embedding(flip_sin_to_cos=True, downscale_freq_shift=0): [cos | sin]
   const float freq = expf(-9.210340371976184f * static_cast<float>(j) / static_cast<float>(half));
   const float a = t * freq;
-  out[static_cast<size_t>(row) * dim + j] = __float2bfloat16_rn(cosf(a));
-  out[static_cast<size_t>(row) * dim + half + j] = __float2bfloat16_rn(sinf(a));
+  out[static_cast<size_t>(row) * dim + j] = to_act(cosf(a));
+  out[static_cast<size_t>(row) * dim + half + j] = to_act(sinf(a));
 }
 
 // one thread per latent pixel (4 channels)
@@ -172,8 +172,8 @@ __global__ void im2col_s2_kernel(const uint4* __restrict__ x, uint4* __restrict_
   }
 }
 
-__global__ void clip_embed_kernel(const int* __restrict__ ids, const bf16* __restrict__ tok,
-                                  const bf16* __restrict__ pos, bf16* __restrict__ out, int rows, int seq, int c,
+__global__ void clip_embed_kernel(const int* __restrict__ ids, const act_t* __restrict__ tok,
+                                  const act_t* __restrict__ pos, act_t* __restrict__ out, int rows, int seq, int c,
                                   int vocab) {
   const int octs = c >> 3;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -187,8 +187,8 @@ __global__ void clip_embed_kernel(const int* __restrict__ ids, const bf16* __res
   uint32_t o[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const float2 fa = unpack_bf16x2(av[k]), fb = unpack_bf16x2(bv[k]);
-    o[k] = pack_bf16x2(fa.x + fb.x, fa.y + fb.y);
+    const float2 fa = unpack_act2(av[k]), fb = unpack_act2(bv[k]);
+    o[k] = pack_act2(fa.x + fb.x, fa.y + fb.y);
   }
   reinterpret_cast<uint4*>(out + static_cast<size_t>(row) * c)[oct] = make_uint4(o[0], o[1], o[2], o[3]);
 }
@@ -204,14 +204,14 @@ __global__ void denorm_u8_kernel(const float* __restrict__ x, uint8_t* __restric
   }
 }
 
-__global__ void latent_to_bf16_kernel(const float4* __restrict__ latents, uint4* __restrict__ out, int npix,
+__global__ void latent_to_act_kernel(const float4* __restrict__ latents, uint4* __restrict__ out, int npix,
                                       float scale) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= npix) return;
   const float4 v = latents[i];
   uint4 u;
-  u.x = pack_bf16x2(v.x * scale, v.y * scale);
-  u.y = pack_bf16x2(v.z * scale, v.w * scale);
+  u.x = pack_act2(v.x * scale, v.y * scale);
+  u.y = pack_act2(v.z * scale, v.w * scale);
   u.z = 0u;
   u.w = 0u;
   out[i] = u;
@@ -239,7 +239,7 @@ extern "C" int b200sd_timestep_embedding(const b200sd_temb_params* p, b200sd_str
                  B200SD_ERR_BAD_ARGUMENT, "timestep_embedding: bad arguments");
   const int n = p->rows * (p->dim / 2);
   timestep_embedding_kernel<<<ceil_div(n, kEwThreads), kEwThreads, 0, EW_STREAM>>>(
-      static_cast<bf16*>(p->out), p->step_table, p->step_counter, p->rows, p->dim);
+      static_cast<act_t*>(p->out), p->step_table, p->step_counter, p->rows, p->dim);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
@@ -295,7 +295,7 @@ extern "C" int b200sd_clip_embed(const b200sd_embed_params* p, b200sd_stream str
                  B200SD_ERR_BAD_ARGUMENT, "clip_embed: bad arguments");
   const int n = p->rows * (p->c / 8);
   clip_embed_kernel<<<ceil_div(n, kEwThreads), kEwThreads, 0, EW_STREAM>>>(
-      p->ids, static_cast<const bf16*>(p->tok), static_cast<const bf16*>(p->pos), static_cast<bf16*>(p->out), p->rows,
+      p->ids, static_cast<const act_t*>(p->tok), static_cast<const act_t*>(p->pos), static_cast<act_t*>(p->out), p->rows,
       p->seq, p->c, p->vocab);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
@@ -310,12 +310,18 @@ extern "C" int b200sd_denorm_u8(const b200sd_denorm_params* p, b200sd_stream str
   return B200SD_OK;
 }
 
-extern "C" int b200sd_latent_to_bf16(const b200sd_latent_cast_params* p, b200sd_stream stream_) {
+extern "C" int b200sd_latent_to_act(const b200sd_latent_cast_params* p, b200sd_stream stream_) {
   B200SD_REQUIRE(p && p->latents && p->out && p->b > 0 && p->hw > 0, B200SD_ERR_BAD_ARGUMENT,
-                 "latent_to_bf16: bad arguments");
+                 "latent_to_act: bad arguments");
   const int npix = p->b * p->hw;
-  latent_to_bf16_kernel<<<ceil_div(npix, kEwThreads), kEwThreads, 0, EW_STREAM>>>(
+  latent_to_act_kernel<<<ceil_div(npix, kEwThreads), kEwThreads, 0, EW_STREAM>>>(
       reinterpret_cast<const float4*>(p->latents), reinterpret_cast<uint4*>(p->out), npix, p->scale);
   B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}
+
+extern "C" int b200sd_memset_zero(const b200sd_memset_params* p, b200sd_stream stream_) {
+  B200SD_REQUIRE(p && p->ptr && p->bytes >= 0, B200SD_ERR_BAD_ARGUMENT, "memset_zero: bad arguments");
+  B200SD_CUDA_CHECK(cudaMemsetAsync(p->ptr, 0, static_cast<size_t>(p->bytes), EW_STREAM));
   return B200SD_OK;
 }

@@ -8,13 +8,13 @@
 //                       (w0 + kw - pad, h0 + kh - pad); out-of-bounds elements are zero-filled by the TMA unit,
 //                       which implements the convolution's zero padding, ragged M tiles and ragged channel counts.
 //                       Up to two NHWC sources are walked back to back along K (virtual channel concat).
-//   warp 1 (1 thread) : tcgen05.mma issuer (128 x BN x 16 UMMAs, bf16 -> fp32 accumulators in TMEM).
+//   warp 1 (1 thread) : tcgen05.mma issuer (128 x BN x 16 UMMAs, act_t -> fp32 accumulators in TMEM).
 //   warp 2            : TMEM allocator (512 columns = 2 accumulator stages of up to 256 columns).
 //   warps 4..7        : epilogue.  tcgen05.ld -> registers -> alpha/bias/time-embedding/activation/GEGLU/residual
-//                       -> bf16 or fp32 global stores.  Double-buffered accumulators let the epilogue of tile i
+//                       -> act_t or fp32 global stores.  Double-buffered accumulators let the epilogue of tile i
 //                       overlap the mainloop of tile i+1.
 //
-// Shared memory: num_stages x (A 128x64 bf16 = 16 KB | B BNx64 bf16) in the canonical K-major SWIZZLE_128B layout,
+// Shared memory: num_stages x (A 128x64 act_t = 16 KB | B BNx64 act_t) in the canonical K-major SWIZZLE_128B layout,
 // filled by TMA and consumed directly by UMMA shared-memory descriptors.
 #include "common.cuh"
 #include "host.cuh"
@@ -34,7 +34,7 @@ struct alignas(64) GemmDev {
   void* out;
   const float* bias;
   const float* rowbias;
-  const bf16* residual;
+  const act_t* residual;
   int M_total, N, BN;
   int nimg, H, W;
   int bw, bh, bn;
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------------------------------------ MMA issuer
-      const uint32_t idesc = make_idesc_bf16(kBlockM, p.BN, 0, 0);
+      const uint32_t idesc = make_idesc_f16(kBlockM, p.BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -147,8 +147,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           const uint64_t bdesc = make_smem_desc_sw128(sa + kABytes, 16, 1024);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
-            // advancing K by 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-            umma_bf16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            // advancing K by 16 act_t = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+            umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
           umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == p.num_stages) {
@@ -239,13 +239,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         if (row_ok) {
           const bool full = (ocol + 32 <= n_out);
           if (p.residual != nullptr) {
-            const bf16* rp = p.residual + row * p.ldr + ocol;
+            const act_t* rp = p.residual + row * p.ldr + ocol;
             if (full && (p.ldr & 7) == 0) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp) + j);
-                const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z),
-                             d = unpack_bf16x2(u.w);
+                const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), cc = unpack_act2(u.z),
+                             d = unpack_act2(u.w);
                 f[8 * j + 0] += a.x;
                 f[8 * j + 1] += a.y;
                 f[8 * j + 2] += b.x;
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (ocol + j < n_out) f[j] += __bfloat162float(rp[j]);
+                if (ocol + j < n_out) f[j] += from_act(rp[j]);
             }
           }
           if (p.out_f32) {
@@ -273,21 +273,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
                 if (ocol + j < n_out) op[j] = f[j];
             }
           } else {
-            bf16* op = reinterpret_cast<bf16*>(p.out) + row * p.ldc + ocol;
+            act_t* op = reinterpret_cast<act_t*>(p.out) + row * p.ldc + ocol;
             if (full && (p.ldc & 7) == 0) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 uint4 u;
-                u.x = pack_bf16x2(f[8 * j + 0], f[8 * j + 1]);
-                u.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-                u.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
-                u.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+                u.x = pack_act2(f[8 * j + 0], f[8 * j + 1]);
+                u.y = pack_act2(f[8 * j + 2], f[8 * j + 3]);
+                u.z = pack_act2(f[8 * j + 4], f[8 * j + 5]);
+                u.w = pack_act2(f[8 * j + 6], f[8 * j + 7]);
                 reinterpret_cast<uint4*>(op)[j] = u;
               }
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (ocol + j < n_out) op[j] = __float2bfloat16_rn(f[j]);
+                if (ocol + j < n_out) op[j] = to_act(f[j]);
             }
           }
         }
@@ -399,7 +399,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.out = h.out;
   d.bias = h.bias;
   d.rowbias = h.rowbias;
-  d.residual = static_cast<const bf16*>(h.residual);
+  d.residual = static_cast<const act_t*>(h.residual);
   d.ldc = h.ldc;
   d.ldr = h.ldr;
   d.ld_rowbias = h.ld_rowbias;
@@ -414,7 +414,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
                             static_cast<uint64_t>(h.ld0) * 2 * h.w_ * h.h};
     const uint32_t box[4] = {kBlockK, static_cast<uint32_t>(d.bw), static_cast<uint32_t>(d.bh),
                              static_cast<uint32_t>(d.bn)};
-    if (int e = encode_tmap_bf16(&d.tmA0, h.a0, 4, dims, st, box)) return e;
+    if (int e = encode_tmap_act(&d.tmA0, h.a0, 4, dims, st, box)) return e;
   }
   if (h.c1 > 0) {
     const uint64_t dims[4] = {static_cast<uint64_t>(h.c1), static_cast<uint64_t>(h.w_), static_cast<uint64_t>(h.h),
@@ -423,14 +423,14 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
                             static_cast<uint64_t>(h.ld1) * 2 * h.w_ * h.h};
     const uint32_t box[4] = {kBlockK, static_cast<uint32_t>(d.bw), static_cast<uint32_t>(d.bh),
                              static_cast<uint32_t>(d.bn)};
-    if (int e = encode_tmap_bf16(&d.tmA1, h.a1, 4, dims, st, box)) return e;
+    if (int e = encode_tmap_act(&d.tmA1, h.a1, 4, dims, st, box)) return e;
   }
   {
     const uint64_t ktot = static_cast<uint64_t>(d.taps) * (d.cblk0 + d.cblk1) * kBlockK;
     const uint64_t dims[2] = {ktot, static_cast<uint64_t>(h.n)};
     const uint64_t st[1] = {ktot * 2};
     const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(d.BN)};
-    if (int e = encode_tmap_bf16(&d.tmB, h.w, 2, dims, st, box)) return e;
+    if (int e = encode_tmap_act(&d.tmB, h.w, 2, dims, st, box)) return e;
   }
 
   const int smem_bytes = d.num_stages * stage_bytes + 1024;

@@ -36,8 +36,8 @@ struct DeviceInfo {
 int get_device_info(DeviceInfo* out);
 
 // cuTensorMapEncodeTiled via the runtime's driver entry point (no -lcuda link dependency).
-// dims/strides innermost first; strides[i] = byte stride of dim i+1 (rank-1 entries); bf16 elements; 128B swizzle.
-int encode_tmap_bf16(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+// dims/strides innermost first; strides[i] = byte stride of dim i+1 (rank-1 entries); act_t elements; 128B swizzle.
+int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const uint32_t* box);
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }

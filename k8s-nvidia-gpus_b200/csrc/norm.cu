@@ -1,5 +1,5 @@
 // Bandwidth-bound normalisation kernels: GroupNorm(+SiLU) over a virtual two-source concat, LayerNorm, row softmax.
-// All statistics are fp32; inputs/outputs bf16, 16-byte vectorised, coalesced along the NHWC channel axis.
+// All statistics are fp32; inputs/outputs act_t, 16-byte vectorised, coalesced along the NHWC channel axis.
 // SURVEY §2.1 K7, K8, K9, K14.
 #include "common.cuh"
 #include "host.cuh"
@@ -8,25 +8,25 @@ namespace b200sd {
 
 static constexpr int kNormThreads = 256;
 
-__device__ __forceinline__ void load8(const bf16* p, float (&f)[8]) {
+__device__ __forceinline__ void load8(const act_t* p, float (&f)[8]) {
   const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
-  const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), c = unpack_act2(u.z), d = unpack_act2(u.w);
   f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
 }
-__device__ __forceinline__ void store8(bf16* p, const float (&f)[8]) {
+__device__ __forceinline__ void store8(act_t* p, const float (&f)[8]) {
   uint4 u;
-  u.x = pack_bf16x2(f[0], f[1]);
-  u.y = pack_bf16x2(f[2], f[3]);
-  u.z = pack_bf16x2(f[4], f[5]);
-  u.w = pack_bf16x2(f[6], f[7]);
+  u.x = pack_act2(f[0], f[1]);
+  u.y = pack_act2(f[2], f[3]);
+  u.z = pack_act2(f[4], f[5]);
+  u.w = pack_act2(f[6], f[7]);
   *reinterpret_cast<uint4*>(p) = u;
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: stats
 // grid (chunks, nimg).  Each thread owns one 8-channel vector column ("octet") and walks pixels, keeping 8 sums and
 // 8 sums of squares in registers; one shared-memory atomic pass per CTA, then one global atomic per (group, CTA).
-__global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const bf16* __restrict__ x0,
-                                                                const bf16* __restrict__ x1, float* __restrict__ stats,
+__global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __restrict__ x0,
+                                                                const act_t* __restrict__ x1, float* __restrict__ stats,
                                                                 int hw, int c0, int c1, int groups, int pix_per_cta) {
   extern __shared__ float gacc[];  // [groups][2]
   const int n = blockIdx.y;
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const bf16* __re
   if (stream < S) {
     for (int oct = threadIdx.x % Wd; oct < octs; oct += Wd) {
       const int ch0 = oct * 8;
-      const bf16* src;
+      const act_t* src;
       int ld;
       if (ch0 < c0) {
         src = x0 + static_cast<size_t>(n) * hw * c0 + ch0;
@@ -102,11 +102,11 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const bf16* __re
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: apply
-__global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const bf16* __restrict__ x0,
-                                                                const bf16* __restrict__ x1,
+__global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const act_t* __restrict__ x0,
+                                                                const act_t* __restrict__ x1,
                                                                 const float* __restrict__ stats,
                                                                 const float* __restrict__ gamma,
-                                                                const float* __restrict__ beta, bf16* __restrict__ out,
+                                                                const float* __restrict__ beta, act_t* __restrict__ out,
                                                                 int hw, int c0, int c1, int groups, int pix_per_cta,
                                                                 int silu, float eps) {
   extern __shared__ float ss[];  // scale[C], shift[C]
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const bf16* __re
     const int p = p_begin + idx / octs;
     const int oct = idx - (idx / octs) * octs;
     const int ch0 = oct * 8;
-    const bf16* src = (ch0 < c0) ? x0 + (static_cast<size_t>(n) * hw + p) * c0 + ch0
+    const act_t* src = (ch0 < c0) ? x0 + (static_cast<size_t>(n) * hw + p) * c0 + ch0
                                  : x1 + (static_cast<size_t>(n) * hw + p) * c1 + (ch0 - c0);
     float f[8];
     load8(src, f);
@@ -152,15 +152,15 @@ __global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const bf16* __re
 // ---------------------------------------------------------------------------------------------- LayerNorm
 // one warp per row; the row lives in registers (two-pass mean / variance like the fp32 reference).
 template <int kVecs>
-__global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const bf16* __restrict__ x,
+__global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const act_t* __restrict__ x,
                                                                  const float* __restrict__ gamma,
-                                                                 const float* __restrict__ beta, bf16* __restrict__ out,
+                                                                 const float* __restrict__ beta, act_t* __restrict__ out,
                                                                  int rows, int c, float eps) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * (kNormThreads / 32) + warp;
   if (row >= rows) return;
   const int octs = c >> 3;
-  const bf16* xr = x + static_cast<size_t>(row) * c;
+  const act_t* xr = x + static_cast<size_t>(row) * c;
   float f[kVecs][8];
   float sum = 0.f;
 #pragma unroll
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const bf16* __r
     }
   }
   const float rstd = rsqrtf(warp_sum(sq) / static_cast<float>(c) + eps);
-  bf16* orow = out + static_cast<size_t>(row) * c;
+  act_t* orow = out + static_cast<size_t>(row) * c;
 #pragma unroll
   for (int v = 0; v < kVecs; ++v) {
     const int oct = lane + 32 * v;
@@ -204,10 +204,18 @@ __global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const bf16* __r
 
 // ---------------------------------------------------------------------------------------------- row softmax (in place)
 // one CTA per row, row held in registers (cols <= 256 * 8 * kVecs).
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+  const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
 template <int kVecs>
-__global__ void __launch_bounds__(kNormThreads) softmax_rows_kernel(bf16* __restrict__ x, int cols) {
+__global__ void __launch_bounds__(kNormThreads) softmax_rows_kernel(const float* __restrict__ x,
+                                                                    act_t* __restrict__ out, int cols) {
   __shared__ float red[kNormThreads / 32];
-  bf16* xr = x + static_cast<size_t>(blockIdx.x) * cols;
+  const float* xr = x + static_cast<size_t>(blockIdx.x) * cols;
+  act_t* orow = out + static_cast<size_t>(blockIdx.x) * cols;
   const int octs = cols >> 3;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float f[kVecs][8];
@@ -216,7 +224,7 @@ __global__ void __launch_bounds__(kNormThreads) softmax_rows_kernel(bf16* __rest
   for (int v = 0; v < kVecs; ++v) {
     const int oct = threadIdx.x + kNormThreads * v;
     if (oct < octs) {
-      load8(xr + oct * 8, f[v]);
+      load8f(xr + oct * 8, f[v]);
 #pragma unroll
       for (int e = 0; e < 8; ++e) mx = fmaxf(mx, f[v][e]);
     }
@@ -253,7 +261,7 @@ __global__ void __launch_bounds__(kNormThreads) softmax_rows_kernel(bf16* __rest
     if (oct < octs) {
 #pragma unroll
       for (int e = 0; e < 8; ++e) f[v][e] *= inv;
-      store8(xr + oct * 8, f[v]);
+      store8(orow + oct * 8, f[v]);
     }
   }
 }
@@ -290,7 +298,7 @@ extern "C" int b200sd_groupnorm_stats(const b200sd_groupnorm_params* hp, b200sd_
   const b200sd_groupnorm_params& h = *hp;
   dim3 grid(chunks, h.nimg);
   gn_stats_kernel<<<grid, kNormThreads, h.groups * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const bf16*>(h.x0), static_cast<const bf16*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
@@ -305,8 +313,8 @@ extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_
   B200SD_REQUIRE(C * 2 * sizeof(float) <= 48 * 1024, B200SD_ERR_TOO_LARGE, "groupnorm_apply: C too large");
   dim3 grid(chunks, h.nimg);
   gn_apply_kernel<<<grid, kNormThreads, C * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const bf16*>(h.x0), static_cast<const bf16*>(h.x1), h.stats, h.gamma, h.beta,
-      static_cast<bf16*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
+      static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
@@ -320,8 +328,8 @@ extern "C" int b200sd_layernorm(const b200sd_layernorm_params* hp, b200sd_stream
   B200SD_REQUIRE(aligned16(h.x) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT, "layernorm: 16-byte alignment");
   cudaStream_t s = static_cast<cudaStream_t>(stream_);
   const int grid = ceil_div(h.rows, kNormThreads / 32);
-  const bf16* x = static_cast<const bf16*>(h.x);
-  bf16* o = static_cast<bf16*>(h.out);
+  const act_t* x = static_cast<const act_t*>(h.x);
+  act_t* o = static_cast<act_t*>(h.out);
   if (h.c <= 512)
     layernorm_kernel<2><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
   else if (h.c <= 1280)
@@ -335,15 +343,15 @@ extern "C" int b200sd_layernorm(const b200sd_layernorm_params* hp, b200sd_stream
 extern "C" int b200sd_softmax_rows(const b200sd_softmax_params* hp, b200sd_stream stream_) {
   B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "softmax_rows: params is NULL");
   const b200sd_softmax_params& h = *hp;
-  B200SD_REQUIRE(h.x && h.rows > 0 && h.cols > 0, B200SD_ERR_BAD_ARGUMENT, "softmax_rows: bad arguments");
+  B200SD_REQUIRE(h.x && h.out && h.rows > 0 && h.cols > 0, B200SD_ERR_BAD_ARGUMENT, "softmax_rows: bad arguments");
   B200SD_REQUIRE((h.cols % 8) == 0 && h.cols <= kNormThreads * 8 * 8, B200SD_ERR_BAD_SHAPE,
                  "softmax_rows: cols must be a multiple of 8, <= %d", kNormThreads * 8 * 8);
   cudaStream_t s = static_cast<cudaStream_t>(stream_);
-  bf16* x = static_cast<bf16*>(h.x);
+  act_t* o = static_cast<act_t*>(h.out);
   if (h.cols <= kNormThreads * 8 * 2)
-    softmax_rows_kernel<2><<<h.rows, kNormThreads, 0, s>>>(x, h.cols);
+    softmax_rows_kernel<2><<<h.rows, kNormThreads, 0, s>>>(h.x, o, h.cols);
   else
-    softmax_rows_kernel<8><<<h.rows, kNormThreads, 0, s>>>(x, h.cols);
+    softmax_rows_kernel<8><<<h.rows, kNormThreads, 0, s>>>(h.x, o, h.cols);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }

@@ -1,0 +1,265 @@
+"""Host-side plan builder: turns a model description + weights into a flat list of prepared C-ABI calls.
+
+A `Plan` is built once per (architecture, batch, resolution); running it enqueues every kernel on the current CUDA
+stream with no allocation and no host synchronisation, so a plan can be captured into a CUDA graph and replayed.
+Activations are NHWC bf16 (`Act`), which makes a feature map [N, H, W, C] and its token view [N, H*W, C] the same
+memory.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import lib as L
+from . import ops
+
+
+class Act:
+    """NHWC bf16 activation: tensor [nimg, h, w, c] (contiguous)."""
+    __slots__ = ("t", "nimg", "h", "w", "c")
+
+    def __init__(self, t, nimg, h, w, c):
+        self.t, self.nimg, self.h, self.w, self.c = t, nimg, h, w, c
+
+    @property
+    def hw(self):
+        return self.h * self.w
+
+    @property
+    def rows(self):
+        return self.nimg * self.h * self.w
+
+
+class Plan:
+    def __init__(self):
+        self.calls = []
+        self.keep = []
+        self.graph = None
+
+    def run(self, stream: int | None = None):
+        s = ops.current_stream() if stream is None else stream
+        for c in self.calls:
+            c(s)
+
+    def capture(self):
+        """Capture the plan into a CUDA graph (after one eager warm-up run on the side stream)."""
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            self.run()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.run()
+        self.graph = g
+        return g
+
+    def launch(self):
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.run()
+
+    def __len__(self):
+        return len(self.calls)
+
+    def kernel_launches(self) -> int:
+        return len(self.calls)
+
+
+class DeviceWeights:
+    """Packs a (diffusers-layout) CPU state dict into the kernels' layouts on first use and caches the result."""
+
+    def __init__(self, sd: dict, device, prefix: str = ""):
+        self.sd, self.device, self.prefix = sd, device, prefix
+        self.cache = {}
+
+    def raw(self, name):
+        return self.sd[self.prefix + name].float()
+
+    def has(self, name):
+        return (self.prefix + name) in self.sd
+
+    def _get(self, key, fn):
+        if key not in self.cache:
+            self.cache[key] = fn().to(self.device)
+        return self.cache[key]
+
+    def conv(self, name, split=None):
+        def f():
+            w = self.raw(name + ".weight")
+            if w.dim() == 2:
+                w = w[:, :, None, None]
+            return ops.pack_conv_weight(w, split)
+        return self._get(("conv", name, split), f)
+
+    def cat_linear(self, names, key=None, perm=None):
+        """Row-concatenated linear weights (fused QKV / KV / all time-embedding projections)."""
+        def f():
+            w = torch.cat([self.raw(n + ".weight") for n in names], dim=0)
+            if perm is not None:
+                w = w[perm]
+            return ops.pack_linear_weight(w)
+        return self._get(("catlin", tuple(names), key), f)
+
+    def cat_bias(self, names, key=None, perm=None):
+        def f():
+            b = torch.cat([self.raw(n + ".bias") for n in names], dim=0)
+            if perm is not None:
+                b = b[perm]
+            return b.contiguous()
+        return self._get(("catbias", tuple(names), key), f)
+
+    def vec(self, name):
+        return self._get(("vec", name), lambda: self.raw(name).contiguous())
+
+    def act16(self, name):
+        return self._get(("act16", name), lambda: self.raw(name).to(ops.act_dtype()).contiguous())
+
+
+class Builder:
+    def __init__(self, device, stats_floats: int = 1 << 20):
+        self.device = device
+        self.plan = Plan()
+        self.pool = {}
+        self.stats = torch.zeros(stats_floats, dtype=torch.float32, device=device)
+        self.stats_off = 0
+        self.plan.keep.append(self.stats)
+
+    # ------------------------------------------------------------------ memory
+    def alloc(self, shape, dtype=None):
+        dtype = dtype or ops.act_dtype()
+        n = 1
+        for s in shape:
+            n *= s
+        key = (n * torch.empty((), dtype=dtype).element_size(), dtype)
+        lst = self.pool.get(key)
+        if lst:
+            return lst.pop().view(shape)
+        t = torch.empty(shape, dtype=dtype, device=self.device)
+        self.plan.keep.append(t)
+        return t
+
+    def persistent(self, shape, dtype=None, zero=True):
+        dtype = dtype or ops.act_dtype()
+        t = (torch.zeros if zero else torch.empty)(shape, dtype=dtype, device=self.device)
+        self.plan.keep.append(t)
+        return t
+
+    def free(self, *acts):
+        for a in acts:
+            t = a.t if isinstance(a, Act) else a
+            if t is None:
+                continue
+            key = (t.numel() * t.element_size(), t.dtype)
+            self.pool.setdefault(key, []).append(t.reshape(-1))
+
+    def add(self, call):
+        self.plan.calls.append(call)
+
+    def finish(self) -> Plan:
+        if self.stats_off:
+            self.plan.calls.insert(0, ops.memset_zero(self.stats, self.stats_off * 4))
+        return self.plan
+
+    # ------------------------------------------------------------------ layers
+    def conv(self, W: DeviceWeights, name, x, cout, ksize, *, bias=True, rowbias=None, ld_rowbias=0, residual=None,
+             act=L.ACT_NONE, out_dtype=None, out=None, ldc=None, wsplit=None):
+        """x: Act or (Act, Act) virtual concat.  Returns Act [nimg, h, w, cout]."""
+        xs = x if isinstance(x, tuple) else (x,)
+        a0 = xs[0]
+        split = wsplit or tuple(a.c for a in xs)  # wsplit: real weight channels when the activation is zero padded
+        w = W.conv(name, split)
+        b = W.vec(name + ".bias") if bias else None
+        if out is None:
+            out = self.alloc((a0.nimg, a0.h, a0.w, cout), out_dtype)
+        a1 = xs[1] if len(xs) > 1 else None
+        self.add(ops.gemm(a0.t, w, out, nimg=a0.nimg, h=a0.h, w_=a0.w, c0=a0.c, n=cout, ksize=ksize,
+                          a1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c, bias=b, rowbias=rowbias,
+                          ld_rowbias=ld_rowbias, residual=None if residual is None else residual.t,
+                          ldr=0 if residual is None else residual.c, ldc=ldc, act=act))
+        return Act(out, a0.nimg, a0.h, a0.w, cout if ldc is None else ldc)
+
+    def linear_w(self, x: Act, w, b, n, *, residual=None, act=L.ACT_NONE, out_dtype=None, rowbias=None,
+                 ld_rowbias=0, per_image_rows=False):
+        """Linear layer over the rows of x with an already packed weight."""
+        n_out = n // 2 if act == L.ACT_GEGLU else n
+        out = self.alloc((x.nimg, x.h, x.w, n_out), out_dtype)
+        if per_image_rows:
+            geo = dict(nimg=x.rows, h=1, w_=1)
+        else:
+            geo = dict(nimg=1, h=1, w_=x.rows)
+        self.add(ops.gemm(x.t, w, out, c0=x.c, n=n, ksize=1, bias=b, residual=None if residual is None else residual.t,
+                          ldr=0 if residual is None else residual.c, act=act, rowbias=rowbias, ld_rowbias=ld_rowbias,
+                          **geo))
+        return Act(out, x.nimg, x.h, x.w, n_out)
+
+    def linear(self, W: DeviceWeights, name, x: Act, n, *, bias=True, **kw):
+        return self.linear_w(x, W.conv(name), W.vec(name + ".bias") if bias else None, n, **kw)
+
+    def groupnorm(self, W: DeviceWeights, name, x, groups, eps, silu):
+        xs = x if isinstance(x, tuple) else (x,)
+        a0 = xs[0]
+        a1 = xs[1] if len(xs) > 1 else None
+        C = sum(a.c for a in xs)
+        out = self.alloc((a0.nimg, a0.h, a0.w, C))
+        nst = a0.nimg * groups * 2
+        assert self.stats_off + nst <= self.stats.numel(), "GroupNorm statistics scratch exhausted"
+        st = self.stats[self.stats_off:self.stats_off + nst]
+        self.stats_off += nst
+        s_call, a_call = ops.groupnorm(a0.t, out, st, W.vec(name + ".weight"), W.vec(name + ".bias"), nimg=a0.nimg,
+                                       hw=a0.hw, c0=a0.c, groups=groups, eps=eps, silu=silu,
+                                       x1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c)
+        self.add(s_call)
+        self.add(a_call)
+        return Act(out, a0.nimg, a0.h, a0.w, C)
+
+    def layernorm(self, W: DeviceWeights, name, x: Act, eps=1e-5):
+        out = self.alloc((x.nimg, x.h, x.w, x.c))
+        self.add(ops.layernorm(x.t, out, W.vec(name + ".weight"), W.vec(name + ".bias"), rows=x.rows, c=x.c, eps=eps))
+        return Act(out, x.nimg, x.h, x.w, x.c)
+
+    def attention(self, q_t, k_t, v_t, *, batch, heads, nq, nk, d, ldq, ldk, ldv, causal=False, like: Act = None):
+        C = heads * d
+        out = self.alloc((like.nimg, like.h, like.w, C))
+        self.add(ops.attention(q_t, k_t, v_t, out, batch=batch, heads=heads, nq=nq, nk=nk, d=d, ldq=ldq, ldk=ldk,
+                               ldv=ldv, ldo=C, scale=d ** -0.5, causal=causal))
+        return Act(out, like.nimg, like.h, like.w, C)
+
+    def upsample2x(self, x: Act):
+        out = self.alloc((x.nimg, 2 * x.h, 2 * x.w, x.c))
+        self.add(ops.upsample2x(x.t, out, nimg=x.nimg, h=x.h, w_=x.w, c=x.c))
+        return Act(out, x.nimg, 2 * x.h, 2 * x.w, x.c)
+
+    def conv_s2(self, W: DeviceWeights, name, x: Act, cout):
+        """3x3 stride-2 pad-1 conv = patch gather into scratch + linear GEMM."""
+        cp = ops.ceil_to(x.c, 64)
+        ho, wo = x.h // 2, x.w // 2
+        col = self.alloc((x.nimg, ho, wo, 9 * cp))
+        self.add(ops.im2col_s2(x.t, col, nimg=x.nimg, h=x.h, w_=x.w, c=x.c))
+        out = self.alloc((x.nimg, ho, wo, cout))
+        self.add(ops.gemm(col, W.conv(name), out, nimg=1, h=1, w_=x.nimg * ho * wo, c0=9 * cp, n=cout, ksize=1,
+                          bias=W.vec(name + ".bias")))
+        self.free(col)
+        return Act(out, x.nimg, ho, wo, cout)
+
+    # ------------------------------------------------------------------ composite blocks (UNet + VAE)
+    def resnet(self, W, p, x, cout, groups, eps, temb=None, ld_temb=0):
+        """ResnetBlock2D: x Act or (Act, Act).  temb: fp32 tensor view [nimg, cout] (row stride ld_temb) or None."""
+        xs = x if isinstance(x, tuple) else (x,)
+        cin = sum(a.c for a in xs)
+        h = self.groupnorm(W, p + ".norm1", x, groups, eps, silu=True)
+        h1 = self.conv(W, p + ".conv1", h, cout, 3, rowbias=temb, ld_rowbias=ld_temb)
+        self.free(h)
+        h2 = self.groupnorm(W, p + ".norm2", h1, groups, eps, silu=True)
+        self.free(h1)
+        if cin != cout:
+            sc = self.conv(W, p + ".conv_shortcut", x, cout, 1)
+        else:
+            assert len(xs) == 1
+            sc = xs[0]
+        out = self.conv(W, p + ".conv2", h2, cout, 3, residual=sc)
+        self.free(h2)
+        if cin != cout:
+            self.free(sc)
+        return out

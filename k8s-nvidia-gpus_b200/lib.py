@@ -12,7 +12,8 @@ _LIB_PATH = Path(__file__).resolve().parent / "libb200sd.so"
 _lib = None
 
 ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU = 0, 1, 2, 3
-BF16, F32 = 0, 1
+ACT16, F32 = 0, 1
+BF16 = ACT16  # historical alias
 ST_TIMESTEP, ST_IN_SCALE, ST_KIND, ST_C0, ST_C1, ST_C2, ST_C3, ST_W0, ST_PNDM_MODE, ST_PUSH, ST_WIDTH = (
     0, 1, 2, 3, 4, 5, 6, 7, 11, 12, 16)
 
@@ -78,16 +79,21 @@ class LatentCastParams(C.Structure):
 
 
 class SoftmaxParams(C.Structure):
-    _fields_ = [("x", vp), ("rows", i32), ("cols", i32)]
+    _fields_ = [("x", vp), ("out", vp), ("rows", i32), ("cols", i32)]
+
+
+class MemsetParams(C.Structure):
+    _fields_ = [("ptr", vp), ("bytes", i64)]
 
 
 # declaration order of include/b200sd.h (b200sd_struct_sizes reports sizeof() in this order)
 STRUCTS = [GemmParams, AttnParams, GroupNormParams, LayerNormParams, PrepParams, TembParams, SchedParams,
-           UpsampleParams, Im2colS2Params, EmbedParams, DenormParams, LatentCastParams, SoftmaxParams]
+           UpsampleParams, Im2colS2Params, EmbedParams, DenormParams, LatentCastParams, SoftmaxParams, MemsetParams]
 
 # entry point -> params struct (None = special signature); must list every symbol include/b200sd.h declares
 ENTRY_POINTS = {
     "b200sd_version": None,
+    "b200sd_act_dtype": None,
     "b200sd_last_error": None,
     "b200sd_device_info": None,
     "b200sd_struct_sizes": None,
@@ -104,8 +110,9 @@ ENTRY_POINTS = {
     "b200sd_im2col_s2_bytes": None,
     "b200sd_clip_embed": EmbedParams,
     "b200sd_denorm_u8": DenormParams,
-    "b200sd_latent_to_bf16": LatentCastParams,
+    "b200sd_latent_to_act": LatentCastParams,
     "b200sd_softmax_rows": SoftmaxParams,
+    "b200sd_memset_zero": MemsetParams,
 }
 
 
@@ -128,6 +135,7 @@ def load():
             "(nvcc, sm_100a). b200sd has no CPU or library fallback.")
     lib = C.CDLL(str(_LIB_PATH))
     lib.b200sd_version.restype = C.c_int
+    lib.b200sd_act_dtype.restype = C.c_int
     lib.b200sd_last_error.restype = C.c_char_p
     lib.b200sd_device_info.argtypes = [C.POINTER(i32)]
     lib.b200sd_struct_sizes.argtypes = [C.POINTER(i32), i32]
@@ -141,6 +149,12 @@ def load():
     lib.b200sd_im2col_s2_bytes.restype = C.c_size_t
     _lib = lib
     return lib
+
+
+def act_dtype():
+    """torch dtype of the library's 16-bit activation / weight element type (fp16 by default, bf16 build optional)."""
+    import torch
+    return torch.float16 if load().b200sd_act_dtype() == 1 else torch.bfloat16
 
 
 def check(code: int, what: str = "") -> None:

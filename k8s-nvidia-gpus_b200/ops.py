@@ -12,6 +12,10 @@ import torch
 from . import lib as L
 
 
+def act_dtype():
+    return L.act_dtype()
+
+
 def _ptr(t):
     return None if t is None else t.data_ptr()
 
@@ -35,7 +39,7 @@ def pack_conv_weight(w: torch.Tensor, split=None) -> torch.Tensor:
         blk[:, :, :c] = wt[:, :, off:off + c]
         parts.append(blk)
         off += c
-    return torch.cat(parts, dim=2).to(torch.bfloat16).contiguous()
+    return torch.cat(parts, dim=2).to(act_dtype()).contiguous()
 
 
 def pack_linear_weight(w: torch.Tensor, split=None) -> torch.Tensor:
@@ -67,7 +71,7 @@ def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld
     p.ld_rowbias = ld_rowbias
     p.act = act
     if out_dtype is None:
-        out_dtype = L.F32 if out.dtype == torch.float32 else L.BF16
+        out_dtype = L.F32 if out.dtype == torch.float32 else L.ACT16
     p.out_dtype = out_dtype
     p.bn_hint = bn_hint
     p.alpha = alpha
@@ -150,16 +154,22 @@ def denorm_u8(x, out, *, npix, ldx):
     return L.Call("b200sd_denorm_u8", p, keep=(x, out))
 
 
-def latent_to_bf16(latents, out, *, b, hw, scale):
+def latent_to_act(latents, out, *, b, hw, scale):
     p = L.LatentCastParams()
     p.latents, p.out, p.b, p.hw, p.scale = _ptr(latents), _ptr(out), b, hw, scale
-    return L.Call("b200sd_latent_to_bf16", p, keep=(latents, out))
+    return L.Call("b200sd_latent_to_act", p, keep=(latents, out))
 
 
-def softmax_rows(x, *, rows, cols):
+def softmax_rows(x, out, *, rows, cols):
     p = L.SoftmaxParams()
-    p.x, p.rows, p.cols = _ptr(x), rows, cols
-    return L.Call("b200sd_softmax_rows", p, keep=(x,))
+    p.x, p.out, p.rows, p.cols = _ptr(x), _ptr(out), rows, cols
+    return L.Call("b200sd_softmax_rows", p, keep=(x, out))
+
+
+def memset_zero(t, nbytes=None):
+    p = L.MemsetParams()
+    p.ptr, p.bytes = _ptr(t), (t.numel() * t.element_size() if nbytes is None else nbytes)
+    return L.Call("b200sd_memset_zero", p, keep=(t,))
 
 
 def current_stream() -> int:

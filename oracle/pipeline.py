@@ -1,0 +1,81 @@
+"""Oracle text-to-image pipeline (fp32 CPU) — restates diffusers==0.30.2
+`pipelines/stable_diffusion/pipeline_stable_diffusion.py::StableDiffusionPipeline.__call__` as invoked by the
+reference at configmap.yaml:105-112 on its CPU branch (TORCH_DTYPE float32, no autocast, CPU generator:
+configmap.yaml:31, 92, 103), with `safety_checker=None` (the checker is outside the hot path).
+
+    tokenise -> CLIP text ([negative; positive]) -> randn latents * init_noise_sigma -> for t: UNet on the
+    duplicated batch, CFG combine, scheduler.step -> VAE decode(latents / scaling_factor) -> clamp(x/2+.5) ->
+    NHWC -> (x*255).round().astype(uint8)
+
+TEST INFRASTRUCTURE — see oracle/__init__.py.  Also the timed CPU baseline of bench.py.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .clip import CLIPTextModel
+from .schedulers import make_scheduler
+from .unet import UNet2DConditionModel
+from .vae import AutoencoderKLDecoder
+
+
+class OraclePipeline:
+    def __init__(self, cfg: dict, unet_sd: dict, vae_sd: dict, text_sd: dict, tokenize, scheduler: str | None = None):
+        """tokenize: callable(list[str]) -> list[list[int]] (oracle.tokenizer.OracleTokenizer, or golden ids)."""
+        self.cfg = cfg
+        self.unet = UNet2DConditionModel(cfg["unet"]).eval()
+        self.vae = AutoencoderKLDecoder(cfg["vae"]).eval()
+        self.text_encoder = CLIPTextModel(cfg["text_encoders"][0]).eval()
+        self.unet.load_state_dict(unet_sd, strict=True)
+        self.vae.load_state_dict(vae_sd, strict=True)
+        self.text_encoder.load_state_dict(text_sd, strict=True)
+        self.tokenize = tokenize
+        self.scheduler_kind = scheduler or cfg["scheduler"]["type"]
+
+    @torch.no_grad()
+    def __call__(self, prompt, num_inference_steps=50, guidance_scale=7.5, width=None, height=None, generator=None,
+                 latents=None, negative_prompt=None, scheduler=None, decode=True, max_evals=None):
+        f = self.vae.scale_factor
+        height = height or self.cfg["unet"]["sample_size"] * f
+        width = width or self.cfg["unet"]["sample_size"] * f
+        prompts = [prompt] if isinstance(prompt, str) else list(prompt)
+        b = len(prompts)
+        neg = [negative_prompt or ""] * b if not isinstance(negative_prompt, (list, tuple)) else list(negative_prompt)
+        do_cfg = guidance_scale > 1.0
+        ids = torch.tensor(self.tokenize(prompts), dtype=torch.long)
+        emb = self.text_encoder(ids)
+        if do_cfg:
+            neg_emb = self.text_encoder(torch.tensor(self.tokenize(neg), dtype=torch.long))
+            emb = torch.cat([neg_emb, emb])
+        sched = make_scheduler(self.cfg["scheduler"], scheduler or self.scheduler_kind)
+        sched.set_timesteps(num_inference_steps)
+        shape = (b, 4, height // f, width // f)
+        if latents is None:
+            if isinstance(generator, (list, tuple)):
+                latents = torch.cat([torch.randn((1,) + shape[1:], generator=g, dtype=torch.float32) for g in generator])
+            else:
+                latents = torch.randn(shape, generator=generator, dtype=torch.float32)
+        latents = latents * sched.init_noise_sigma
+        per_step = []
+        eps_per_step = []
+        for i, t in enumerate(sched.timesteps):
+            if max_evals is not None and i >= max_evals:
+                break
+            x_in = torch.cat([latents] * 2) if do_cfg else latents
+            x_in = sched.scale_model_input(x_in, t)
+            eps = self.unet(x_in, t.to(torch.float32), emb)
+            eps_per_step.append(eps.clone())
+            if do_cfg:
+                e_u, e_c = eps.chunk(2)
+                eps = e_u + guidance_scale * (e_c - e_u)
+            latents = sched.step(eps, t, latents)
+            per_step.append(latents.clone())
+        out = {"latents": latents, "per_step": per_step, "eps": eps_per_step, "text": emb,
+               "timesteps": [int(t) for t in sched.timesteps]}
+        if decode:
+            image = self.vae.decode(latents / self.cfg["vae"]["scaling_factor"])
+            out["image_f32"] = image
+            img = (image / 2 + 0.5).clamp(0, 1).permute(0, 2, 3, 1).float().numpy()
+            out["images"] = (img * 255).round().astype("uint8")
+        return out

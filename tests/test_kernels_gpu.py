@@ -5,7 +5,7 @@ import pytest
 import torch
 import torch.nn.functional as F
 
-from test_gemm_gpu import _rand, _report
+from test_gemm_gpu import ACT, _rand, _report
 
 pytestmark = pytest.mark.gpu
 
@@ -17,12 +17,12 @@ def test_groupnorm(cuda_lib, b200sd, nimg, hw, c0, c1, groups, silu):
     torch.manual_seed(0)
     ops = b200sd.ops
     C = c0 + c1
-    x0 = (_rand(nimg, hw, c0).float() * 2 + 0.7).to(torch.bfloat16)
-    x1 = (_rand(nimg, hw, c1).float() * 0.5 - 1.1).to(torch.bfloat16) if c1 else None
+    x0 = (_rand(nimg, hw, c0).float() * 2 + 0.7).to(ACT())
+    x1 = (_rand(nimg, hw, c1).float() * 0.5 - 1.1).to(ACT()) if c1 else None
     gamma = torch.randn(C, device="cuda")
     beta = torch.randn(C, device="cuda")
     stats = torch.zeros(nimg, groups, 2, device="cuda")
-    out = torch.empty(nimg, hw, C, device="cuda", dtype=torch.bfloat16)
+    out = torch.empty(nimg, hw, C, device="cuda", dtype=ACT())
     st, ap = ops.groupnorm(x0, out, stats, gamma, beta, nimg=nimg, hw=hw, c0=c0, groups=groups, eps=1e-5, silu=silu,
                            x1=x1, c1=c1)
     s = ops.current_stream()
@@ -40,7 +40,7 @@ def test_groupnorm(cuda_lib, b200sd, nimg, hw, c0, c1, groups, silu):
 def test_layernorm(cuda_lib, b200sd, rows, c):
     torch.manual_seed(0)
     ops = b200sd.ops
-    x = (_rand(rows, c).float() * 3 + 1).to(torch.bfloat16)
+    x = (_rand(rows, c).float() * 3 + 1).to(ACT())
     g, b = torch.randn(c, device="cuda"), torch.randn(c, device="cuda")
     out = torch.empty_like(x)
     ops.layernorm(x, out, g, b, rows=rows, c=c, eps=1e-5)(ops.current_stream())
@@ -50,11 +50,11 @@ def test_layernorm(cuda_lib, b200sd, rows, c):
 
 def test_softmax_rows(cuda_lib, b200sd):
     ops = b200sd.ops
-    x = (_rand(50, 4096).float() * 4).to(torch.bfloat16)
-    ref = torch.softmax(x.float(), dim=-1)
-    ops.softmax_rows(x, rows=50, cols=4096)(ops.current_stream())
+    x = torch.randn(50, 4096, device="cuda") * 4
+    out = torch.empty(50, 4096, device="cuda", dtype=ACT())
+    ops.softmax_rows(x, out, rows=50, cols=4096)(ops.current_stream())
     torch.cuda.synchronize()
-    _report("softmax_rows", x, ref, 1e-2)
+    _report("softmax_rows", out, torch.softmax(x, dim=-1), 1e-2)
 
 
 @pytest.mark.parametrize("batch,heads,nq,nk,d,causal", [
@@ -77,7 +77,7 @@ def test_attention(cuda_lib, b200sd, batch, heads, nq, nk, d, causal):
     kv = _rand(batch, nk, 2 * C)
     q = qkv[..., :C]
     k, v = kv[..., :C], kv[..., C:]
-    out = torch.full((batch, nq, C), float("nan"), device="cuda", dtype=torch.bfloat16)
+    out = torch.full((batch, nq, C), float("nan"), device="cuda", dtype=ACT())
     scale = d ** -0.5
     ops.attention(q, k, v, out, batch=batch, heads=heads, nq=nq, nk=nk, d=d, ldq=3 * C, ldk=2 * C, ldv=2 * C, ldo=C,
                   scale=scale, causal=causal)(ops.current_stream())
@@ -112,9 +112,9 @@ def test_prep_temb_sched_ddim_euler(cuda_lib, b200sd):
     ])
     counter = torch.zeros(2, dtype=torch.int32, device="cuda")
     s = ops.current_stream()
-    xin = torch.empty(2 * b, hw, 8, device="cuda", dtype=torch.bfloat16)
+    xin = torch.empty(2 * b, hw, 8, device="cuda", dtype=ACT())
     ops.prep_unet_input(lat, xin, table, counter, b=b, hw=hw, cfg=True)(s)
-    temb = torch.empty(2 * b, 320, device="cuda", dtype=torch.bfloat16)
+    temb = torch.empty(2 * b, 320, device="cuda", dtype=ACT())
     ops.timestep_embedding(temb, table, counter, rows=2 * b, dim=320)(s)
     torch.cuda.synchronize()
     ref_in = torch.cat([lat * 0.5, torch.zeros_like(lat)], dim=-1)
@@ -147,7 +147,7 @@ def test_layout_kernels(cuda_lib, b200sd):
     ops = b200sd.ops
     s = ops.current_stream()
     x = _rand(2, 6, 10, 64)
-    up = torch.empty(2, 12, 20, 64, device="cuda", dtype=torch.bfloat16)
+    up = torch.empty(2, 12, 20, 64, device="cuda", dtype=ACT())
     ops.upsample2x(x, up, nimg=2, h=6, w_=10, c=64)(s)
     ref = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest").permute(0, 2, 3, 1)
     torch.cuda.synchronize()
@@ -159,7 +159,7 @@ def test_layout_kernels(cuda_lib, b200sd):
     w = _rand(cout, c, 3, 3, scale=(9 * c) ** -0.5)
     nbytes = ops.im2col_s2_bytes(nimg=nimg, h=H, w_=W, c=c)
     assert nbytes == nimg * 8 * 8 * 9 * 64 * 2
-    col = torch.empty(nbytes // 2, device="cuda", dtype=torch.bfloat16)
+    col = torch.empty(nbytes // 2, device="cuda", dtype=ACT())
     ops.im2col_s2(x, col, nimg=nimg, h=H, w_=W, c=c)(s)
     out = torch.empty(nimg, 8, 8, cout, device="cuda", dtype=torch.float32)
     ops.gemm(col, ops.pack_conv_weight(w.float().cpu()).cuda().view(cout, 1, -1), out, nimg=1, h=1, w_=nimg * 64,
@@ -170,7 +170,7 @@ def test_layout_kernels(cuda_lib, b200sd):
 
     ids = torch.randint(0, 1000, (2 * 77,), device="cuda", dtype=torch.int32)
     tok, pos = _rand(1000, 64), _rand(77, 64)
-    emb = torch.empty(2 * 77, 64, device="cuda", dtype=torch.bfloat16)
+    emb = torch.empty(2 * 77, 64, device="cuda", dtype=ACT())
     ops.clip_embed(ids, tok, pos, emb, rows=2 * 77, seq=77, c=64, vocab=1000)(s)
     torch.cuda.synchronize()
     ref = tok.float()[ids.long()] + pos.float().repeat(2, 1)
@@ -184,7 +184,7 @@ def test_layout_kernels(cuda_lib, b200sd):
     assert torch.equal(u8, ref)
 
     lat = torch.randn(2, 64, 4, device="cuda")
-    o = torch.empty(2, 64, 8, device="cuda", dtype=torch.bfloat16)
-    ops.latent_to_bf16(lat, o, b=2, hw=64, scale=1 / 0.18215)(s)
+    o = torch.empty(2, 64, 8, device="cuda", dtype=ACT())
+    ops.latent_to_act(lat, o, b=2, hw=64, scale=1 / 0.18215)(s)
     torch.cuda.synchronize()
     _report("latent_to_bf16", o, torch.cat([lat / 0.18215, torch.zeros_like(lat)], -1), 1e-2)

@@ -1,0 +1,99 @@
+"""End-to-end GPU parity (BASELINE.json configs[0]): tiny SD-architecture UNet/VAE/CLIP, 2 prompts, 64x64, 4 steps —
+the product pipeline (CUDA kernels through the C ABI) against the fp32 CPU oracle on identical weights, prompts and
+CPU-generator seeds.  Tolerances are BASELINE.json's north_star: tokenisation and timesteps bit-exact, per-step
+latents within 1e-2 relative error, final image PSNR >= 30 dB."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+PROMPTS = ["a photo of a panda riding a motorbike", "a cabin in the forest at night, detailed"]
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
+
+
+def _psnr(a, b):
+    mse = np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)
+    return 99.0 if mse == 0 else 10 * math.log10(255.0 ** 2 / mse)
+
+
+@pytest.fixture(scope="module")
+def tiny(b200sd, cuda_lib):
+    import importlib
+    W = importlib.import_module("k8s-nvidia-gpus_b200.weights")
+    T = importlib.import_module("k8s-nvidia-gpus_b200.tokenizer")
+    P = importlib.import_module("k8s-nvidia-gpus_b200.pipeline")
+    from oracle.pipeline import OraclePipeline
+    cfg = W.load_config("tiny")
+    usd = W.random_state_dict(W.unet_schema(cfg["unet"]), 0)
+    vsd = W.random_state_dict(W.vae_decoder_schema(cfg["vae"]), 1)
+    tsd = W.random_state_dict(W.clip_text_schema(cfg["text_encoders"][0]), 2)
+    tok = T.CLIPTokenizer.synthetic(cfg["text_encoders"][0]["vocab_size"])
+    oracle = OraclePipeline(cfg, usd, vsd, tsd, tok)
+    pipe = P.StableDiffusionPipeline(cfg, usd, vsd, tsd, tokenizer=tok)
+    return cfg, oracle, pipe
+
+
+def _gens():
+    return [torch.Generator().manual_seed(1234 + i) for i in range(len(PROMPTS))]
+
+
+def test_text_encoder_parity(tiny):
+    cfg, oracle, pipe = tiny
+    ids, ctx, _ = pipe._encode(PROMPTS, [""] * len(PROMPTS))
+    torch.cuda.synchronize()
+    ref_ids = oracle.tokenize([""] * len(PROMPTS) + PROMPTS)
+    assert ids.tolist() == ref_ids  # bit-exact tokenisation
+    with torch.no_grad():
+        ref = oracle.text_encoder(torch.tensor(ref_ids, dtype=torch.long))
+    r = _rel(ctx.cpu(), ref)
+    print("text encoder rel err", r)
+    assert r < 1e-2
+
+
+@pytest.mark.parametrize("kind,steps", [("ddim", 4), ("pndm", 4), ("euler", 4)])
+def test_denoise_and_image_parity(tiny, kind, steps):
+    cfg, oracle, pipe = tiny
+    ref = oracle(PROMPTS, num_inference_steps=steps, guidance_scale=7.5, width=64, height=64, generator=_gens(),
+                 scheduler=kind)
+    got_steps, got_t = [], []
+    out = pipe(PROMPTS, num_inference_steps=steps, guidance_scale=7.5, width=64, height=64, generator=_gens(),
+               scheduler=kind, output_type="u8",
+               callback_on_step_end=lambda p, i, t, kw: (got_steps.append(kw["latents"]), got_t.append(int(t))))
+    assert got_t == ref["timesteps"]  # bit-exact timestep table
+    assert len(got_steps) == len(ref["per_step"])
+    rels = [_rel(a, b) for a, b in zip(got_steps, ref["per_step"])]
+    print(kind, "per-step latent rel err", ["%.2e" % r for r in rels])
+    assert max(rels) <= 1e-2, rels
+    psnr = [_psnr(out.images[i], ref["images"][i]) for i in range(len(PROMPTS))]
+    print(kind, "PSNR", psnr, "timings", pipe.last_timings)
+    assert min(psnr) >= 30.0, psnr
+
+
+def test_single_prompt_single_generator_and_pil(tiny):
+    """The exact call the reference server makes (configmap.yaml:105-112): one prompt, one generator, .images[0]."""
+    cfg, oracle, pipe = tiny
+    g = torch.Generator().manual_seed(7)
+    ref = oracle("a red motorbike", num_inference_steps=3, guidance_scale=7.5, width=64, height=64,
+                 generator=torch.Generator().manual_seed(7), scheduler="ddim")
+    img = pipe("a red motorbike", num_inference_steps=3, guidance_scale=7.5, width=64, height=64, generator=g,
+               scheduler="ddim").images[0]
+    assert img.size == (64, 64) and img.mode == "RGB"
+    assert _psnr(np.asarray(img), ref["images"][0]) >= 30.0
+    # guidance <= 1 disables CFG (single UNet batch), like upstream
+    ref1 = oracle("a red motorbike", num_inference_steps=2, guidance_scale=1.0, width=64, height=64,
+                  generator=torch.Generator().manual_seed(7), scheduler="ddim")
+    lat = pipe("a red motorbike", num_inference_steps=2, guidance_scale=1.0, width=64, height=64,
+               generator=torch.Generator().manual_seed(7), scheduler="ddim", output_type="latent").images
+    assert _rel(lat, ref1["latents"]) <= 1e-2
+
+
+def test_rejects_bad_size(tiny):
+    _, _, pipe = tiny
+    with pytest.raises(ValueError, match="divisible by 8"):
+        pipe("x", num_inference_steps=1, width=60, height=64)
