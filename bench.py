@@ -1,0 +1,401 @@
+#!/usr/bin/env python3
+"""bench.py — images/sec of the SD-class batch text-to-image hot path on N B200s of one node.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one rank per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (fp32 oracle) on the host cores
+
+One bench "step" = one full pass of the hot path over one batch of synthetic prompts: CLIP text encoding, cross-
+attention K/V projection, 25 DDIM denoise steps (CFG 7.5, UNet on the duplicated batch) and VAE decode to uint8 images,
+SD 1.5 architecture at 512x512, batch 8 per GPU (BASELINE.json configs[1]; configs[2] when N > 1: prompts sharded
+data-parallel, one NCCL gather of the uint8 images per batch).  Weights are random-init (no checkpoints offline).
+
+Prints ONE JSON line (rank 0).  `value`: inputs resident in HBM.  `e2e`: through the public pipeline call with host
+prompts / host latents / host images, copies inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+UNET_GF_PER_SAMPLE = 803.27  # SURVEY.md §8(d), algorithmic 2*MAC of the SD1.5 UNet forward at 64x64 latent
+VAE_GF_PER_IMAGE = 2514.5
+CLIP_GF_PER_SEQ = 13.30
+
+
+def synthetic_prompts(n, offset=0):
+    subj = ["panda", "astronaut", "robot", "dragon", "cat", "horse", "castle", "cabin"]
+    return [f"a photo of synthetic subject {i + offset:03d}, a {subj[(i + offset) % len(subj)]} riding a motorbike, "
+            f"variant {(i + offset) % 7}" for i in range(n)]
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"tf_burst": d.get("bf16_tflops"), "tf_sustained": d.get("bf16_tflops_sustained"),
+                "hbm_gbs": d.get("hbm_gbs"), "source": "measured"}
+    return {"tf_burst": 1590.0, "tf_sustained": 1400.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.path = tempfile.mktemp(suffix=".csv")
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, parts[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        try:
+            os.unlink(self.path)
+        except OSError:
+            pass
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------- reference arm
+def build_oracle(cfg):
+    """fp32 CPU oracle modules with their own default (random) init — same distributions as the GPU arm's weights."""
+    from oracle.clip import CLIPTextModel
+    from oracle.unet import UNet2DConditionModel
+    from oracle.vae import AutoencoderKLDecoder
+    torch.manual_seed(0)
+    return (UNet2DConditionModel(cfg["unet"]).eval(), AutoencoderKLDecoder(cfg["vae"]).eval(),
+            CLIPTextModel(cfg["text_encoders"][0]).eval())
+
+
+@torch.no_grad()
+def cpu_sample(cfg, unet, vae, clip, steps, warmup, inference_steps, h, w):
+    """Bounded sample of the reference CPU path for ONE image: `steps` timed CFG-paired UNet evaluations (2 samples),
+    plus one VAE decode and one 2-sequence CLIP pass; images/sec = 1 / (inference_steps * t_unet + t_vae + t_clip)."""
+    ids = torch.randint(0, cfg["text_encoders"][0]["vocab_size"], (2, 77))
+    t0 = time.perf_counter()
+    ctx = clip(ids)
+    t_clip = time.perf_counter() - t0
+    x = torch.randn(2, 4, h, w)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        unet(x, torch.tensor([961.0]), ctx)
+        times.append(time.perf_counter() - t0)
+    t_unet = sum(times[warmup:]) / max(1, steps)
+    t0 = time.perf_counter()
+    vae.decode(torch.randn(1, 4, h, w))
+    t_vae = time.perf_counter() - t0
+    ips = 1.0 / (inference_steps * t_unet + t_vae + t_clip)
+    return {"ips": ips, "t_unet_pair_s": t_unet, "t_vae_s": t_vae, "t_clip_s": t_clip}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import importlib
+    Wt = importlib.import_module("k8s-nvidia-gpus_b200.weights")
+    cfg = Wt.load_config(args.model)
+    torch.set_num_threads(os.cpu_count() or 1)
+    unet, vae, clip = build_oracle(cfg)
+    f = 2 ** (len(cfg["vae"]["block_out_channels"]) - 1)
+    h, w = args.height // f, args.width // f
+    r = cpu_sample(cfg, unet, vae, clip, args.steps, args.warmup, args.inference_steps, h, w)
+    sample = (f"1 image: {args.steps} timed + {args.warmup} warm-up CFG-paired UNet evaluations (2 samples, "
+              f"{h}x{w} latent), 1 VAE decode, 1 CLIP pass of 2 sequences; images/sec = 1/({args.inference_steps}"
+              f"*t_unet + t_vae + t_clip)")
+    line = {
+        "impl": "reference", "metric": "images/sec", "value": r["ips"], "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["t_unet_pair_s"] * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, cfg, 1),
+        "cpu_baseline": {"value": r["ips"], "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": r["ips"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "detail": {k: round(v, 4) for k, v in r.items()},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, cfg, n_gpus):
+    return {"workload": f"{cfg['name']} architecture (random-init), {args.width}x{args.height}, "
+                        f"{args.inference_steps} DDIM steps, CFG {args.guidance_scale}, batch {args.batch} per GPU",
+            "global_batch": args.batch * n_gpus, "per_gpu_batch": args.batch, "scheduler": args.scheduler,
+            "inference_steps": args.inference_steps, "guidance_scale": args.guidance_scale,
+            "resolution": [args.width, args.height], "parallelism": f"dp{n_gpus} (prompt sharding, image gather)",
+            "l2": "inputs larger than L2: each step streams ~2 GB of weights plus activations through a 126 MB L2; "
+                  "no explicit flush"}
+
+
+# ---------------------------------------------------------------------------------------------------- CUDA arm
+def flops_of_call(call):
+    p = call.params
+    if call.name == "b200sd_gemm":
+        m = p.nimg * p.h * p.w_
+        return 2.0 * m * p.n * (p.ksize * p.ksize) * (p.c0 + p.c1), "gemm"
+    if call.name == "b200sd_attention":
+        return 4.0 * p.batch * p.heads * p.nq * p.nk * p.d, "attention"
+    return 0.0, call.name.replace("b200sd_", "")
+
+
+def profile_plan(plan, blocker=None):
+    """Per-launch device time with CUDA events on the launching stream.  A long-running `blocker` plan is enqueued
+    first so the host runs ahead of the GPU and launch latency does not leak into the per-kernel intervals."""
+    from b200sd import ops
+    s = ops.current_stream()
+    n = len(plan.calls)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+    if blocker is not None:
+        blocker.run()
+    ev[0].record()
+    for i, c in enumerate(plan.calls):
+        c(s)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    agg = {}
+    for i, c in enumerate(plan.calls):
+        fl, kind = flops_of_call(c)
+        a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0})
+        a["launches"] += 1
+        a["ms"] += ev[i].elapsed_time(ev[i + 1])
+        a["flops"] += fl
+    return agg
+
+
+def run_cuda(args):
+    import importlib
+    import torch.distributed as dist
+    import b200sd
+    P = importlib.import_module("k8s-nvidia-gpus_b200.pipeline")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    b200sd.lib.load()
+    info = b200sd.lib.device_info()
+    pipe = P.StableDiffusionPipeline.from_pretrained(args.model, device=f"cuda:{local}", scheduler=args.scheduler)
+    cfg = pipe.cfg
+    f = pipe.vae_scale_factor
+    h, w = args.height // f, args.width // f
+    B = args.batch
+    sched = pipe.make_schedule(args.inference_steps)
+    evals = sched.num_evals
+    job = pipe.job(B, h, w, args.guidance_scale, True)
+
+    # synthetic inputs for this rank's shard (global image index = rank * B + i; seed = 1234 + index)
+    prompts = synthetic_prompts(B, rank * B)
+    gens = [torch.Generator().manual_seed(1234 + rank * B + i) for i in range(B)]
+    ids = pipe.tokenize(prompts, [""] * B, True)
+    lat = pipe.prepare_latents(B, h, w, gens, sched.init_noise_sigma)
+    job.ids_dev.copy_(ids)
+    job.init_latents.copy_(lat.permute(0, 2, 3, 1).reshape(B, h * w, 4))
+    job.step_table[:evals].copy_(sched.table)
+    gathered = None
+    if world > 1:
+        gathered = torch.empty((world,) + tuple(job.images.shape), dtype=torch.uint8, device=job.images.device)
+
+    def one_batch_resident():
+        job.reset()
+        job.run(evals)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, job.images)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_batch_resident()
+    sampler = ClockSampler(local)
+    sync_all()
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    e0.record()
+    for _ in range(args.steps):
+        one_batch_resident()
+    e1.record()
+    sync_all()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=job.images.device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = ms.item()
+
+    # UNet ms per denoise step (graph replay of one CFG-paired evaluation of the local batch + scheduler update)
+    job.reset()
+    torch.cuda.synchronize()
+    u0, u1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    u0.record()
+    for _ in range(evals):
+        job.step_plan.launch()
+    u1.record()
+    torch.cuda.synchronize()
+    unet_ms = u0.elapsed_time(u1) / evals
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end to end through the public call: host prompts / CPU-generator latents in, host uint8 images out
+    def one_batch_e2e():
+        g = [torch.Generator().manual_seed(1234 + rank * B + i) for i in range(B)]
+        out = pipe(prompts, num_inference_steps=args.inference_steps, guidance_scale=args.guidance_scale,
+                   width=args.width, height=args.height, generator=g, output_type="u8")
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, job.images)
+        return out
+
+    one_batch_e2e()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_batch_e2e()
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=job.images.device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_ips = args.steps * B * world / e2e_s.item()
+    h2d = job.ids_host.numel() * 4 + job.lat_host.numel() * 4 + evals * 16 * 4
+    d2h = job.img_host.numel()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # per-kernel breakdown of one denoise step (eager launches with events; VAE plan as the run-ahead blocker)
+    job.reset()
+    prof = profile_plan(job.step_plan, blocker=job.vae_plan)
+    vprof = profile_plan(job.vae_plan, blocker=job.vae_plan)
+    peaks = measured_peaks()
+    gm = prof["gemm"]
+    achieved_tf = gm["flops"] / (gm["ms"] * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("gemm_conv_kernel_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "tensor", "kernel": "gemm_conv_kernel (tcgen05 implicit-GEMM conv/linear)",
+                "achieved": achieved_tf, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                "frac": achieved_tf / peaks["tf_sustained"], "traffic": traffic,
+                "peak_source": f"{peaks['source']} (sustained cuBLAS bf16; burst {peaks['tf_burst']})",
+                "launches_per_unet_step": gm["launches"], "flops_per_launch": gm["flops"] / gm["launches"],
+                "avg_launch_ms": gm["ms"] / gm["launches"],
+                "share_of_unet_step": gm["ms"] / sum(a["ms"] for a in prof.values())}
+    step_flops = sum(a["flops"] for a in prof.values())
+    breakdown = {k: {"launches": a["launches"], "ms": round(a["ms"], 4),
+                     "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None}
+                 for k, a in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+    vae_breakdown = {k: {"launches": a["launches"], "ms": round(a["ms"], 4),
+                         "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None}
+                     for k, a in sorted(vprof.items(), key=lambda kv: -kv[1]["ms"])}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        unet, vae, clip = build_oracle(cfg)
+        r = cpu_sample(cfg, unet, vae, clip, 2, 1, args.inference_steps, h, w)
+        cpu = {"value": r["ips"], "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
+               "sample": f"1 image: 2 timed + 1 warm-up CFG-paired UNet evaluations, 1 VAE decode, 1 CLIP pass; "
+                         f"images/sec = 1/({args.inference_steps}*t_unet + t_vae + t_clip)",
+               "detail": {k: round(v, 4) for k, v in r.items()}}
+
+    ips = args.steps * B * world / (total_ms * 1e-3)
+    img_tf = (evals * 2 * UNET_GF_PER_SAMPLE + VAE_GF_PER_IMAGE + 2 * CLIP_GF_PER_SEQ) / 1e3
+    line = {
+        "metric": "images/sec", "value": ips, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "fp16" if b200sd.lib.act_dtype() == torch.float16 else "bf16",
+        "data": "synthetic", "config": workload_config(args, cfg, world),
+        "unet_ms_per_step": unet_ms,
+        "unet_tflops": 2 * B * UNET_GF_PER_SAMPLE / 1e3 / (unet_ms * 1e-3) if cfg["name"] == "sd15" else None,
+        "unet_step_algorithmic_tflop": step_flops / 1e12,
+        "image_algorithmic_tflop": img_tf if cfg["name"] == "sd15" else None,
+        "e2e": {"value": e2e_ips, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": args.steps * job.launches(evals),
+        "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        "unet_step_breakdown": breakdown, "vae_breakdown": vae_breakdown,
+        "device": {"sm_count": info["sm_count"], "cc": list(info["cc"])},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="sd15")
+    ap.add_argument("--batch", type=int, default=8, help="images per GPU per bench step")
+    ap.add_argument("--inference-steps", type=int, default=25)
+    ap.add_argument("--guidance-scale", type=float, default=7.5)
+    ap.add_argument("--width", type=int, default=512)
+    ap.add_argument("--height", type=int, default=512)
+    ap.add_argument("--scheduler", default="ddim")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args(argv)
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus and args.gpus > 1:
+        print(f"bench.py: --gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})", file=sys.stderr)
+        return 2
+    return run_cuda(args)
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

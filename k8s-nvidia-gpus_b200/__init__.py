@@ -6,5 +6,14 @@ The directory name contains '-' so import it with importlib (see `b200sd.py` at 
 """
 from . import lib  # noqa: F401
 from . import ops  # noqa: F401
+from . import tokenizer  # noqa: F401
+from . import weights  # noqa: F401
+from . import schedulers  # noqa: F401
+from . import engine  # noqa: F401
+from . import clip  # noqa: F401
+from . import unet  # noqa: F401
+from . import vae  # noqa: F401
+from . import pipeline  # noqa: F401
+from .pipeline import StableDiffusionPipeline  # noqa: F401
 
 __version__ = "0.1.0"

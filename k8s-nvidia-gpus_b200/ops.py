@@ -26,24 +26,28 @@ def ceil_to(v: int, m: int) -> int:
 
 # ------------------------------------------------------------------------------------------------ weight packing
 def pack_conv_weight(w: torch.Tensor, split=None) -> torch.Tensor:
-    """[Cout, Cin, kh, kw] (upstream layout) -> bf16 [Cout, kh*kw, c0p + c1p], channels zero-padded to 64
-    per source so each 64-wide K block of the implicit GEMM belongs to exactly one source / filter tap."""
+    """[Cout, Cin, kh, kw] (upstream layout) -> act16 [Cout, kh*kw, c0p + c1p], channels zero-padded to
+    64 per source so each 64-wide K block of the implicit GEMM belongs to exactly one source / filter tap.  Runs on
+    whatever device `w` lives on."""
     cout, cin, kh, kw = w.shape
     split = split or (cin,)
     assert sum(split) == cin
+    dt = act_dtype()
     wt = w.permute(0, 2, 3, 1).reshape(cout, kh * kw, cin)
+    if len(split) == 1 and cin % 64 == 0:
+        return wt.to(dt).contiguous()
     parts, off = [], 0
     for c in split:
         cp = ceil_to(c, 64)
-        blk = torch.zeros(cout, kh * kw, cp, dtype=torch.float32)
-        blk[:, :, :c] = wt[:, :, off:off + c]
+        blk = torch.zeros(cout, kh * kw, cp, dtype=dt, device=w.device)
+        blk[:, :, :c] = wt[:, :, off:off + c].to(dt)
         parts.append(blk)
         off += c
-    return torch.cat(parts, dim=2).to(act_dtype()).contiguous()
+    return torch.cat(parts, dim=2).contiguous()
 
 
 def pack_linear_weight(w: torch.Tensor, split=None) -> torch.Tensor:
-    """[N, K] -> bf16 [N, 1, Kp]."""
+    """[N, K] -> act16 [N, 1, Kp]."""
     return pack_conv_weight(w[:, :, None, None], split)
 
 

@@ -13,7 +13,6 @@ uint8 image runs as b200sd CUDA kernels; there is no CPU or library fallback.
 from __future__ import annotations
 
 import os
-from types import SimpleNamespace
 
 import numpy as np
 import torch
@@ -50,6 +49,66 @@ class _VaeHandle:
         return self
 
 
+class Job:
+    """Everything prepared for one (batch, latent size, guidance, scheduler kind) shape: device buffers + plans.
+    `run(num_evals)` enqueues text encoder -> K/V projection -> denoise steps -> VAE decode on the current stream,
+    reading token ids / initial latents from `ids_dev` / `init_latents` (already resident in HBM)."""
+
+    def __init__(self, pipe, batch, h, w, guidance_scale, cfg_on):
+        self.pipe, self.batch, self.h, self.w = pipe, batch, h, w
+        self.cfg_on = cfg_on
+        dev = pipe.device
+        self.n_text = batch * (2 if cfg_on else 1)
+        self.ids_dev = torch.zeros(self.n_text * 77, dtype=torch.int32, device=dev)
+        self.init_latents = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=dev)
+        self.latents = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=dev)
+        self.history = torch.zeros(4, batch, h * w, 4, dtype=torch.float32, device=dev)
+        self.cur_sample = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=dev)
+        self.step_table = torch.zeros(MAX_EVALS, 16, dtype=torch.float32, device=dev)
+        self.step_counter = torch.zeros(2, dtype=torch.int32, device=dev)
+        # pinned staging for the end-to-end path (host -> device inputs, device -> host images)
+        self.ids_host = torch.zeros(self.n_text * 77, dtype=torch.int32).pin_memory()
+        self.lat_host = torch.zeros(batch, h * w, 4, dtype=torch.float32).pin_memory()
+        self.table_host = torch.zeros(MAX_EVALS, 16, dtype=torch.float32).pin_memory()
+        self.text_plan, self.ctx = pipe.text_encoder.build_plan(self.n_text, self.ids_dev)
+        self.kv_plan, self.kv = pipe.unet.build_kv_plan(self.n_text, self.ctx)
+        self.step_plan, self.dbg = pipe.unet.build_step_plan(
+            batch, h, w, self.latents, self.step_table, self.step_counter, self.kv, guidance_scale=guidance_scale,
+            cfg_on=cfg_on, history=self.history, cur_sample=self.cur_sample)
+        self.vae_plan, self.images = pipe.vae_engine.build_plan(batch, h, w, self.latents)
+        f = pipe.vae_scale_factor
+        self.img_host = torch.zeros(batch, h * f, w * f, 3, dtype=torch.uint8).pin_memory()
+        # one eager pass validates every launch configuration before capture
+        self.text_plan.run()
+        self.kv_plan.run()
+        self.vae_plan.run()
+        if pipe.use_cuda_graph:
+            self.step_plan.capture()
+        else:
+            self.step_plan.run()
+        torch.cuda.synchronize()
+
+    def reset(self):
+        """Start a new generation from `init_latents` (device -> device)."""
+        self.latents.copy_(self.init_latents)
+        self.step_counter.zero_()
+        self.history.zero_()
+
+    def run(self, num_evals, decode=True, on_step=None):
+        self.text_plan.run()
+        self.kv_plan.run()
+        for i in range(num_evals):
+            self.step_plan.launch()
+            if on_step is not None:
+                on_step(i)
+        if decode:
+            self.vae_plan.run()
+
+    def launches(self, num_evals, decode=True):
+        n = len(self.text_plan) + len(self.kv_plan) + num_evals * len(self.step_plan)
+        return n + (len(self.vae_plan) if decode else 0)
+
+
 class StableDiffusionPipeline:
     def __init__(self, cfg: dict, unet_sd: dict, vae_sd: dict, text_sd: dict, tokenizer: CLIPTokenizer | None = None,
                  device: str = "cuda", scheduler: str | None = None):
@@ -71,12 +130,9 @@ class StableDiffusionPipeline:
         self.scheduler_kind = (scheduler or cfg["scheduler"]["type"]).lower()
         self.vae_scale_factor = self.vae_engine.scale_factor
         self.use_cuda_graph = os.environ.get("B200SD_NO_GRAPH", "0") != "1"
-        self._text_cache = {}
-        self._step_cache = {}
-        self._vae_cache = {}
-        self.step_table = torch.zeros(MAX_EVALS, 16, dtype=torch.float32, device=self.device)
-        self.step_counter = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self._jobs = {}
         self.last_timings = {}
+        self.model_id = cfg.get("name", "?")
 
     # ------------------------------------------------------------------ construction (reference configmap.yaml:41)
     @classmethod
@@ -85,16 +141,18 @@ class StableDiffusionPipeline:
         """model_id: a config name under configs/ ("sd15", "tiny"), a config .json path, or a hub-style id such as
         "runwayml/stable-diffusion-v1-5" (mapped to the sd15 architecture).  No checkpoints exist offline, so
         weights are random-init (seeded) in the diffusers key layout; `torch_dtype` is accepted for signature
-        compatibility (compute is bf16 operands / fp32 accumulation and statistics)."""
+        compatibility (compute is 16-bit operands with fp32 accumulation and statistics; lib.act_dtype())."""
         name = model_id
         if not os.path.exists(model_id) and not os.path.exists(os.path.join(Wt.CONFIG_DIR, f"{model_id}.json")):
-            low = model_id.lower()
-            name = "sdxl" if "xl" in low else "sd15"
+            name = "sdxl" if "xl" in model_id.lower() else "sd15"
         cfg = Wt.load_config(name)
-        unet_sd = Wt.random_state_dict(Wt.unet_schema(cfg["unet"]), seed)
-        vae_sd = Wt.random_state_dict(Wt.vae_decoder_schema(cfg["vae"]), seed + 1)
-        text_sd = Wt.random_state_dict(Wt.clip_text_schema(cfg["text_encoders"][0]), seed + 2)
-        return cls(cfg, unet_sd, vae_sd, text_sd, device=device, scheduler=scheduler)
+        kw = dict(round_dtype=ops.act_dtype(), device=device, store_dtype=ops.act_dtype())  # drawn on the GPU
+        unet_sd = Wt.random_state_dict(Wt.unet_schema(cfg["unet"]), seed, **kw)
+        vae_sd = Wt.random_state_dict(Wt.vae_decoder_schema(cfg["vae"]), seed + 1, **kw)
+        text_sd = Wt.random_state_dict(Wt.clip_text_schema(cfg["text_encoders"][0]), seed + 2, **kw)
+        pipe = cls(cfg, unet_sd, vae_sd, text_sd, device=device, scheduler=scheduler)
+        pipe.model_id = model_id
+        return pipe
 
     # memory toggles of the reference (configmap.yaml:42-43, 46-47): identity maths, ignored on 180 GB parts
     def enable_attention_slicing(self, *_a, **_k):
@@ -107,44 +165,21 @@ class StableDiffusionPipeline:
         return self
 
     # ------------------------------------------------------------------ stages
-    def _encode(self, prompts, negative):
-        """[uncond; cond] bf16 [2B, 77, C] — StableDiffusionPipeline.encode_prompt ordering."""
-        texts = list(negative) + list(prompts)
-        ids = torch.tensor(self.tokenizer(texts), dtype=torch.int32)
-        n = len(texts)
-        if n not in self._text_cache:
-            ids_dev = torch.zeros(n * 77, dtype=torch.int32, device=self.device)
-            plan, out = self.text_encoder.build_plan(n, ids_dev)
-            kv_plan, kv = self.unet.build_kv_plan(n, out)
-            self._text_cache[n] = (ids_dev, plan, out, kv_plan, kv)
-        ids_dev, plan, out, kv_plan, kv = self._text_cache[n]
-        ids_dev.copy_(ids.reshape(-1), non_blocking=True)
-        plan.run()
-        kv_plan.run()
-        return ids, out, kv
+    def job(self, batch, h, w, guidance_scale, cfg_on) -> Job:
+        key = (batch, h, w, float(guidance_scale), cfg_on)
+        if key not in self._jobs:
+            self._jobs[key] = Job(self, batch, h, w, guidance_scale, cfg_on)
+        return self._jobs[key]
 
-    def _step_plan(self, batch, h, w, kv, guidance_scale, cfg_on, n_text):
-        key = (batch, h, w, float(guidance_scale), cfg_on, n_text)
-        if key not in self._step_cache:
-            latents = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=self.device)
-            history = torch.zeros(4, batch, h * w, 4, dtype=torch.float32, device=self.device)
-            cur = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=self.device)
-            plan, dbg = self.unet.build_step_plan(batch, h, w, latents, self.step_table, self.step_counter, kv,
-                                                  guidance_scale=guidance_scale, cfg_on=cfg_on, history=history,
-                                                  cur_sample=cur)
-            if self.use_cuda_graph:
-                saved = (latents.clone(), self.step_counter.clone())
-                plan.capture()
-                latents.copy_(saved[0])
-                self.step_counter.copy_(saved[1])
-            self._step_cache[key] = (plan, latents, history, cur, dbg)
-        return self._step_cache[key]
+    def make_schedule(self, num_inference_steps, scheduler=None):
+        kind = (scheduler or self.scheduler_kind).lower()
+        return S.make_schedule(kind, num_inference_steps,
+                               **{k: v for k, v in self.cfg["scheduler"].items() if k != "type"})
 
-    def _vae_plan(self, batch, h, w, latents):
-        key = (batch, h, w, latents.data_ptr())
-        if key not in self._vae_cache:
-            self._vae_cache[key] = self.vae_engine.build_plan(batch, h, w, latents)
-        return self._vae_cache[key]
+    def tokenize(self, prompts, negative, cfg_on):
+        """int32 [n_text * 77] in encode_prompt order: [negative...; positive...]."""
+        texts = (list(negative) if cfg_on else []) + list(prompts)
+        return torch.tensor(self.tokenizer(texts), dtype=torch.int32).reshape(-1)
 
     def prepare_latents(self, batch, h, w, generator, init_sigma):
         """randn_tensor semantics: one draw of the full batch for a single generator, one [1,4,h,w] draw per image for
@@ -191,46 +226,42 @@ class StableDiffusionPipeline:
                 raise ValueError("`negative_prompt` batch size does not match `prompt`")
         cfg_on = guidance_scale > 1.0
         h, w = height // f, width // f
-        kind = (scheduler or self.scheduler_kind).lower()
-        sched = S.make_schedule(kind, num_inference_steps, **{k: v for k, v in self.cfg["scheduler"].items()
-                                                              if k != "type"})
+        sched = self.make_schedule(num_inference_steps, scheduler)
         if sched.num_evals > MAX_EVALS:
             raise ValueError("too many inference steps")
+        job = self.job(batch, h, w, guidance_scale, cfg_on)
 
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-        ev[0].record()
-        _ids, _ctx, kv = self._encode(prompts, negative if cfg_on else [])
-        n_text = len(prompts) + (len(negative) if cfg_on else 0)
-        ev[1].record()
-
-        plan, lat_dev, history, cur, _dbg = self._step_plan(batch, h, w, kv, guidance_scale, cfg_on, n_text)
+        # host side: tokenise, draw latents (NCHW, upstream RNG order) -> NHWC pinned staging
+        job.ids_host.copy_(self.tokenize(prompts, negative, cfg_on))
         if latents is None:
-            latents = self.prepare_latents(batch, h, w, generator, sched.init_noise_sigma)
+            lat = self.prepare_latents(batch, h, w, generator, sched.init_noise_sigma)
         else:
-            latents = latents.to(torch.float32).cpu() * sched.init_noise_sigma
-        # NCHW (upstream layout, RNG order) -> NHWC device latents
-        lat_dev.copy_(latents.permute(0, 2, 3, 1).reshape(batch, h * w, 4).contiguous(), non_blocking=True)
-        self.step_table[: sched.num_evals].copy_(sched.table, non_blocking=True)
-        self.step_counter.zero_()
-        if kind == "pndm":
-            history.zero_()
-        for i, t in enumerate(sched.timesteps):
-            plan.launch()
-            if callback_on_step_end is not None:
-                cb_lat = lat_dev.view(batch, h, w, 4).permute(0, 3, 1, 2).contiguous().cpu()
-                callback_on_step_end(self, i, t, {"latents": cb_lat})
-        ev[2].record()
-        if output_type == "latent":
-            out = lat_dev.view(batch, h, w, 4).permute(0, 3, 1, 2).contiguous().cpu()
+            lat = latents.to(torch.float32).cpu() * sched.init_noise_sigma
+        job.lat_host.copy_(lat.permute(0, 2, 3, 1).reshape(batch, h * w, 4))
+        job.table_host[: sched.num_evals].copy_(sched.table)
+
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        job.ids_dev.copy_(job.ids_host, non_blocking=True)
+        job.init_latents.copy_(job.lat_host, non_blocking=True)
+        job.step_table.copy_(job.table_host, non_blocking=True)
+        job.reset()
+        on_step = None
+        if callback_on_step_end is not None:
+            def on_step(i):
+                cb = job.latents.view(batch, h, w, 4).permute(0, 3, 1, 2).contiguous().cpu()
+                callback_on_step_end(self, i, sched.timesteps[i], {"latents": cb})
+        decode = output_type != "latent"
+        job.run(sched.num_evals, decode=decode, on_step=on_step)
+        if not decode:
+            out = job.latents.view(batch, h, w, 4).permute(0, 3, 1, 2).contiguous().cpu()
             return PipelineOutput(images=out, latents=out)
-        vplan, img_dev = self._vae_plan(batch, h, w, lat_dev)
-        vplan.run()
-        ev[3].record()
-        img = img_dev.cpu().numpy()  # [B, H, W, 3] uint8 (device -> host copy synchronises)
-        self.last_timings = {"text_ms": ev[0].elapsed_time(ev[1]), "denoise_ms": ev[1].elapsed_time(ev[2]),
-                             "vae_ms": ev[2].elapsed_time(ev[3]), "unet_evals": sched.num_evals,
-                             "launches_per_step": plan.kernel_launches(), "vae_launches": vplan.kernel_launches()}
-        final_lat = None
+        job.img_host.copy_(job.images, non_blocking=True)
+        ev[1].record()
+        ev[1].synchronize()
+        img = job.img_host.numpy().copy()
+        self.last_timings = {"gpu_ms": ev[0].elapsed_time(ev[1]), "unet_evals": sched.num_evals,
+                             "launches": job.launches(sched.num_evals)}
         if output_type == "u8":
             images = img
         elif output_type == "np":
@@ -240,7 +271,7 @@ class StableDiffusionPipeline:
             images = [Image.fromarray(a) for a in img]
         else:
             raise ValueError(f"unknown output_type {output_type!r}")
-        return PipelineOutput(images=images, nsfw_content_detected=None, latents=final_lat)
+        return PipelineOutput(images=images, nsfw_content_detected=None)
 
 
 def make_generator(seed: int, device: str = "cpu") -> torch.Generator:

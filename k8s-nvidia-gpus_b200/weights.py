@@ -164,29 +164,31 @@ def num_params(schema: OrderedDict) -> int:
     return sum(math.prod(v[1]) for v in schema.values())
 
 
-def random_state_dict(schema: OrderedDict, seed: int = 0, round_dtype=torch.float16) -> OrderedDict:
-    """torch default-init equivalents (kaiming-uniform(a=sqrt 5) weights, U(+-1/sqrt(fan_in)) biases, N(0,1)
-    embeddings, norm affine 1/0).  Values are rounded to `round_dtype`-representable fp32 (fp16 = the library's
-    default 16-bit type; pass None to keep full fp32) so the fp32 CPU oracle and the 16-bit GPU path hold identical
-    weights."""
-    g = torch.Generator().manual_seed(seed)
+def random_state_dict(schema: OrderedDict, seed: int = 0, round_dtype=torch.float16, device="cpu",
+                      store_dtype=torch.float32) -> OrderedDict:
+    """torch default-init equivalents (kaiming-uniform(a=sqrt 5) weights, U(+-1/sqrt(fan_in)) biases, N(0,1)*0.02
+    embeddings, norm affine 1/0).  Values are rounded to `round_dtype`-representable numbers (fp16 = the library's
+    default 16-bit type; None keeps full fp32) so the fp32 CPU oracle and the 16-bit GPU path hold identical weights.
+    `device="cuda"` draws directly on the GPU (benchmarks: 860 M parameters in a second instead of a minute) and
+    `store_dtype=torch.float16` halves the staging memory; the CPU stream (device="cpu") is the one parity tests use."""
+    g = torch.Generator(device=device).manual_seed(seed)
     sd = OrderedDict()
     for name, spec in schema.items():
         kind, shape = spec[0], spec[1]
         if kind in ("linear", "conv"):
             fan_in = math.prod(shape[1:])
             bound = 1.0 / math.sqrt(fan_in)
-            t = (torch.rand(shape, generator=g) * 2 - 1) * bound
+            t = (torch.rand(shape, generator=g, device=device) * 2 - 1) * bound
         elif kind == "bias":
             bound = 1.0 / math.sqrt(spec[2])
-            t = (torch.rand(shape, generator=g) * 2 - 1) * bound
+            t = (torch.rand(shape, generator=g, device=device) * 2 - 1) * bound
         elif kind == "embed":
-            t = torch.randn(shape, generator=g) * 0.02
+            t = torch.randn(shape, generator=g, device=device) * 0.02
         elif kind == "ones":
-            t = torch.ones(shape)
+            t = torch.ones(shape, device=device)
         else:
-            t = torch.zeros(shape)
+            t = torch.zeros(shape, device=device)
         if round_dtype is not None:
-            t = t.to(round_dtype).to(torch.float32)
-        sd[name] = t
+            t = t.to(round_dtype)
+        sd[name] = t.to(store_dtype)
     return sd

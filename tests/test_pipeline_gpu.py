@@ -45,13 +45,16 @@ def _gens():
 
 def test_text_encoder_parity(tiny):
     cfg, oracle, pipe = tiny
-    ids, ctx, _ = pipe._encode(PROMPTS, [""] * len(PROMPTS))
+    ids = pipe.tokenize(PROMPTS, [""] * len(PROMPTS), True)
+    job = pipe.job(len(PROMPTS), 32, 32, 7.5, True)
+    job.ids_dev.copy_(ids)
+    job.text_plan.run()
     torch.cuda.synchronize()
     ref_ids = oracle.tokenize([""] * len(PROMPTS) + PROMPTS)
-    assert ids.tolist() == ref_ids  # bit-exact tokenisation
+    assert ids.view(-1, 77).tolist() == ref_ids  # bit-exact tokenisation
     with torch.no_grad():
         ref = oracle.text_encoder(torch.tensor(ref_ids, dtype=torch.long))
-    r = _rel(ctx.cpu(), ref)
+    r = _rel(job.ctx.cpu(), ref)
     print("text encoder rel err", r)
     assert r < 1e-2
 
