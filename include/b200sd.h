@@ -124,6 +124,29 @@ typedef struct {
 int b200sd_groupnorm_stats(const b200sd_groupnorm_params* p, b200sd_stream stream);
 int b200sd_groupnorm_apply(const b200sd_groupnorm_params* p, b200sd_stream stream);
 
+/* GroupNorm (+ optional SiLU) in ONE call that needs no scratch from the caller and allocates nothing.
+ * (No counterpart in the reference: it has no C ABI at all; this exists for hosts of this library.)
+ *
+ * Who needs it: a caller that is handed only its input and output buffers and has no way to obtain more device
+ * memory at call time — for example a normalisation hook running inside another runtime's pre-planned memory arena,
+ * or a service pinned to a fixed memory budget (the reference pod runs under a hard memory limit, deployment.yaml:
+ * 59-66) where a cudaMalloc in the request path may fail, and in any case synchronises the whole device.
+ *
+ * Same parameters and same result as b200sd_groupnorm_stats followed by b200sd_groupnorm_apply, except that
+ * p->stats is IGNORED: the per-(image, group) sums are kept in a fixed array inside the library,
+ * B200SD_GN_NOALLOC_MAX_STATS floats (64 KiB) that every GPU which loads the library holds until the process exits.
+ *   - limit: nimg * groups * 2 <= B200SD_GN_NOALLOC_MAX_STATS, otherwise B200SD_ERR_TOO_LARGE is returned and nothing
+ *     is launched (use the two-call form with your own scratch);
+ *   - the array is shared by all calls on a device and still holds the previous call's sums, so each call first
+ *     clears the part it uses (a cudaMemsetAsync on `stream`); two calls whose GPU work overlaps (different streams,
+ *     or several host threads) race on it — serialise them or use the two-call form;
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress, with that device
+ *     current); make that first call before starting any stream capture;
+ *   - no cudaMalloc / cudaFree or other allocating routine is called on any path.
+ */
+#define B200SD_GN_NOALLOC_MAX_STATS 16384
+int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* p, b200sd_stream stream);
+
 /* LayerNorm over the last dim. Replaces nn.LayerNorm in BasicTransformerBlock.norm1-3 / CLIPEncoderLayer (K9). */
 typedef struct {
   const void* x; /* act16 [rows, c] */

@@ -1,6 +1,8 @@
 // Bandwidth-bound normalisation kernels: GroupNorm(+SiLU) over a virtual two-source concat, LayerNorm, row softmax.
 // All statistics are fp32; inputs/outputs act_t, 16-byte vectorised, coalesced along the NHWC channel axis.
 // SURVEY §2.1 K7, K8, K9, K14.
+#include <mutex>
+
 #include "common.cuh"
 #include "host.cuh"
 
@@ -313,6 +315,62 @@ extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_
   B200SD_REQUIRE(C * 2 * sizeof(float) <= 48 * 1024, B200SD_ERR_TOO_LARGE, "groupnorm_apply: C too large");
   dim3 grid(chunks, h.nimg);
   gn_apply_kernel<<<grid, kNormThreads, C * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
+      static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- GroupNorm, no allocation
+// Built-in statistics scratch for b200sd_groupnorm_noalloc: lives in the library image, so every GPU that loads
+// libb200sd.so carries these 64 KiB until the process exits.  The name below is only a device symbol — host code
+// must not treat it as a pointer; the device address is looked up once per device with cudaGetSymbolAddress.
+static __device__ __align__(256) float g_gn_noalloc_scratch[B200SD_GN_NOALLOC_MAX_STATS];
+
+namespace b200sd {
+static std::mutex g_gn_noalloc_mu;
+static float* g_gn_noalloc_ptr[64] = {nullptr};
+
+// Device address of the built-in scratch on the CURRENT device (resolved on first use, then cached per device).
+static int gn_noalloc_scratch(float** out) {
+  int dev = 0;
+  B200SD_CUDA_CHECK(cudaGetDevice(&dev));
+  B200SD_REQUIRE(dev >= 0 && dev < 64, B200SD_ERR_CUDA, "groupnorm_noalloc: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_gn_noalloc_mu);
+  if (g_gn_noalloc_ptr[dev] == nullptr) {
+    float* ptr = nullptr;
+    B200SD_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_gn_noalloc_scratch));
+    B200SD_REQUIRE(ptr != nullptr, B200SD_ERR_CUDA, "groupnorm_noalloc: scratch symbol has no device address");
+    g_gn_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_gn_noalloc_ptr[dev];
+  return B200SD_OK;
+}
+}  // namespace b200sd
+
+extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200sd_stream stream_) {
+  B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: params is NULL");
+  B200SD_REQUIRE(hp->nimg > 0 && hp->groups > 0, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: bad arguments");
+  const long long need = 2ll * hp->nimg * hp->groups;
+  B200SD_REQUIRE(need <= B200SD_GN_NOALLOC_MAX_STATS, B200SD_ERR_TOO_LARGE,
+                 "groupnorm_noalloc: nimg * groups * 2 = %lld statistics exceed the built-in scratch of %d floats "
+                 "(use b200sd_groupnorm_stats/_apply with caller-provided scratch for larger problems)",
+                 need, B200SD_GN_NOALLOC_MAX_STATS);
+  b200sd_groupnorm_params h = *hp;  // same kernels as the two-call path; only the scratch pointer differs
+  if (int e = gn_noalloc_scratch(&h.stats)) return e;
+  int ppc, chunks;
+  if (int e = gn_check(h, &ppc, &chunks)) return e;
+  B200SD_REQUIRE(h.out && h.gamma && h.beta, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: out/gamma/beta required");
+  const int C = h.c0 + h.c1;
+  B200SD_REQUIRE(C * 2 * sizeof(float) <= 48 * 1024, B200SD_ERR_TOO_LARGE, "groupnorm_noalloc: C too large");
+  cudaStream_t s = static_cast<cudaStream_t>(stream_);
+  // the scratch still holds the previous call's sums: the accumulators of this call must start from zero
+  B200SD_CUDA_CHECK(cudaMemsetAsync(h.stats, 0, static_cast<size_t>(need) * sizeof(float), s));
+  dim3 grid(chunks, h.nimg);
+  gn_stats_kernel<<<grid, kNormThreads, h.groups * 2 * sizeof(float), s>>>(
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  gn_apply_kernel<<<grid, kNormThreads, C * 2 * sizeof(float), s>>>(
       static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
       static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());

@@ -14,6 +14,7 @@ _lib = None
 ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU = 0, 1, 2, 3
 ACT16, F32 = 0, 1
 BF16 = ACT16  # historical alias
+GN_NOALLOC_MAX_STATS = 16384  # B200SD_GN_NOALLOC_MAX_STATS
 ST_TIMESTEP, ST_IN_SCALE, ST_KIND, ST_C0, ST_C1, ST_C2, ST_C3, ST_W0, ST_PNDM_MODE, ST_PUSH, ST_WIDTH = (
     0, 1, 2, 3, 4, 5, 6, 7, 11, 12, 16)
 
@@ -101,6 +102,7 @@ ENTRY_POINTS = {
     "b200sd_attention": AttnParams,
     "b200sd_groupnorm_stats": GroupNormParams,
     "b200sd_groupnorm_apply": GroupNormParams,
+    "b200sd_groupnorm_noalloc": GroupNormParams,
     "b200sd_layernorm": LayerNormParams,
     "b200sd_prep_unet_input": PrepParams,
     "b200sd_timestep_embedding": TembParams,
