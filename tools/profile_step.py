@@ -1,0 +1,113 @@
+#!/usr/bin/env python3
+"""Short, graph-free invocations of the hot path for ncu (see /opt/skills/guides/B200_PROFILING.md).
+
+    python tools/profile_step.py step      # SD1.5 batch 8: text + K/V + 2 denoise steps + VAE, eager launches
+    python tools/profile_step.py kernels   # the heaviest individual shapes of the UNet step, one launch each
+
+Timing numbers printed here are CUDA-event times of the plain run; numbers under ncu are never bench values.
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+os.environ["B200SD_NO_GRAPH"] = "1"
+
+import torch  # noqa: E402
+
+
+def mode_step():
+    import b200sd
+    pipe = b200sd.StableDiffusionPipeline.from_pretrained("sd15", scheduler="ddim")
+    job = pipe.job(8, 64, 64, 7.5, True)
+    sched = pipe.make_schedule(25)
+    job.step_table[: sched.num_evals].copy_(sched.table)
+    job.init_latents.normal_()
+    job.reset()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    job.run(2)
+    e1.record()
+    torch.cuda.synchronize()
+    print(f"step mode: text+kv+2 steps+vae = {e0.elapsed_time(e1):.2f} ms, launches {job.launches(2)}")
+
+
+def mode_kernels():
+    import b200sd
+    ops = b200sd.ops
+    dt = b200sd.lib.act_dtype()
+    s = ops.current_stream()
+    n = 16  # CFG-paired batch of 8
+
+    def rnd(*shape, scale=1.0):
+        return (torch.randn(*shape, device="cuda") * scale).to(dt)
+
+    def timed(name, call, flops):
+        call(s)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        call(s)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        print(f"{name:44s} {ms:8.3f} ms  {flops / ms / 1e9:8.1f} TFLOP/s")
+
+    convs = [(64, 320, 320), (32, 640, 640), (16, 1280, 1280), (8, 1280, 1280), (64, 640, 320), (16, 2560, 1280)]
+    for hw, cin, cout in convs:
+        x = rnd(n, hw, hw, cin)
+        w = rnd(cout, 9, cin, scale=(9 * cin) ** -0.5)
+        out = torch.empty(n, hw, hw, cout, device="cuda", dtype=dt)
+        bias = torch.zeros(cout, device="cuda")
+        timed(f"conv3x3 {cin}->{cout} @{hw}x{hw} x{n}",
+              ops.gemm(x, w, out, nimg=n, h=hw, w_=hw, c0=cin, n=cout, ksize=3, bias=bias),
+              2.0 * n * hw * hw * cout * 9 * cin)
+    lins = [(n * 4096, 320, 2560, True), (n * 4096, 1280, 320, False), (n * 1024, 640, 5120, True),
+            (n * 4096, 320, 960, False), (n * 256, 1280, 10240, True)]
+    for m, k, nn, geglu in lins:
+        x = rnd(m, k)
+        w = rnd(nn, 1, k, scale=k ** -0.5)
+        out = torch.empty(m, nn // 2 if geglu else nn, device="cuda", dtype=dt)
+        bias = torch.zeros(nn, device="cuda")
+        timed(f"linear {m}x{k}x{nn}{' geglu' if geglu else ''}",
+              ops.gemm(x, w, out, nimg=1, h=1, w_=m, c0=k, n=nn, bias=bias,
+                       act=b200sd.lib.ACT_GEGLU if geglu else b200sd.lib.ACT_NONE), 2.0 * m * k * nn)
+    for tokens, heads, d in [(4096, 8, 40), (1024, 8, 80), (256, 8, 160)]:
+        c = heads * d
+        qkv = rnd(n, tokens, 3 * c)
+        out = torch.empty(n, tokens, c, device="cuda", dtype=dt)
+        q2 = qkv.view(-1, 3 * c)
+        timed(f"self-attention {tokens} tok d={d} x{n}",
+              ops.attention(q2, q2[:, c:], q2[:, 2 * c:], out, batch=n, heads=heads, nq=tokens, nk=tokens, d=d,
+                            ldq=3 * c, ldk=3 * c, ldv=3 * c, ldo=c, scale=d ** -0.5), 4.0 * n * heads * tokens * tokens * d)
+    kv = rnd(n, 77, 640)
+    q = rnd(n, 4096, 320)
+    out = torch.empty(n, 4096, 320, device="cuda", dtype=dt)
+    kv2 = kv.view(-1, 640)
+    timed("cross-attention 4096x77 d=40", ops.attention(q, kv2, kv2[:, 320:], out, batch=n, heads=8, nq=4096, nk=77,
+                                                        d=40, ldq=320, ldk=640, ldv=640, ldo=320, scale=40 ** -0.5),
+          4.0 * n * 8 * 4096 * 77 * 40)
+    # bandwidth-bound kernels
+    x = rnd(n, 4096, 320)
+    o = torch.empty_like(x)
+    g, b = torch.ones(320, device="cuda"), torch.zeros(320, device="cuda")
+    st = torch.zeros(n, 32, 2, device="cuda")
+    sc, ac = ops.groupnorm(x, o, st, g, b, nimg=n, hw=4096, c0=320, groups=32, eps=1e-5, silu=True)
+    nbytes = x.numel() * 2
+    for name, call, byt in (("groupnorm stats 320@64x64", sc, nbytes), ("groupnorm apply 320@64x64", ac, 2 * nbytes),
+                            ("layernorm 65536x320", ops.layernorm(x, o, g, b, rows=n * 4096, c=320, eps=1e-5),
+                             2 * nbytes)):
+        call(s)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        call(s)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        print(f"{name:44s} {ms:8.3f} ms  {byt / ms / 1e6:8.1f} GB/s")
+
+
+if __name__ == "__main__":
+    {"step": mode_step, "kernels": mode_kernels}[sys.argv[1] if len(sys.argv) > 1 else "kernels"]()
