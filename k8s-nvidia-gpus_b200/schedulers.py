@@ -104,7 +104,7 @@ def make_schedule(kind: str, num_inference_steps: int, *, steps_offset=1, beta_s
 
     if kind == "euler":
         tsf = (np.arange(0, n) * ratio).round()[::-1].copy().astype(np.float32) + steps_offset
-        sig = np.array(((1 - ac) / ac) ** 0.5)
+        sig = (((1 - ac) / ac) ** 0.5).numpy()
         sig = np.interp(tsf, np.arange(0, len(sig)), sig)
         sig = torch.from_numpy(np.concatenate([sig, [0.0]]).astype(np.float32))
         table = torch.zeros(n, W, dtype=torch.float32)

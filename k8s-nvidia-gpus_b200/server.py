@@ -1,0 +1,116 @@
+"""HTTP front end with the reference service's contract (drop-in boundary B2).
+
+Same surface as the FastAPI app embedded in cluster-config/apps/sd15-api/configmap.yaml:16-121:
+  POST /generate  {prompt, steps?=30, guidance_scale?=7.5, seed?, width?=512, height?=512} -> image/png,
+                  header X-Gen-Time "<seconds>.2fs"; 400 "prompt is required" for a blank prompt; falsy optional
+                  fields fall back to the defaults (configmap.yaml:86-121)
+  GET  /healthz   {"ok": true}                                   (configmap.yaml:60-62; the Deployment's readinessProbe)
+  GET  /last      last PNG or 404                                (configmap.yaml:80-84)
+  GET  /          HTML preview of the last image                 (configmap.yaml:64-78)
+Differences, all deliberate: the pipeline is b200sd's; access to it is serialised with a lock (the reference calls its
+stateful pipeline from Starlette's thread pool unguarded, configmap.yaml:105-112); the seed drives a CPU generator —
+the reference's CPU branch (configmap.yaml:92) — so a seed reproduces the oracle's image.
+
+    uvicorn app:app --host 0.0.0.0 --port 8000      # from the repo root, exactly the command of deployment.yaml:42
+                                                    # (env MODEL_ID as in deployment.yaml:45-46)
+"""
+from __future__ import annotations
+
+import base64
+import io
+import logging
+import os
+import time
+from threading import Lock
+
+import torch
+from fastapi import FastAPI, HTTPException
+from fastapi.responses import HTMLResponse, Response
+from pydantic import BaseModel
+
+logger = logging.getLogger("sd15-api")
+
+DEFAULT_STEPS, DEFAULT_GUIDANCE, DEFAULT_SIZE = 30, 7.5, 512
+
+
+class GenReq(BaseModel):
+    prompt: str
+    steps: int | None = DEFAULT_STEPS
+    guidance_scale: float | None = DEFAULT_GUIDANCE
+    seed: int | None = None
+    width: int | None = DEFAULT_SIZE
+    height: int | None = DEFAULT_SIZE
+
+
+def create_app(pipe=None, pipe_factory=None) -> FastAPI:
+    """pipe: an object with the StableDiffusionPipeline call surface; pipe_factory: built lazily on first use."""
+    app = FastAPI(title="SD15 Minimal API (b200sd)")
+    state = {"pipe": pipe, "last": None}
+    last_lock, pipe_lock = Lock(), Lock()
+
+    def get_pipe():
+        if state["pipe"] is None:
+            with pipe_lock:
+                if state["pipe"] is None:
+                    state["pipe"] = (pipe_factory or _default_factory)()
+        return state["pipe"]
+
+    @app.get("/healthz")
+    def healthz():
+        return {"ok": True}
+
+    @app.get("/", response_class=HTMLResponse)
+    def index():
+        if state["last"] is None:
+            return "<h1>SD1.5 GPU API</h1><p>No image generated yet. POST /generate to create one.</p>"
+        b64 = base64.b64encode(state["last"]).decode("ascii")
+        return ("<html><head><title>SD1.5 Demo</title></head><body style='background:#0b0b0f;color:#f0f0f0;"
+                "font-family:sans-serif;'><h1>Latest image</h1>"
+                f"<img src='data:image/png;base64,{b64}' alt='latest image' style='max-width:90vw;height:auto;'/>"
+                "<p>POST <code>/generate</code> with a prompt to update this preview.</p></body></html>")
+
+    @app.get("/last")
+    def last_image():
+        if state["last"] is None:
+            raise HTTPException(404, "No image generated yet")
+        return Response(content=state["last"], media_type="image/png")
+
+    @app.post("/generate")
+    def generate(req: GenReq):
+        if not req.prompt or not req.prompt.strip():
+            raise HTTPException(400, "prompt is required")
+        steps = req.steps or DEFAULT_STEPS
+        gs = req.guidance_scale or DEFAULT_GUIDANCE
+        width, height = req.width or DEFAULT_SIZE, req.height or DEFAULT_SIZE
+        gen = torch.Generator(device="cpu").manual_seed(req.seed) if req.seed is not None else None
+        t0 = time.time()
+        logger.info("Generating prompt='%s' steps=%s guidance=%.2f seed=%s size=%sx%s", req.prompt, steps, gs,
+                    req.seed if req.seed is not None else "auto", width, height)
+        p = get_pipe()
+        with pipe_lock:  # one generation at a time per GPU; pipeline errors surface as 500 like the reference's
+            image = p(req.prompt, num_inference_steps=steps, guidance_scale=gs, width=width, height=height,
+                      generator=gen).images[0]
+        buf = io.BytesIO()
+        image.save(buf, format="PNG")
+        png = buf.getvalue()
+        latency = time.time() - t0
+        logger.info("Completed generation in %.2fs", latency)
+        with last_lock:
+            state["last"] = png
+        return Response(content=png, media_type="image/png", headers={"X-Gen-Time": f"{latency:.2f}s"})
+
+    return app
+
+
+def _default_factory():
+    from .pipeline import StableDiffusionPipeline
+    model_id = os.getenv("MODEL_ID", "runwayml/stable-diffusion-v1-5")
+    pipe = StableDiffusionPipeline.from_pretrained(model_id)
+    pipe.enable_attention_slicing()
+    pipe.enable_vae_slicing()
+    logger.info("Loaded %s on CUDA (b200sd)", model_id)
+    return pipe
+
+
+logging.basicConfig(level=logging.INFO)
+app = create_app()

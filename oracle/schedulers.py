@@ -119,7 +119,7 @@ class EulerDiscreteScheduler:
         self.num_inference_steps = n
         ratio = self.n_train // n
         ts = (np.arange(0, n) * ratio).round()[::-1].copy().astype(np.float32) + self.steps_offset
-        sig = np.array(((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5)
+        sig = (((1 - self.alphas_cumprod) / self.alphas_cumprod) ** 0.5).numpy()
         sig = np.interp(ts, np.arange(0, len(sig)), sig)
         sig = np.concatenate([sig, [0.0]]).astype(np.float32)
         self.sigmas = torch.from_numpy(sig)

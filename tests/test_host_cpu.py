@@ -1,0 +1,248 @@
+"""CPU tests (no GPU) of the host side: the C-ABI library loads and exports every symbol include/b200sd.h declares (no
+compute calls), ctypes mirrors match the C structs, weight packing, the CLI / HTTP boundaries (B1/B2) with a fake
+pipeline, and the multi-GPU sharding logic on world_size-2 gloo."""
+import ctypes
+import io
+import json
+import os
+import re
+import socket
+import subprocess
+import sys
+import threading
+from http.server import BaseHTTPRequestHandler, HTTPServer
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+# ------------------------------------------------------------------------------------------------ C ABI
+def test_library_exports_every_declared_symbol(b200sd):
+    lib = b200sd.lib.load()          # loads without a GPU; raises if the .so is missing (no fallback)
+    header = (ROOT / "include" / "b200sd.h").read_text()
+    declared = set(re.findall(r"\b(b200sd_[a-z0-9_]+)\s*\(", header)) - {"b200sd_stream"}
+    assert len(declared) >= 20
+    nm = subprocess.run(["nm", "-D", "--defined-only", str(b200sd.lib.lib_path())], capture_output=True, text=True).stdout
+    exported = set(re.findall(r"\bT (b200sd_[a-z0-9_]+)", nm))
+    assert declared <= exported, declared - exported
+    assert declared == set(b200sd.lib.ENTRY_POINTS), declared ^ set(b200sd.lib.ENTRY_POINTS)
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert lib.b200sd_version() >= 100
+    assert lib.b200sd_act_dtype() in (0, 1)
+
+
+def test_ctypes_mirrors_match_c_structs(b200sd):
+    assert b200sd.lib.struct_sizes() == [ctypes.sizeof(s) for s in b200sd.lib.STRUCTS]
+
+
+def test_no_gpu_means_loud_failure(b200sd):
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(b200sd.lib.B200SDError):
+        b200sd.lib.device_info()                      # CUDA error surfaces, nothing falls back
+    W = b200sd.weights
+    cfg = W.load_config("tiny")
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        b200sd.StableDiffusionPipeline(cfg, {}, {}, {})
+
+
+def test_product_never_imports_the_oracle():
+    for p in (ROOT / "k8s-nvidia-gpus_b200").glob("*.py"):
+        src = p.read_text()
+        assert "import oracle" not in src and "from oracle" not in src, p
+    for p in (ROOT / "scripts").glob("*.py"):
+        assert "oracle" not in p.read_text(), p
+
+
+# ------------------------------------------------------------------------------------------------ weight packing
+def test_weight_packing_layouts(b200sd):
+    ops = b200sd.ops
+    w = torch.arange(2 * 6 * 3 * 3, dtype=torch.float32).reshape(2, 6, 3, 3) / 64
+    p = ops.pack_conv_weight(w, (4, 2)).float()
+    assert p.shape == (2, 9, 128)
+    assert torch.equal(p[:, :, :4], w.permute(0, 2, 3, 1).reshape(2, 9, 6)[:, :, :4])
+    assert torch.equal(p[:, :, 64:66], w.permute(0, 2, 3, 1).reshape(2, 9, 6)[:, :, 4:])
+    assert p[:, :, 4:64].abs().sum() == 0 and p[:, :, 66:].abs().sum() == 0
+    perm = ops.geglu_perm(128)
+    assert perm[:32].tolist() == list(range(32)) and perm[32:64].tolist() == list(range(64, 96))
+    assert sorted(perm.tolist()) == list(range(128))
+
+
+def test_bn_independent_flop_model(b200sd):
+    """bench.py's algorithmic-FLOP model over a built plan equals SURVEY's 803.27 GF/sample (needs no GPU: counts only)."""
+    sys.path.insert(0, str(ROOT))
+    import bench
+    p = b200sd.lib.GemmParams()
+    p.nimg, p.h, p.w_, p.c0, p.c1, p.n, p.ksize = 16, 64, 64, 320, 0, 320, 3
+
+    class C_:
+        name, params = "b200sd_gemm", p
+    fl, kind = bench.flops_of_call(C_)
+    assert kind == "gemm" and fl == 2.0 * 16 * 4096 * 320 * 9 * 320
+
+
+# ------------------------------------------------------------------------------------------------ fake pipeline
+class FakePipe:
+    """Stands in for the GPU pipeline in boundary tests: deterministic image from (prompt, seed)."""
+    device = torch.device("cpu")
+
+    def __init__(self):
+        self.calls = []
+
+    def __call__(self, prompt, num_inference_steps=50, guidance_scale=7.5, width=512, height=512, generator=None,
+                 output_type="pil", **kw):
+        prompts = [prompt] if isinstance(prompt, str) else list(prompt)
+        gens = generator if isinstance(generator, (list, tuple)) else [generator] * len(prompts)
+        self.calls.append(dict(prompts=prompts, steps=num_inference_steps, gs=guidance_scale, w=width, h=height))
+        imgs = []
+        for p_, g in zip(prompts, gens):
+            seed = int(torch.randint(0, 256, (1,), generator=g).item()) if g is not None else 7
+            imgs.append(np.full((height, width, 3), (len(p_) * 3 + seed) % 256, dtype=np.uint8))
+        arr = np.stack(imgs)
+        if output_type == "u8":
+            images = arr
+        else:
+            from PIL import Image
+            images = [Image.fromarray(a) for a in arr]
+        return type("Out", (), {"images": images})()
+
+
+# ------------------------------------------------------------------------------------------------ B2: HTTP server
+def test_http_contract_matches_reference(b200sd):
+    from fastapi.testclient import TestClient
+    import importlib
+    server = importlib.import_module("k8s-nvidia-gpus_b200.server")
+    fake = FakePipe()
+    c = TestClient(server.create_app(pipe=fake))
+    assert c.get("/healthz").json() == {"ok": True}
+    assert c.get("/last").status_code == 404
+    assert "No image generated yet" in c.get("/").text
+    r = c.post("/generate", json={"prompt": "   "})
+    assert r.status_code == 400 and r.json()["detail"] == "prompt is required"
+    assert c.post("/generate", json={}).status_code == 422                      # prompt is a required field
+    r = c.post("/generate", json={"prompt": "a panda", "steps": 0, "guidance_scale": 0.0, "seed": 3, "width": 64,
+                                  "height": 64})
+    assert r.status_code == 200 and r.headers["content-type"] == "image/png"
+    assert re.fullmatch(r"\d+\.\d\ds", r.headers["X-Gen-Time"])
+    assert r.content[:8] == b"\x89PNG\r\n\x1a\n"
+    assert fake.calls[-1]["steps"] == 30 and fake.calls[-1]["gs"] == 7.5      # falsy -> defaults (configmap.yaml:107-110)
+    assert fake.calls[-1]["w"] == 64 and fake.calls[-1]["h"] == 64
+    r2 = c.post("/generate", json={"prompt": "a panda", "steps": 25})
+    assert fake.calls[-1]["w"] == 512 and fake.calls[-1]["steps"] == 25
+    assert c.get("/last").content == r2.content
+    assert "data:image/png;base64," in c.get("/").text
+
+
+# ------------------------------------------------------------------------------------------------ B1: CLI
+class _Stub(BaseHTTPRequestHandler):
+    bodies = []
+
+    def do_POST(self):
+        n = int(self.headers["Content-Length"])
+        _Stub.bodies.append((self.headers["Content-Type"], json.loads(self.rfile.read(n))))
+        self.send_response(200)
+        self.send_header("Content-Type", "image/png")
+        self.send_header("X-Gen-Time", "1.23s")
+        self.end_headers()
+        self.wfile.write(b"\x89PNG fake")
+
+    def log_message(self, *a):
+        pass
+
+
+def _load_cli():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("batch_generate_cli", ROOT / "scripts" / "batch_generate.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_cli_http_mode_is_wire_compatible(tmp_path, capsys):
+    cli = _load_cli()
+    _Stub.bodies.clear()
+    srv = HTTPServer(("127.0.0.1", 0), _Stub)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    try:
+        rc = cli.main(["a panda on a motorbike", "3", "panda", str(tmp_path / "out"), "--steps", "25", "--url",
+                       f"http://127.0.0.1:{srv.server_port}/generate"])
+    finally:
+        srv.shutdown()
+    assert rc == 0
+    assert [b for _, b in _Stub.bodies] == [{"prompt": "a panda on a motorbike", "steps": 25}] * 3
+    assert all(ct == "application/json" for ct, _ in _Stub.bodies)
+    assert sorted(p.name for p in (tmp_path / "out").iterdir()) == ["panda_01.png", "panda_02.png", "panda_03.png"]
+    out = capsys.readouterr().out
+    assert "[*] Generating panda_01.png -> " in out and "✔ done in 1.23ss" in out and "All done. Images saved under" in out
+
+
+def test_cli_defaults_and_failure_keeps_going(tmp_path, capsys):
+    cli = _load_cli()
+    a = cli.build_parser().parse_args(["p", "2", "x"])
+    assert (a.steps, a.url, a.delay, a.out_dir) == (40, "http://192.168.0.176:30800/generate", 0, "outputs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()                                                     # nothing listens: every request fails
+    rc = cli.main(["p", "2", "x", str(tmp_path), "--url", f"http://127.0.0.1:{port}/generate"])
+    out = capsys.readouterr().out
+    assert rc == 0 and out.count("✖ Request failed") == 2 and "Generation loop finished" in out
+
+
+def test_cli_local_mode_batches_and_seeds(tmp_path, capsys):
+    cli = _load_cli()
+    fake = FakePipe()
+    cli.generate_local(["a", "bb"], 4, tmp_path, "img", 5, batch_size=2, seed=100, guidance_scale=7.5, width=64,
+                       height=64, scheduler="ddim", model="tiny", pipe=fake)
+    assert [c["prompts"] for c in fake.calls] == [["a", "bb"], ["a", "bb"], ["a"]]
+    assert sorted(p.name for p in tmp_path.iterdir()) == [f"img_{i:02d}.png" for i in range(1, 6)]
+
+
+# ------------------------------------------------------------------------------------------------ multi-GPU logic
+def test_shard_ranges(b200sd):
+    import importlib
+    D = importlib.import_module("k8s-nvidia-gpus_b200.dist")
+    for n in (0, 1, 7, 8, 64, 65):
+        for w in (1, 2, 4, 8):
+            spans = [D.shard_range(n, w, r) for r in range(w)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = D.shard_sizes(n, w)
+            assert max(sizes) - min(sizes) <= 1 and sizes == sorted(sizes, reverse=True)
+
+
+def _gloo_worker(rank, world, port, n_prompts, out_dir):
+    import importlib
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    sys.path.insert(0, str(ROOT))
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    D = importlib.import_module("k8s-nvidia-gpus_b200.dist")
+    prompts = [f"prompt {'x' * i}" for i in range(n_prompts)]
+    imgs = D.generate_sharded(FakePipe(), prompts, base_seed=1234, max_batch=2, num_inference_steps=2, width=16,
+                              height=16)
+    np.save(os.path.join(out_dir, f"r{rank}.npy"), imgs.numpy())
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_prompts", [5, 1])
+def test_sharded_generation_is_world_size_invariant(tmp_path, n_prompts):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_gloo_worker, args=(2, port, n_prompts, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = np.load(tmp_path / "r0.npy"), np.load(tmp_path / "r1.npy")
+    assert r0.shape == (n_prompts, 16, 16, 3) and np.array_equal(r0, r1)
+    # single-process result (world 1) is identical: per-image seed = base + global index
+    import importlib
+    D = importlib.import_module("k8s-nvidia-gpus_b200.dist")
+    prompts = [f"prompt {'x' * i}" for i in range(n_prompts)]
+    one = D.generate_sharded(FakePipe(), prompts, base_seed=1234, max_batch=2, num_inference_steps=2, width=16, height=16)
+    assert np.array_equal(one.numpy(), r0)
