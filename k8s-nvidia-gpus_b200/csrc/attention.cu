@@ -1,38 +1,43 @@
 // Flash attention forward on tcgen05 (sm_100a): out = softmax(Q K^T * scale [+ causal]) V per (batch, head).
 // SURVEY §2.1 K5 (self-attention), K6 (cross-attention, nk = 77), K15 (CLIP causal attention).
 //
-// One CTA per (128-query tile, head, batch):
+// One CTA per (up to two 128-query tiles, head, batch); 12 warps:
 //   warp 0 (1 thread) : TMA producer.  Q/K/V are read straight out of the projection GEMM outputs through 4-D
 //                       tensor maps {d, head, token, batch}; the box is 64 wide in d, so head dims that are not a
 //                       multiple of 64 (40, 80, 160) and ragged token counts are zero-filled by the TMA unit —
-//                       no padded copies of Q/K/V exist in HBM.
-//   warp 1 (1 thread) : tcgen05.mma issuer.  S = Q K^T (K-major A and B) into TMEM columns [0,128);
-//                       O += P V with P (act_t, written by the softmax warps) as the K-major A operand in shared
-//                       memory and V consumed in place as an MN-major B operand; O lives in TMEM columns [128, ...).
+//                       no padded copies of Q/K/V exist in HBM.  K/V tiles are shared by both query tiles.
+//   warp 1 (1 thread) : tcgen05.mma issuer.  S_t = Q_t K^T (K-major A and B) into TMEM; O_t += P_t V with P_t
+//                       (16-bit, written by softmax warpgroup t) as the K-major A operand in shared memory and V
+//                       consumed in place as an MN-major B operand.  S_t(j+1) is issued as soon as warpgroup t has
+//                       consumed S_t(j), before P_t(j) V(j), so the two warpgroups and the tensor pipe ping-pong.
 //   warp 2            : TMEM allocator.
-//   warps 4..7        : online softmax (thread = query row): tcgen05.ld S, running max / sum in fp32 registers,
-//                       exp2 with the scale folded in, P -> swizzled shared memory, lazy rescale of O in TMEM,
-//                       final normalisation and act_t store.
-// S_{j+1} is issued before P_j V_j so the tensor pipe computes the next scores while the softmax warps work.
+//   warps 4..7 / 8..11: softmax warpgroup 0 / 1 (thread = query row).  Pass 1: tcgen05.ld S -> row max.  Pass 2:
+//                       tcgen05.ld S again -> exp2 (packed ex2.f16x2 in the fp16 build; the result IS the packed P)
+//                       -> swizzled shared memory.  Lazy rescale of O in TMEM; final normalisation and store.
+//   Row sums: when the head dim leaves a spare UMMA column (d = 40 -> N = 48) column d of every V tile is set to
+//   1.0 after the TMA lands, so the tensor pipe accumulates sum_j P_ij in fp32 as column d of O for free (and it is
+//   rescaled together with O); otherwise the sum is accumulated in registers.
 #include "common.cuh"
 #include "host.cuh"
 
 namespace b200sd {
 
-static constexpr int kAttThreads = 256;
-static constexpr int kBQ = 128;   // query rows per CTA (UMMA M)
+static constexpr int kAttThreads = 384;
+static constexpr int kBQ = 128;   // query rows per tile (UMMA M)
 static constexpr int kBKV = 128;  // keys per tile
-static constexpr uint32_t kAtomBytes = 128 * 128;  // 128 rows x 64 act_t, one swizzle-128B atom column
+static constexpr uint32_t kAtomBytes = 128 * 128;  // 128 rows x 64 elements, one swizzle-128B atom column
 
 struct alignas(64) AttnDev {
   CUtensorMap tmQ, tmK, tmV;
   act_t* out;
   int batch, heads, nq, nk, d;
   int ldo;
-  int nd;      // 64-wide d atoms
-  int dN;      // d rounded up to 16 (UMMA N of the PV product, K extent of QK^T)
-  int stages;  // K/V ring depth (1 or 2)
+  int nd;         // 64-wide d atoms
+  int dN;         // UMMA N of the PV product / K extent of QK^T (d rounded up to 16)
+  int stages;     // K/V ring depth (1 or 2)
+  int qtiles;     // query tiles per CTA (1 or 2)
   int tmem_cols;
+  int sum_col;    // >= 0: column of O that accumulates the row sums (ones column in V); -1: register sums
   int causal;
   float scale_log2;
 };
@@ -43,24 +48,47 @@ __device__ __forceinline__ float ex2f(float x) {
   return y;
 }
 
-__global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_constant__ AttnDev p) {
+// p = 2^(s * scale - mb) for two scores, packed as two act_t (the P operand layout); adds p0 + p1 to `sum` when asked
+template <bool kSum>
+__device__ __forceinline__ uint32_t exp2_pack(float s0, float s1, float scale, float mb, float& sum) {
+  const float x0 = fmaf(s0, scale, -mb), x1 = fmaf(s1, scale, -mb);
+#ifdef B200SD_ACT_BF16
+  const float p0 = ex2f(x0), p1 = ex2f(x1);
+  if (kSum) sum += p0 + p1;
+  return pack_act2(p0, p1);
+#else
+  uint32_t xh, ph;
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(xh) : "f"(x1), "f"(x0));
+  asm("ex2.approx.f16x2 %0, %1;" : "=r"(ph) : "r"(xh));
+  if (kSum) {
+    const float2 pf = unpack_act2(ph);
+    sum += pf.x + pf.y;
+  }
+  return ph;
+#endif
+}
+
+template <bool kOnes>
+__global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_constant__ AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t q_full, s_full, p_full, pv_done;
+  __shared__ __align__(8) uint64_t q_full;
+  __shared__ __align__(8) uint64_t s_full[2], p_full[2], pv_done[2];
   __shared__ __align__(8) uint64_t k_full[2], v_full[2], k_empty[2], v_empty[2];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * kBQ;
+  const int q0 = blockIdx.x * kBQ * p.qtiles;
   const int head = blockIdx.y;
   const int b = blockIdx.z;
+  const int ntiles = (p.qtiles == 2 && q0 + kBQ < p.nq) ? 2 : 1;  // query tiles this CTA really has
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t tile_bytes = p.nd * kAtomBytes;
-  const uint32_t sQ = base;
-  const uint32_t sK = sQ + tile_bytes;
-  const uint32_t sV = sK + p.stages * tile_bytes;
-  const uint32_t sP = sV + p.stages * tile_bytes;
+  const uint32_t sQ = base;                                   // [qtiles][nd atoms]
+  const uint32_t sK = sQ + p.qtiles * tile_bytes;             // [stages][nd atoms]
+  const uint32_t sV = sK + p.stages * tile_bytes;             // [stages][nd atoms]
+  const uint32_t sP = sV + p.stages * tile_bytes;             // [qtiles][2 atoms]
   int kv_end = p.nk;
-  if (p.causal) kv_end = min(p.nk, q0 + kBQ);  // keys beyond the last query row of this tile are fully masked
+  if (p.causal) kv_end = min(p.nk, q0 + kBQ * ntiles);  // keys beyond the last query row are fully masked
   const int T = (kv_end + kBKV - 1) / kBKV;
 
   if (warp == 0 && lane == 0) {
@@ -70,10 +98,10 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
   }
   if (warp == 1 && lane == 0) {
     mbar_init(smem_u32(&q_full), 1);
-    mbar_init(smem_u32(&s_full), 1);
-    mbar_init(smem_u32(&p_full), 128);
-    mbar_init(smem_u32(&pv_done), 1);
     for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&s_full[s]), 1);
+      mbar_init(smem_u32(&p_full[s]), 128);
+      mbar_init(smem_u32(&pv_done[s]), 1);
       mbar_init(smem_u32(&k_full[s]), 1);
       mbar_init(smem_u32(&v_full[s]), 1);
       mbar_init(smem_u32(&k_empty[s]), 1);
@@ -86,14 +114,16 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
-  const uint32_t tS = tmem_base;        // 128 fp32 columns
-  const uint32_t tO = tmem_base + 128;  // dN fp32 columns
+  // TMEM columns: S_t at t*128; O_t after the S block(s)
+  const uint32_t tO_base = tmem_base + p.qtiles * 128;
 
   if (warp == 0) {
     if (lane == 0) {
       // ---------------------------------------------------------------- TMA producer
-      mbar_arrive_expect_tx(smem_u32(&q_full), tile_bytes);
-      for (int a = 0; a < p.nd; ++a) tma_load_4d(sQ + a * kAtomBytes, &p.tmQ, smem_u32(&q_full), a * 64, head, q0, b);
+      mbar_arrive_expect_tx(smem_u32(&q_full), ntiles * tile_bytes);
+      for (int t = 0; t < ntiles; ++t)
+        for (int a = 0; a < p.nd; ++a)
+          tma_load_4d(sQ + t * tile_bytes + a * kAtomBytes, &p.tmQ, smem_u32(&q_full), a * 64, head, q0 + t * kBQ, b);
       for (int j = 0; j < T; ++j) {
         const int st = j % p.stages;
         const uint32_t ph = ((j / p.stages) & 1) ^ 1u;
@@ -113,128 +143,196 @@ __global__ void __launch_bounds__(kAttThreads) attention_kernel(const __grid_con
       const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 128] = Q (K-major) x K (K-major)
       const uint32_t idesc_o = make_idesc_f16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
       const int ksteps_s = p.dN / 16;
-      auto issue_s = [&](int j) {
+      auto issue_s = [&](int t, int j) {  // caller has waited for K_j
         const int st = j % p.stages;
-        mbar_wait(smem_u32(&k_full[st]), (j / p.stages) & 1);
-        tc_fence_after();
         for (int s = 0; s < ksteps_s; ++s) {
           const uint32_t off = (s >> 2) * kAtomBytes + (s & 3) * 32;
-          const uint64_t adesc = make_smem_desc_sw128(sQ + off, 16, 1024);
+          const uint64_t adesc = make_smem_desc_sw128(sQ + t * tile_bytes + off, 16, 1024);
           const uint64_t bdesc = make_smem_desc_sw128(sK + st * tile_bytes + off, 16, 1024);
-          umma_f16_ss(tS, adesc, bdesc, idesc_s, s != 0);
+          umma_f16_ss(tmem_base + t * 128, adesc, bdesc, idesc_s, s != 0);
         }
-        umma_commit(smem_u32(&k_empty[st]));
-        umma_commit(smem_u32(&s_full));
+        umma_commit(smem_u32(&s_full[t]));
       };
       mbar_wait(smem_u32(&q_full), 0);
-      issue_s(0);
+      mbar_wait(smem_u32(&k_full[0]), 0);
+      tc_fence_after();
+      for (int t = 0; t < ntiles; ++t) issue_s(t, 0);
+      umma_commit(smem_u32(&k_empty[0]));
       for (int j = 0; j < T; ++j) {
         const int st = j % p.stages;
-        mbar_wait(smem_u32(&p_full), j & 1);  // S_j consumed, P_j in smem, O rescaled
-        tc_fence_after();
-        if (j + 1 < T) issue_s(j + 1);
-        mbar_wait(smem_u32(&v_full[st]), (j / p.stages) & 1);
-        tc_fence_after();
+        for (int t = 0; t < ntiles; ++t) {
+          mbar_wait(smem_u32(&p_full[t]), j & 1);  // S_t(j) consumed, P_t(j) in smem, O_t rescaled
+          tc_fence_after();
+          if (j + 1 < T) {
+            if (t == 0) {
+              mbar_wait(smem_u32(&k_full[(j + 1) % p.stages]), ((j + 1) / p.stages) & 1);
+              tc_fence_after();
+            }
+            issue_s(t, j + 1);
+            if (t == ntiles - 1) umma_commit(smem_u32(&k_empty[(j + 1) % p.stages]));
+          }
+          if (t == 0) {
+            mbar_wait(smem_u32(&v_full[st]), (j / p.stages) & 1);
+            tc_fence_after();
+          }
 #pragma unroll
-        for (int s = 0; s < kBKV / 16; ++s) {
-          const uint64_t adesc = make_smem_desc_sw128(sP + (s >> 2) * kAtomBytes + (s & 3) * 32, 16, 1024);
-          // V tile: [kv rows at 128 B pitch][64 d per atom]; 16 kv rows per step = 2048 B; atoms kAtomBytes apart
-          const uint64_t bdesc = make_smem_desc_sw128(sV + st * tile_bytes + s * 2048, kAtomBytes, 1024);
-          umma_f16_ss(tO, adesc, bdesc, idesc_o, (j | s) != 0);
+          for (int s = 0; s < kBKV / 16; ++s) {
+            const uint64_t adesc =
+                make_smem_desc_sw128(sP + t * 2 * kAtomBytes + (s >> 2) * kAtomBytes + (s & 3) * 32, 16, 1024);
+            // V tile: [kv rows at 128 B pitch][64 d per atom]; 16 kv rows per step = 2048 B; atoms kAtomBytes apart
+            const uint64_t bdesc = make_smem_desc_sw128(sV + st * tile_bytes + s * 2048, kAtomBytes, 1024);
+            umma_f16_ss(tO_base + t * 128, adesc, bdesc, idesc_o, (j | s) != 0);
+          }
+          if (t == ntiles - 1) umma_commit(smem_u32(&v_empty[st]));
+          umma_commit(smem_u32(&pv_done[t]));
         }
-        umma_commit(smem_u32(&v_empty[st]));
-        umma_commit(smem_u32(&pv_done));
       }
     }
   } else if (warp >= 4) {
     // ------------------------------------------------------------------ softmax / correction / epilogue
-    const int qd = warp & 3;
-    const int r = qd * 32 + lane;  // row in tile == TMEM lane
-    const int qrow = q0 + r;
-    const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
-    float m_run = -INFINITY;
-    float l_run = 0.f;
-    for (int j = 0; j < T; ++j) {
-      mbar_wait(smem_u32(&s_full), j & 1);
-      tc_fence_after();
-      uint32_t sv[4][32];
-#pragma unroll
-      for (int c = 0; c < 4; ++c) tmem_ld32(tS + lane_off + c * 32, sv[c]);
-      tmem_ld_wait();
-      // mask + tile max
-      const int col0 = j * kBKV;
-      int limit = p.nk - col0;                                   // valid columns: [0, limit)
-      if (p.causal) limit = min(limit, qrow - col0 + 1);
-      float mx = -INFINITY;
-#pragma unroll
-      for (int c = 0; c < 4; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(sv[c][i]);
-          s = (c * 32 + i < limit) ? s : -INFINITY;
-          sv[c][i] = __float_as_uint(s);
-          mx = fmaxf(mx, s);
-        }
-      const float m_new = fmaxf(m_run, mx);
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = ex2f((m_run - m_use) * p.scale_log2);  // m_run = -inf -> 0
-      const float mb = m_use * p.scale_log2;
-      float psum = 0.f;
-      // P_{j-1} V_{j-1} must have completed before P smem is overwritten / O is rescaled
-      if (j > 0) {
-        mbar_wait(smem_u32(&pv_done), (j - 1) & 1);
+    const int t = (warp - 4) >> 2;  // warpgroup = query tile
+    if (t < ntiles) {
+      const int qd = warp & 3;
+      const int r = qd * 32 + lane;  // row in tile == TMEM lane
+      const int qrow = q0 + t * kBQ + r;
+      const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
+      const uint32_t tS = tmem_base + t * 128 + lane_off;
+      const uint32_t tO = tO_base + t * 128 + lane_off;
+      const uint32_t sPt = sP + t * 2 * kAtomBytes + r * 128;
+      constexpr bool ones_col = kOnes;
+      float m_run = -INFINITY;
+      float l_run = 0.f;
+      for (int j = 0; j < T; ++j) {
+        const int col0 = j * kBKV;
+        int limit = p.nk - col0;  // valid columns: [0, limit)
+        if (p.causal) limit = min(limit, qrow - col0 + 1);
+        const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
+        mbar_wait(smem_u32(&s_full[t]), j & 1);
         tc_fence_after();
-      }
-#pragma unroll
-      for (int c16 = 0; c16 < 16; ++c16) {
-        float pv[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float s = __uint_as_float(sv[c16 >> 2][(c16 & 3) * 8 + e]);
-          pv[e] = ex2f(fmaf(s, p.scale_log2, -mb));
-          psum += pv[e];
-        }
-        const uint32_t addr = sP + (c16 >> 3) * kAtomBytes + r * 128 + (((c16 & 7) ^ (r & 7)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(pack_act2(pv[0], pv[1])),
-                     "r"(pack_act2(pv[2], pv[3])), "r"(pack_act2(pv[4], pv[5])), "r"(pack_act2(pv[6], pv[7]))
-                     : "memory");
-      }
-      l_run = l_run * alpha + psum;
-      m_run = m_new;
-      if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
-        for (int c = 0; c < p.dN; c += 16) {
-          uint32_t o[16];
-          tmem_ld16(tO + lane_off + c, o);
+        // ---- pass 1: row max (next chunk's tcgen05.ld is in flight while the current one is reduced)
+        float mx = -INFINITY;
+        {
+          uint32_t sv[2][32];
+          tmem_ld32(tS, sv[0]);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tmem_st16(tO + lane_off + c, o);
-        }
-        tmem_st_wait();
-      }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(smem_u32(&p_full));
-    }
-    // final: O / l -> act_t -> global
-    mbar_wait(smem_u32(&pv_done), (T - 1) & 1);
-    tc_fence_after();
-    const float inv_l = 1.f / l_run;
-    act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
-    for (int c = 0; c < p.dN; c += 16) {
-      uint32_t o[16];
-      tmem_ld16(tO + lane_off + c, o);
-      tmem_ld_wait();
-      if (qrow < p.nq) {
+          for (int c = 0; c < 4; ++c) {
+            if (c < 3) tmem_ld32(tS + (c + 1) * 32, sv[(c + 1) & 1]);
+            const uint32_t(&cur)[32] = sv[c & 1];
+            if (need_mask) {
 #pragma unroll
-        for (int h8 = 0; h8 < 2; ++h8) {
-          if (c + h8 * 8 < p.d) {  // d is a multiple of 8
-            uint4 u;
-            u.x = pack_act2(__uint_as_float(o[h8 * 8 + 0]) * inv_l, __uint_as_float(o[h8 * 8 + 1]) * inv_l);
-            u.y = pack_act2(__uint_as_float(o[h8 * 8 + 2]) * inv_l, __uint_as_float(o[h8 * 8 + 3]) * inv_l);
-            u.z = pack_act2(__uint_as_float(o[h8 * 8 + 4]) * inv_l, __uint_as_float(o[h8 * 8 + 5]) * inv_l);
-            u.w = pack_act2(__uint_as_float(o[h8 * 8 + 6]) * inv_l, __uint_as_float(o[h8 * 8 + 7]) * inv_l);
-            *reinterpret_cast<uint4*>(orow + c + h8 * 8) = u;
+              for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < limit) ? __uint_as_float(cur[i]) : -INFINITY);
+            } else {
+              float m0 = mx, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                m0 = fmaxf(m0, __uint_as_float(cur[i]));
+                m1 = fmaxf(m1, __uint_as_float(cur[i + 1]));
+                m2 = fmaxf(m2, __uint_as_float(cur[i + 2]));
+                m3 = fmaxf(m3, __uint_as_float(cur[i + 3]));
+              }
+              mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+            }
+            if (c < 3) tmem_ld_wait();
+          }
+        }
+        const float m_new = fmaxf(m_run, mx);
+        const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+        const float alpha = ex2f((m_run - m_use) * p.scale_log2);  // m_run = -inf -> 0
+        const float mb = m_use * p.scale_log2;
+        m_run = m_new;
+        // P_t(j-1) V(j-1) must have completed before P smem is overwritten / O is rescaled
+        if (j > 0) {
+          mbar_wait(smem_u32(&pv_done[t]), (j - 1) & 1);
+          tc_fence_after();
+        }
+        // ---- pass 2: exponentials -> P (packed 16-bit) -> swizzled smem (TMEM loads pipelined as in pass 1)
+        float psum = 0.f;
+        {
+          uint32_t sv[2][32];
+          tmem_ld32(tS, sv[0]);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (c < 3) tmem_ld32(tS + (c + 1) * 32, sv[(c + 1) & 1]);
+            uint32_t(&cur)[32] = sv[c & 1];
+            if (need_mask) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (c * 32 + i >= limit) cur[i] = __float_as_uint(-INFINITY);
+            }
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte chunk
+              uint32_t w[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                w[e] = exp2_pack<!ones_col>(__uint_as_float(cur[g * 8 + 2 * e]), __uint_as_float(cur[g * 8 + 2 * e + 1]),
+                                            p.scale_log2, mb, psum);
+              const int c16 = c * 4 + g;
+              const uint32_t addr = sPt + (c16 >> 3) * kAtomBytes + (((c16 & 7) ^ (r & 7)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                           "r"(w[3])
+                           : "memory");
+            }
+            if (c < 3) tmem_ld_wait();
+          }
+        }
+        l_run = l_run * alpha + psum;
+        if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
+          for (int c = 0; c < p.dN; c += 16) {
+            uint32_t o[16];
+            tmem_ld16(tO + c, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st16(tO + c, o);
+          }
+          tmem_st_wait();
+        }
+        if (ones_col && t == 0) {
+          // V(j) has landed: set column `sum_col` of kv row r to 1.0 so O[:, sum_col] accumulates the row sums
+          const int st = j % p.stages;
+          mbar_wait(smem_u32(&v_full[st]), (j / p.stages) & 1);
+          const int sc = p.sum_col;
+          const uint32_t va = sV + st * tile_bytes + (sc >> 6) * kAtomBytes + r * 128 +
+                              (((((sc & 63) >> 3)) ^ (r & 7)) << 4) + (sc & 7) * 2;
+          const act_t one = to_act(1.f);
+          asm volatile("st.shared.b16 [%0], %1;" ::"r"(va), "h"(*reinterpret_cast<const uint16_t*>(&one)) : "memory");
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(smem_u32(&p_full[t]));
+      }
+      // final: O / l -> 16-bit -> global
+      mbar_wait(smem_u32(&pv_done[t]), (T - 1) & 1);
+      tc_fence_after();
+      act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
+      float inv_l = 1.f / l_run;
+      if (ones_col) {
+        uint32_t o[16];
+        tmem_ld16(tO + (p.sum_col & ~15), o);
+        tmem_ld_wait();
+        float l = 0.f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (i == (p.sum_col & 15)) l = __uint_as_float(o[i]);
+        inv_l = 1.f / l;
+      }
+      for (int c = 0; c < p.dN; c += 16) {
+        uint32_t o[16];
+        tmem_ld16(tO + c, o);
+        tmem_ld_wait();
+        if (qrow < p.nq) {
+#pragma unroll
+          for (int h8 = 0; h8 < 2; ++h8) {
+            if (c + h8 * 8 < p.d) {  // d is a multiple of 8
+              uint4 u;
+              u.x = pack_act2(__uint_as_float(o[h8 * 8 + 0]) * inv_l, __uint_as_float(o[h8 * 8 + 1]) * inv_l);
+              u.y = pack_act2(__uint_as_float(o[h8 * 8 + 2]) * inv_l, __uint_as_float(o[h8 * 8 + 3]) * inv_l);
+              u.z = pack_act2(__uint_as_float(o[h8 * 8 + 4]) * inv_l, __uint_as_float(o[h8 * 8 + 5]) * inv_l);
+              u.w = pack_act2(__uint_as_float(o[h8 * 8 + 6]) * inv_l, __uint_as_float(o[h8 * 8 + 7]) * inv_l);
+              *reinterpret_cast<uint4*>(orow + c + h8 * 8) = u;
+            }
           }
         }
       }
@@ -272,6 +370,7 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   B200SD_REQUIRE(aligned16(h.q) && aligned16(h.k) && aligned16(h.v) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
                  "attention: pointers must be 16-byte aligned");
   B200SD_REQUIRE(h.heads <= 65535 && h.batch <= 65535, B200SD_ERR_TOO_LARGE, "attention: grid too large");
+  B200SD_REQUIRE(h.scale > 0.f, B200SD_ERR_BAD_ARGUMENT, "attention: scale must be positive");
 
   AttnDev d;
   memset(&d, 0, sizeof(d));
@@ -284,8 +383,10 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   d.ldo = h.ldo;
   d.nd = ceil_div(h.d, 64);
   d.dN = ceil_div(h.d, 16) * 16;
-  d.stages = (d.nd == 2) ? 2 : 1;
-  d.tmem_cols = (128 + d.dN <= 256) ? 256 : 512;
+  d.qtiles = (d.dN <= 128 && h.nq > kBQ) ? 2 : 1;
+  d.stages = (d.nd == 1) ? 2 : ((d.qtiles == 1 && d.nd == 2) ? 2 : 1);
+  d.tmem_cols = (d.qtiles == 2) ? 512 : ((128 + d.dN <= 256) ? 256 : 512);
+  d.sum_col = (d.dN > h.d) ? h.d : -1;
   d.causal = h.causal;
   d.scale_log2 = h.scale * 1.4426950408889634f;
 
@@ -301,14 +402,20 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   if (int e = enc(&d.tmK, h.k, h.nk, h.ldk)) return e;
   if (int e = enc(&d.tmV, h.v, h.nk, h.ldv)) return e;
 
-  const int smem_bytes = d.nd * kAtomBytes * (1 + 2 * d.stages) + 2 * kAtomBytes + 1024;
+  const int smem_bytes = d.nd * kAtomBytes * (d.qtiles + 2 * d.stages) + d.qtiles * 2 * kAtomBytes + 1024;
+  B200SD_REQUIRE(smem_bytes <= di.max_smem_optin - 512, B200SD_ERR_TOO_LARGE, "attention: shared memory budget");
   if (!g_attn_attr_set) {
-    B200SD_CUDA_CHECK(
-        cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, di.max_smem_optin - 512));
+    B200SD_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           di.max_smem_optin - 512));
+    B200SD_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           di.max_smem_optin - 512));
     g_attn_attr_set = true;
   }
-  dim3 grid(ceil_div(h.nq, kBQ), h.heads, h.batch);
-  attention_kernel<<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
+  dim3 grid(ceil_div(h.nq, kBQ * d.qtiles), h.heads, h.batch);
+  if (d.sum_col >= 0)
+    attention_kernel<true><<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
+  else
+    attention_kernel<false><<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }

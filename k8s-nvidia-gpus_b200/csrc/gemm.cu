@@ -10,9 +10,10 @@
 //                       Up to two NHWC sources are walked back to back along K (virtual channel concat).
 //   warp 1 (1 thread) : tcgen05.mma issuer (128 x BN x 16 UMMAs, act_t -> fp32 accumulators in TMEM).
 //   warp 2            : TMEM allocator (512 columns = 2 accumulator stages of up to 256 columns).
-//   warps 4..7        : epilogue.  tcgen05.ld -> registers -> alpha/bias/time-embedding/activation/GEGLU/residual
-//                       -> act_t or fp32 global stores.  Double-buffered accumulators let the epilogue of tile i
-//                       overlap the mainloop of tile i+1.
+//   warps 4..11       : epilogue (2 warpgroups on alternate 128-byte column groups).  tcgen05.ld -> registers ->
+//                       alpha/bias/time-embedding/activation/GEGLU/residual -> per-warp swizzled smem staging ->
+//                       coalesced 16-bit or fp32 global stores.  Double-buffered accumulators let the epilogue of
+//                       tile i overlap the mainloop of tile i+1.
 //
 // Shared memory: num_stages x (A 128x64 act_t = 16 KB | B BNx64 act_t) in the canonical K-major SWIZZLE_128B layout,
 // filled by TMA and consumed directly by UMMA shared-memory descriptors.
@@ -24,7 +25,8 @@ namespace b200sd {
 static constexpr int kBlockM = 128;
 static constexpr int kBlockK = 64;
 static constexpr int kMaxStages = 8;
-static constexpr int kGemmThreads = 256;
+static constexpr int kGemmThreads = 384;
+static constexpr int kEpiStageBytes = 8 * 4096;  // per-epilogue-warp 32 x 128 B staging tiles
 static constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
 
 struct alignas(64) GemmDev {
@@ -88,7 +90,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&tfull_bar[s]), 1);
-      mbar_init(smem_u32(&tempty_bar[s]), 4);  // one arrive per epilogue warp
+      mbar_init(smem_u32(&tempty_bar[s]), 8);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -164,14 +166,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       }
     }
   } else if (warp >= 4) {
-    // -------------------------------------------------------------- epilogue (128 threads, thread = accumulator row)
+    // -------------------------------------------------------------- epilogue: 8 warps = 2 warpgroups
+    // warp % 4 selects the TMEM lane quarter (32 accumulator rows, thread = row); the warpgroup takes alternate
+    // 128-byte column groups (64 16-bit or 32 fp32 output columns).  Each warp stages its 32 rows x 128 B through a
+    // private XOR-swizzled shared-memory tile so that residual loads and output stores are issued as 4 full 128-byte
+    // lines per instruction instead of 32 scattered 16-byte pieces.
     const int q = warp & 3;
+    const int half = (warp - 4) >> 2;
     const int r = q * 32 + lane;
     const int iw = r % p.bw;
     const int ih = (r / p.bw) % p.bh;
     const int in = r / (p.bw * p.bh);
     const bool geglu = (p.act == B200SD_ACT_GEGLU);
     const int n_out = geglu ? p.N / 2 : p.N;
+    const int gcols = p.out_f32 ? 32 : 64;        // output columns per 128-byte group
+    const int acols = geglu ? 2 * gcols : gcols;  // accumulator columns per group
+    const int esz = p.out_f32 ? 4 : 2;
+    const int cpc = 16 / esz;                     // output columns per 16-byte chunk
+    const uint32_t stg = tiles_base + p.num_stages * stage_bytes + (warp - 4) * 4096;
+    const uint32_t my_row_smem = stg + lane * 128;
+    const int rd_row = lane >> 3, rd_chunk = lane & 7;  // coalesced phase: 4 rows x 8 chunks per instruction
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -179,118 +193,161 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       decode_tile(p, tile, n0, h0, w0, col0);
       const int img = n0 + in, y = h0 + ih, x = w0 + iw;
       const bool row_ok = (img < p.nimg) && (y < p.H) && (x < p.W);
-      const long long row = (static_cast<long long>(img) * p.H + y) * p.W + x;
+      const int row = row_ok ? (img * p.H + y) * p.W + x : 0;
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
-      const int ncols = min(p.BN, p.N - col0);  // valid accumulator columns in this tile
-      for (int c = 0; c < ncols; c += (geglu ? 64 : 32)) {
+      const int ncols = min(p.BN, p.N - col0);                    // valid accumulator columns in this tile
+      const int out_end = geglu ? (col0 + ncols) / 2 : col0 + ncols;  // one past the last output column of the tile
+      const int ngroups = (ncols + acols - 1) / acols;
+
+      // accumulator columns [ac, ac+32) -> f[] = alpha * acc + bias
+      auto load_chunk = [&](int ac, float(&f)[32]) {
         uint32_t v[32];
-        float f[32];
-        tmem_ld32(taddr + c, v);
+        tmem_ld32(taddr + ac, v);
         tmem_ld_wait();
-        const int col = col0 + c;
+        if (p.alpha != 1.f) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * p.alpha;
+          for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(v[k]) * p.alpha;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(v[k]);
+        }
         if (p.bias != nullptr) {
+          const int col = col0 + ac;
           if (col + 32 <= p.N) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col) + j);
-              f[4 * j + 0] += b4.x;
-              f[4 * j + 1] += b4.y;
-              f[4 * j + 2] += b4.z;
-              f[4 * j + 3] += b4.w;
+            for (int k = 0; k < 8; ++k) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col) + k);
+              f[4 * k + 0] += b4.x;
+              f[4 * k + 1] += b4.y;
+              f[4 * k + 2] += b4.z;
+              f[4 * k + 3] += b4.w;
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col + j < p.N) f[j] += __ldg(p.bias + col + j);
+            for (int k = 0; k < 32; ++k)
+              if (col + k < p.N) f[k] += __ldg(p.bias + col + k);
           }
         }
-        int ocol = col;  // output column of f[0]
-        if (geglu) {
-          // columns [c, c+32) = value, [c+32, c+64) = gate (weights packed that way): out = value * gelu(gate)
-          uint32_t g[32];
-          tmem_ld32(taddr + c + 32, g);
-          tmem_ld_wait();
+      };
+
+      for (int g = half; g < ngroups; g += 2) {
+        const int ac0 = g * acols;
+        const int ocol0 = geglu ? (col0 + ac0) / 2 : col0 + ac0;  // first output column of this group
+        if (p.residual != nullptr) {
+          // coalesced residual load (16-bit, 64 columns x 32 rows) into the staging tile
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float gv = __uint_as_float(g[j]) * p.alpha;
-            if (p.bias != nullptr) gv += __ldg(p.bias + col + 32 + j);
-            f[j] *= gelu_erf_f(gv);
+          for (int i = 0; i < 8; ++i) {
+            const int rr = i * 4 + rd_row;
+            const int grow = __shfl_sync(0xffffffffu, row, rr);
+            const int gok = __shfl_sync(0xffffffffu, static_cast<int>(row_ok), rr);
+            const int c = ocol0 + rd_chunk * 8;
+            uint4 u = make_uint4(0u, 0u, 0u, 0u);
+            if (gok && c < out_end)
+              u = __ldg(reinterpret_cast<const uint4*>(p.residual + static_cast<long long>(grow) * p.ldr + c));
+            const uint32_t a = stg + rr * 128 + ((rd_chunk ^ (rr & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w)
+                         : "memory");
           }
-          ocol = col / 2;
-        } else {
-          if (p.rowbias != nullptr && row_ok) {
-            const float* rb = p.rowbias + static_cast<long long>(img) * p.ld_rowbias + col;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col + j < p.N) f[j] += __ldg(rb + j);
-          }
-          if (p.act == B200SD_ACT_SILU) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = silu_f(f[j]);
-          } else if (p.act == B200SD_ACT_QUICK_GELU) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = quick_gelu_f(f[j]);
-          }
+          __syncwarp();
         }
-        if (row_ok) {
-          const bool full = (ocol + 32 <= n_out);
-          if (p.residual != nullptr) {
-            const act_t* rp = p.residual + row * p.ldr + ocol;
-            if (full && (p.ldr & 7) == 0) {
+        uint32_t w[32];  // this row's 128 output bytes
+        const int nsub = p.out_f32 ? 1 : 2;
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp) + j);
-                const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), cc = unpack_act2(u.z),
-                             d = unpack_act2(u.w);
-                f[8 * j + 0] += a.x;
-                f[8 * j + 1] += a.y;
-                f[8 * j + 2] += b.x;
-                f[8 * j + 3] += b.y;
-                f[8 * j + 4] += cc.x;
-                f[8 * j + 5] += cc.y;
-                f[8 * j + 6] += d.x;
-                f[8 * j + 7] += d.y;
+        for (int hh = 0; hh < 2; ++hh) {
+          if (hh < nsub) {
+            float f[32];
+            if (geglu) {
+              // packed weights: 64-row groups [32 value | 32 gate] -> out = value * gelu(gate)
+              float gt[32];
+              load_chunk(ac0 + hh * 64, f);
+              load_chunk(ac0 + hh * 64 + 32, gt);
+#pragma unroll
+              for (int k = 0; k < 32; ++k) f[k] *= gelu_erf_f(gt[k]);
+            } else {
+              const int ac = ac0 + hh * 32;
+              load_chunk(ac, f);
+              if (p.rowbias != nullptr && row_ok) {
+                const float* rb = p.rowbias + static_cast<long long>(img) * p.ld_rowbias + col0 + ac;
+#pragma unroll
+                for (int k = 0; k < 32; ++k)
+                  if (col0 + ac + k < p.N) f[k] += __ldg(rb + k);
               }
-            } else {
+              if (p.act == B200SD_ACT_SILU) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (ocol + j < n_out) f[j] += from_act(rp[j]);
+                for (int k = 0; k < 32; ++k) f[k] = silu_f(f[k]);
+              } else if (p.act == B200SD_ACT_QUICK_GELU) {
+#pragma unroll
+                for (int k = 0; k < 32; ++k) f[k] = quick_gelu_f(f[k]);
+              }
             }
-          }
-          if (p.out_f32) {
-            float* op = reinterpret_cast<float*>(p.out) + row * p.ldc + ocol;
-            if (full && (p.ldc & 3) == 0) {
+            if (p.residual != nullptr) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
-                reinterpret_cast<float4*>(op)[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (ocol + j < n_out) op[j] = f[j];
-            }
-          } else {
-            act_t* op = reinterpret_cast<act_t*>(p.out) + row * p.ldc + ocol;
-            if (full && (p.ldc & 7) == 0) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int k = 0; k < 4; ++k) {  // my row, chunks hh*4 .. hh*4+3
+                const int ch = hh * 4 + k;
                 uint4 u;
-                u.x = pack_act2(f[8 * j + 0], f[8 * j + 1]);
-                u.y = pack_act2(f[8 * j + 2], f[8 * j + 3]);
-                u.z = pack_act2(f[8 * j + 4], f[8 * j + 5]);
-                u.w = pack_act2(f[8 * j + 6], f[8 * j + 7]);
-                reinterpret_cast<uint4*>(op)[j] = u;
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+                             : "r"(my_row_smem + ((ch ^ (lane & 7)) << 4)));
+                const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), cc = unpack_act2(u.z), d = unpack_act2(u.w);
+                f[8 * k + 0] += a.x;
+                f[8 * k + 1] += a.y;
+                f[8 * k + 2] += b.x;
+                f[8 * k + 3] += b.y;
+                f[8 * k + 4] += cc.x;
+                f[8 * k + 5] += cc.y;
+                f[8 * k + 6] += d.x;
+                f[8 * k + 7] += d.y;
               }
+            }
+            if (p.out_f32) {
+#pragma unroll
+              for (int k = 0; k < 32; ++k) w[k] = __float_as_uint(f[k]);
             } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
-                if (ocol + j < n_out) op[j] = to_act(f[j]);
+              for (int k = 0; k < 16; ++k) w[hh * 16 + k] = pack_act2(f[2 * k], f[2 * k + 1]);
             }
           }
         }
+        __syncwarp();
+        // my row -> staging (chunk k at (k ^ row) : bank-conflict free for both access patterns)
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row_smem + ((k ^ (lane & 7)) << 4)),
+                       "r"(w[4 * k]), "r"(w[4 * k + 1]), "r"(w[4 * k + 2]), "r"(w[4 * k + 3])
+                       : "memory");
+        __syncwarp();
+        // staging -> global, 4 rows x 128 B per instruction
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = i * 4 + rd_row;
+          const int grow = __shfl_sync(0xffffffffu, row, rr);
+          const int gok = __shfl_sync(0xffffffffu, static_cast<int>(row_ok), rr);
+          uint4 u;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+                       : "r"(stg + rr * 128 + ((rd_chunk ^ (rr & 7)) << 4)));
+          const int c = ocol0 + rd_chunk * cpc;
+          if (gok && c < out_end) {
+            uint8_t* op = reinterpret_cast<uint8_t*>(p.out) + (static_cast<long long>(grow) * p.ldc + c) * esz;
+            if (c + cpc <= out_end && ((p.ldc * esz) & 15) == 0) {
+              *reinterpret_cast<uint4*>(op) = u;
+            } else if (p.out_f32) {
+              const uint32_t e[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                if (c + k < out_end) reinterpret_cast<uint32_t*>(op)[k] = e[k];
+            } else {
+              const uint32_t e[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (c + k < out_end)
+                  reinterpret_cast<uint16_t*>(op)[k] = static_cast<uint16_t>(e[k >> 1] >> ((k & 1) * 16));
+            }
+          }
+        }
+        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
@@ -317,7 +374,7 @@ static int pick_bn(int M_tiles, int N, int sm_count, bool geglu) {
   int best = 128;
   double best_cost = 1e30;
   for (int bn : cands) {
-    if (geglu && (bn % 64) != 0) continue;
+    if (geglu && (bn % 128) != 0) continue;
     if (bn > 32 && bn - 32 >= N) continue;  // tile far wider than N
     const int tn = (N + bn - 1) / bn;
     const long long tiles = static_cast<long long>(M_tiles) * tn;
@@ -358,7 +415,10 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
                      aligned16(h.residual),
                  B200SD_ERR_BAD_ALIGNMENT, "gemm: pointers must be 16-byte aligned");
   const bool geglu = (h.act == B200SD_ACT_GEGLU);
-  B200SD_REQUIRE(!geglu || (h.n % 64) == 0, B200SD_ERR_BAD_SHAPE, "gemm: GEGLU needs n %% 64 == 0");
+  B200SD_REQUIRE(!geglu || (h.n % 128) == 0, B200SD_ERR_BAD_SHAPE, "gemm: GEGLU needs n %% 128 == 0");
+  B200SD_REQUIRE(!geglu || h.out_dtype != B200SD_F32, B200SD_ERR_BAD_ARGUMENT, "gemm: GEGLU output is 16-bit");
+  B200SD_REQUIRE(h.residual == nullptr || (h.out_dtype != B200SD_F32 && (h.ldr % 8) == 0 && (h.n % 8) == 0),
+                 B200SD_ERR_BAD_ARGUMENT, "gemm: residual needs 16-bit output and n, ldr multiples of 8");
   B200SD_REQUIRE(!geglu || (h.rowbias == nullptr && h.residual == nullptr), B200SD_ERR_BAD_ARGUMENT,
                  "gemm: GEGLU epilogue takes no rowbias/residual");
   B200SD_REQUIRE(h.act >= 0 && h.act <= 3, B200SD_ERR_BAD_ARGUMENT, "gemm: bad act %d", h.act);
@@ -378,7 +438,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.tiles_m = d.tiles_w * d.tiles_h * d.tiles_n;
   int bn_tile = h.bn_hint;
   if (bn_tile == 0) bn_tile = pick_bn(d.tiles_m, h.n, di.sm_count, geglu);
-  B200SD_REQUIRE(bn_tile >= 32 && bn_tile <= 256 && (bn_tile % 32) == 0 && (!geglu || (bn_tile % 64) == 0),
+  B200SD_REQUIRE(bn_tile >= 32 && bn_tile <= 256 && (bn_tile % 32) == 0 && (!geglu || (bn_tile % 128) == 0),
                  B200SD_ERR_BAD_ARGUMENT, "gemm: bad bn_hint %d", bn_tile);
   d.BN = bn_tile;
   d.tiles_ncol = ceil_div(h.n, d.BN);
@@ -393,7 +453,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.cblk0 = ceil_div(h.c0, kBlockK);
   d.cblk1 = ceil_div(h.c1, kBlockK);
   const uint32_t stage_bytes = kABytes + d.BN * kBlockK * 2;
-  const int smem_budget = di.max_smem_optin - 1024 /*align slack*/ - 512 /*static*/;
+  const int smem_budget = di.max_smem_optin - 1024 /*align slack*/ - 512 /*static*/ - kEpiStageBytes;
   d.num_stages = min(kMaxStages, smem_budget / static_cast<int>(stage_bytes));
   B200SD_REQUIRE(d.num_stages >= 2, B200SD_ERR_CUDA, "gemm: not enough shared memory (%d B opt-in)", di.max_smem_optin);
   d.out = h.out;
@@ -433,7 +493,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
     if (int e = encode_tmap_act(&d.tmB, h.w, 2, dims, st, box)) return e;
   }
 
-  const int smem_bytes = d.num_stages * stage_bytes + 1024;
+  const int smem_bytes = d.num_stages * stage_bytes + kEpiStageBytes + 1024;
   if (!g_gemm_attr_set) {
     B200SD_CUDA_CHECK(
         cudaFuncSetAttribute(gemm_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, di.max_smem_optin - 512));

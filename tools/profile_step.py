@@ -109,5 +109,34 @@ def mode_kernels():
         print(f"{name:44s} {ms:8.3f} ms  {byt / ms / 1e6:8.1f} GB/s")
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and (len(sys.argv) < 2 or sys.argv[1] in ("step", "kernels")):
     {"step": mode_step, "kernels": mode_kernels}[sys.argv[1] if len(sys.argv) > 1 else "kernels"]()
+
+
+def mode_lin():
+    """Short-K linear (65536 x 320 -> 960) under different tile widths; used for ncu and quick A/B timing."""
+    import b200sd
+    ops = b200sd.ops
+    dt = b200sd.lib.act_dtype()
+    s = ops.current_stream()
+    m, k, nn = 65536, 320, 960
+    x = (torch.randn(m, k, device="cuda")).to(dt)
+    w = (torch.randn(nn, 1, k, device="cuda") * k ** -0.5).to(dt)
+    out = torch.empty(m, nn, device="cuda", dtype=dt)
+    bias = torch.zeros(nn, device="cuda")
+    for bn in (0, 64, 128, 192, 256):
+        call = ops.gemm(x, w, out, nimg=1, h=1, w_=m, c0=k, n=nn, bias=bias, bn_hint=bn)
+        call(s)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            call(s)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        print(f"linear {m}x{k}x{nn} bn={bn:3d}: {ms:.3f} ms  {2.0 * m * k * nn / ms / 1e9:.1f} TFLOP/s")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "lin":
+    mode_lin()
