@@ -54,8 +54,8 @@ static const CUtensorMapDataType kTmaDtype = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
 static const int kActCode = 1;
 #endif
 
-int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                     const uint32_t* box) {
+static int encode_tmap_any(CUtensorMap* tm, CUtensorMapDataType dtype, const void* base, int rank, const uint64_t* dims,
+                           const uint64_t* strides_bytes, const uint32_t* box) {
   if (g_encode == nullptr) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (g_encode == nullptr) {
@@ -80,7 +80,7 @@ int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t*
   for (int i = 0; i + 1 < rank; ++i)
     B200SD_REQUIRE((gstr[i] % 16) == 0, B200SD_ERR_BAD_ALIGNMENT, "TMA stride %d (%llu B) not a multiple of 16", i,
                    (unsigned long long)gstr[i]);
-  CUresult r = g_encode(tm, kTmaDtype, static_cast<cuuint32_t>(rank), const_cast<void*>(base),
+  CUresult r = g_encode(tm, dtype, static_cast<cuuint32_t>(rank), const_cast<void*>(base),
                         gdims, gstr, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200SD_REQUIRE(r == CUDA_SUCCESS, B200SD_ERR_CUDA,
@@ -89,6 +89,15 @@ int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t*
                  (unsigned long long)(rank > 2 ? gdims[2] : 0), (unsigned long long)(rank > 3 ? gdims[3] : 0), gbox[0],
                  rank > 1 ? gbox[1] : 0, rank > 2 ? gbox[2] : 0, rank > 3 ? gbox[3] : 0);
   return B200SD_OK;
+}
+
+int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box) {
+  return encode_tmap_any(tm, kTmaDtype, base, rank, dims, strides_bytes, box);
+}
+int encode_tmap_f32(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box) {
+  return encode_tmap_any(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_bytes, box);
 }
 
 }  // namespace b200sd

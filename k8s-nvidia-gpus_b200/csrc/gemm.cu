@@ -8,15 +8,18 @@
 //                       (w0 + kw - pad, h0 + kh - pad); out-of-bounds elements are zero-filled by the TMA unit,
 //                       which implements the convolution's zero padding, ragged M tiles and ragged channel counts.
 //                       Up to two NHWC sources are walked back to back along K (virtual channel concat).
-//   warp 1 (1 thread) : tcgen05.mma issuer (128 x BN x 16 UMMAs, act_t -> fp32 accumulators in TMEM).
+//   warp 1 (1 thread) : tcgen05.mma issuer (128 x N x 16 UMMAs, 16-bit operands -> fp32 accumulators in TMEM; N is
+//                       the tile width, shrunk to the valid width on the last column tile).
 //   warp 2            : TMEM allocator (512 columns = 2 accumulator stages of up to 256 columns).
-//   warps 4..11       : epilogue (2 warpgroups on alternate 128-byte column groups).  tcgen05.ld -> registers ->
-//                       alpha/bias/time-embedding/activation/GEGLU/residual -> per-warp swizzled smem staging ->
-//                       coalesced 16-bit or fp32 global stores.  Double-buffered accumulators let the epilogue of
-//                       tile i overlap the mainloop of tile i+1.
+//   warps 4..11       : epilogue, 2 warpgroups on alternate 128-byte column groups (64 16-bit / 32 fp32 columns).
+//                       tcgen05.ld -> registers -> alpha/bias/time-embedding/activation/GEGLU/residual -> one
+//                       swizzle-128B staging tile per warpgroup -> ONE 4-D TMA store per group (the TMA unit clips
+//                       ragged rows/columns, so the epilogue has no address arithmetic or predicates).  The residual
+//                       tile arrives the same way (TMA load into the staging tile).  Double-buffered accumulators
+//                       let the epilogue of tile i overlap the mainloop of tile i+1.
 //
-// Shared memory: num_stages x (A 128x64 act_t = 16 KB | B BNx64 act_t) in the canonical K-major SWIZZLE_128B layout,
-// filled by TMA and consumed directly by UMMA shared-memory descriptors.
+// Shared memory: num_stages x (A 128x64 = 16 KB | B BNx64) in the canonical K-major SWIZZLE_128B layout, filled by
+// TMA and consumed directly by UMMA shared-memory descriptors, + 2 x 16 KB epilogue staging.
 #include "common.cuh"
 #include "host.cuh"
 
@@ -26,26 +29,27 @@ static constexpr int kBlockM = 128;
 static constexpr int kBlockK = 64;
 static constexpr int kMaxStages = 8;
 static constexpr int kGemmThreads = 384;
-static constexpr int kEpiStageBytes = 8 * 4096;  // per-epilogue-warp 32 x 128 B staging tiles
 static constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
+static constexpr uint32_t kEpiTileBytes = 128 * 128;        // 128 rows x 128 B
+static constexpr int kEpiStageBytes = 2 * kEpiTileBytes;    // one staging tile per epilogue warpgroup
 
 struct alignas(64) GemmDev {
   CUtensorMap tmA0;
   CUtensorMap tmA1;
   CUtensorMap tmB;
-  void* out;
+  CUtensorMap tmO;  // output, box {64 16-bit | 32 fp32 columns, bw, bh, bn}
+  CUtensorMap tmR;  // residual (16-bit), same box
   const float* bias;
   const float* rowbias;
-  const act_t* residual;
-  int M_total, N, BN;
+  int N, BN;
   int nimg, H, W;
   int bw, bh, bn;
   int tiles_w, tiles_h, tiles_n, tiles_m, tiles_ncol;
   int ksize, pad, taps;
   int cblk0, cblk1;
   int num_stages;
-  int ldc, ldr, ld_rowbias;
-  int act, out_f32;
+  int ld_rowbias;
+  int act;
   float alpha;
 };
 
@@ -61,12 +65,14 @@ __device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int& n0,
   col0 = nt * p.BN;
 }
 
+template <bool kOutF32, bool kGeglu, bool kRes>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid_constant__ GemmDev p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
   __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
   __shared__ __align__(8) uint64_t tfull_bar[2];
   __shared__ __align__(8) uint64_t tempty_bar[2];
+  __shared__ __align__(8) uint64_t res_bar[2];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5;
@@ -82,6 +88,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     tma_prefetch_desc(&p.tmA0);
     if (p.cblk1 > 0) tma_prefetch_desc(&p.tmA1);
     tma_prefetch_desc(&p.tmB);
+    tma_prefetch_desc(&p.tmO);
+    if (kRes) tma_prefetch_desc(&p.tmR);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
@@ -91,6 +99,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&tfull_bar[s]), 1);
       mbar_init(smem_u32(&tempty_bar[s]), 8);  // one arrive per epilogue warp
+      mbar_init(smem_u32(&res_bar[s]), 1);
     }
     fence_mbar_init();
   }
@@ -132,12 +141,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   } else if (warp == 1) {
     if (lane == 0) {
       // ------------------------------------------------------------ MMA issuer
-      const uint32_t idesc = make_idesc_f16(kBlockM, p.BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int col0 = (tile % p.tiles_ncol) * p.BN;
+        const int ncols = min(p.BN, p.N - col0);
+        const uint32_t idesc = make_idesc_f16(kBlockM, (ncols + 15) & ~15, 0, 0);  // no MMA work on padding columns
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -149,7 +160,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           const uint64_t bdesc = make_smem_desc_sw128(sa + kABytes, 16, 1024);
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
-            // advancing K by 16 act_t = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+            // advancing K by 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
             umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
           umma_commit(smem_u32(&empty_bar[stage]));
@@ -166,39 +177,33 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       }
     }
   } else if (warp >= 4) {
-    // -------------------------------------------------------------- epilogue: 8 warps = 2 warpgroups
-    // warp % 4 selects the TMEM lane quarter (32 accumulator rows, thread = row); the warpgroup takes alternate
-    // 128-byte column groups (64 16-bit or 32 fp32 output columns).  Each warp stages its 32 rows x 128 B through a
-    // private XOR-swizzled shared-memory tile so that residual loads and output stores are issued as 4 full 128-byte
-    // lines per instruction instead of 32 scattered 16-byte pieces.
-    const int q = warp & 3;
-    const int half = (warp - 4) >> 2;
-    const int r = q * 32 + lane;
+    // -------------------------------------------------------------- epilogue: 2 warpgroups x 4 warps
+    const int q = warp & 3;            // TMEM lane quarter
+    const int wg = (warp - 4) >> 2;    // warpgroup: alternate column groups
+    const int r = q * 32 + lane;       // accumulator row == staging row
     const int iw = r % p.bw;
     const int ih = (r / p.bw) % p.bh;
     const int in = r / (p.bw * p.bh);
-    const bool geglu = (p.act == B200SD_ACT_GEGLU);
-    const int n_out = geglu ? p.N / 2 : p.N;
-    const int gcols = p.out_f32 ? 32 : 64;        // output columns per 128-byte group
-    const int acols = geglu ? 2 * gcols : gcols;  // accumulator columns per group
-    const int esz = p.out_f32 ? 4 : 2;
-    const int cpc = 16 / esz;                     // output columns per 16-byte chunk
-    const uint32_t stg = tiles_base + p.num_stages * stage_bytes + (warp - 4) * 4096;
-    const uint32_t my_row_smem = stg + lane * 128;
-    const int rd_row = lane >> 3, rd_chunk = lane & 7;  // coalesced phase: 4 rows x 8 chunks per instruction
+    constexpr int gcols = kOutF32 ? 32 : 64;        // output columns per 128-byte group
+    constexpr int acols = kGeglu ? 2 * gcols : gcols;  // accumulator columns per group
+    constexpr int nsub = kOutF32 ? 1 : 2;           // 32-column sub-blocks per group
+    const uint32_t stg = tiles_base + p.num_stages * stage_bytes + wg * kEpiTileBytes;
+    const uint32_t my_row = stg + r * 128;
+    const uint32_t sw = static_cast<uint32_t>(r & 7);
+    const bool issuer = (q == 0 && lane == 0);
+    const int bar_id = 1 + wg;
+    const uint32_t resb = smem_u32(&res_bar[wg]);
+    uint32_t res_phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int n0, h0, w0, col0;
       decode_tile(p, tile, n0, h0, w0, col0);
-      const int img = n0 + in, y = h0 + ih, x = w0 + iw;
-      const bool row_ok = (img < p.nimg) && (y < p.H) && (x < p.W);
-      const int row = row_ok ? (img * p.H + y) * p.W + x : 0;
+      const int img = min(n0 + in, p.nimg - 1);  // rows beyond the tensor are clipped by the TMA store
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
-      const int ncols = min(p.BN, p.N - col0);                    // valid accumulator columns in this tile
-      const int out_end = geglu ? (col0 + ncols) / 2 : col0 + ncols;  // one past the last output column of the tile
+      const int ncols = min(p.BN, p.N - col0);  // valid accumulator columns in this tile
       const int ngroups = (ncols + acols - 1) / acols;
 
       // accumulator columns [ac, ac+32) -> f[] = alpha * acc + bias
@@ -232,122 +237,89 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         }
       };
 
-      for (int g = half; g < ngroups; g += 2) {
+      for (int g = wg; g < ngroups; g += 2) {
         const int ac0 = g * acols;
-        const int ocol0 = geglu ? (col0 + ac0) / 2 : col0 + ac0;  // first output column of this group
-        if (p.residual != nullptr) {
-          // coalesced residual load (16-bit, 64 columns x 32 rows) into the staging tile
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rr = i * 4 + rd_row;
-            const int grow = __shfl_sync(0xffffffffu, row, rr);
-            const int gok = __shfl_sync(0xffffffffu, static_cast<int>(row_ok), rr);
-            const int c = ocol0 + rd_chunk * 8;
-            uint4 u = make_uint4(0u, 0u, 0u, 0u);
-            if (gok && c < out_end)
-              u = __ldg(reinterpret_cast<const uint4*>(p.residual + static_cast<long long>(grow) * p.ldr + c));
-            const uint32_t a = stg + rr * 128 + ((rd_chunk ^ (rr & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w)
-                         : "memory");
+        const int ocol0 = kGeglu ? (col0 + ac0) / 2 : col0 + ac0;  // first output column of this group
+        if (kRes) {
+          // the residual tile lands in the staging tile (after the previous store has finished reading it)
+          if (issuer) {
+            bulk_wait_read0();
+            mbar_arrive_expect_tx(resb, kEpiTileBytes);
+            tma_load_4d(stg, &p.tmR, resb, ocol0, w0, h0, n0);
           }
-          __syncwarp();
         }
         uint32_t w[32];  // this row's 128 output bytes
-        const int nsub = p.out_f32 ? 1 : 2;
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          if (hh < nsub) {
-            float f[32];
-            if (geglu) {
-              // packed weights: 64-row groups [32 value | 32 gate] -> out = value * gelu(gate)
-              float gt[32];
-              load_chunk(ac0 + hh * 64, f);
-              load_chunk(ac0 + hh * 64 + 32, gt);
+        for (int hh = 0; hh < nsub; ++hh) {
+          float f[32];
+          if (kGeglu) {
+            // packed weights: 64-row groups [32 value | 32 gate] -> out = value * gelu(gate)
+            float gt[32];
+            load_chunk(ac0 + hh * 64, f);
+            load_chunk(ac0 + hh * 64 + 32, gt);
 #pragma unroll
-              for (int k = 0; k < 32; ++k) f[k] *= gelu_erf_f(gt[k]);
-            } else {
-              const int ac = ac0 + hh * 32;
-              load_chunk(ac, f);
-              if (p.rowbias != nullptr && row_ok) {
-                const float* rb = p.rowbias + static_cast<long long>(img) * p.ld_rowbias + col0 + ac;
+            for (int k = 0; k < 32; ++k) f[k] *= gelu_erf_f(gt[k]);
+          } else {
+            const int ac = ac0 + hh * 32;
+            load_chunk(ac, f);
+            if (p.rowbias != nullptr) {
+              const float* rb = p.rowbias + static_cast<long long>(img) * p.ld_rowbias + col0 + ac;
 #pragma unroll
-                for (int k = 0; k < 32; ++k)
-                  if (col0 + ac + k < p.N) f[k] += __ldg(rb + k);
-              }
-              if (p.act == B200SD_ACT_SILU) {
-#pragma unroll
-                for (int k = 0; k < 32; ++k) f[k] = silu_f(f[k]);
-              } else if (p.act == B200SD_ACT_QUICK_GELU) {
-#pragma unroll
-                for (int k = 0; k < 32; ++k) f[k] = quick_gelu_f(f[k]);
-              }
+              for (int k = 0; k < 32; ++k)
+                if (col0 + ac + k < p.N) f[k] += __ldg(rb + k);
             }
-            if (p.residual != nullptr) {
+            if (p.act == B200SD_ACT_SILU) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {  // my row, chunks hh*4 .. hh*4+3
-                const int ch = hh * 4 + k;
-                uint4 u;
-                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                             : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
-                             : "r"(my_row_smem + ((ch ^ (lane & 7)) << 4)));
-                const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), cc = unpack_act2(u.z), d = unpack_act2(u.w);
-                f[8 * k + 0] += a.x;
-                f[8 * k + 1] += a.y;
-                f[8 * k + 2] += b.x;
-                f[8 * k + 3] += b.y;
-                f[8 * k + 4] += cc.x;
-                f[8 * k + 5] += cc.y;
-                f[8 * k + 6] += d.x;
-                f[8 * k + 7] += d.y;
-              }
-            }
-            if (p.out_f32) {
+              for (int k = 0; k < 32; ++k) f[k] = silu_f(f[k]);
+            } else if (p.act == B200SD_ACT_QUICK_GELU) {
 #pragma unroll
-              for (int k = 0; k < 32; ++k) w[k] = __float_as_uint(f[k]);
-            } else {
-#pragma unroll
-              for (int k = 0; k < 16; ++k) w[hh * 16 + k] = pack_act2(f[2 * k], f[2 * k + 1]);
+              for (int k = 0; k < 32; ++k) f[k] = quick_gelu_f(f[k]);
             }
           }
+          if (kRes) {
+            if (hh == 0) {
+              mbar_wait(resb, res_phase);
+              res_phase ^= 1u;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {  // my row, 16-byte chunks hh*4 .. hh*4+3
+              uint4 u;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
+                           : "r"(my_row + (((hh * 4 + k) ^ sw) << 4)));
+              const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), cc = unpack_act2(u.z), d = unpack_act2(u.w);
+              f[8 * k + 0] += a.x;
+              f[8 * k + 1] += a.y;
+              f[8 * k + 2] += b.x;
+              f[8 * k + 3] += b.y;
+              f[8 * k + 4] += cc.x;
+              f[8 * k + 5] += cc.y;
+              f[8 * k + 6] += d.x;
+              f[8 * k + 7] += d.y;
+            }
+          }
+          if (kOutF32) {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) w[k] = __float_as_uint(f[k]);
+          } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) w[hh * 16 + k] = pack_act2(f[2 * k], f[2 * k + 1]);
+          }
         }
-        __syncwarp();
-        // my row -> staging (chunk k at (k ^ row) : bank-conflict free for both access patterns)
+        // staging tile free: residual consumed by everyone (kRes) / previous store has finished reading it
+        if (!kRes && issuer) bulk_wait_read0();
+        named_bar_sync(bar_id, 128);
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row_smem + ((k ^ (lane & 7)) << 4)),
-                       "r"(w[4 * k]), "r"(w[4 * k + 1]), "r"(w[4 * k + 2]), "r"(w[4 * k + 3])
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((k ^ sw) << 4)), "r"(w[4 * k]),
+                       "r"(w[4 * k + 1]), "r"(w[4 * k + 2]), "r"(w[4 * k + 3])
                        : "memory");
-        __syncwarp();
-        // staging -> global, 4 rows x 128 B per instruction
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = i * 4 + rd_row;
-          const int grow = __shfl_sync(0xffffffffu, row, rr);
-          const int gok = __shfl_sync(0xffffffffu, static_cast<int>(row_ok), rr);
-          uint4 u;
-          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                       : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
-                       : "r"(stg + rr * 128 + ((rd_chunk ^ (rr & 7)) << 4)));
-          const int c = ocol0 + rd_chunk * cpc;
-          if (gok && c < out_end) {
-            uint8_t* op = reinterpret_cast<uint8_t*>(p.out) + (static_cast<long long>(grow) * p.ldc + c) * esz;
-            if (c + cpc <= out_end && ((p.ldc * esz) & 15) == 0) {
-              *reinterpret_cast<uint4*>(op) = u;
-            } else if (p.out_f32) {
-              const uint32_t e[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int k = 0; k < 4; ++k)
-                if (c + k < out_end) reinterpret_cast<uint32_t*>(op)[k] = e[k];
-            } else {
-              const uint32_t e[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int k = 0; k < 8; ++k)
-                if (c + k < out_end)
-                  reinterpret_cast<uint16_t*>(op)[k] = static_cast<uint16_t>(e[k >> 1] >> ((k & 1) * 16));
-            }
-          }
+        fence_proxy_async_smem();
+        named_bar_sync(bar_id, 128);
+        if (issuer) {
+          tma_store_4d(&p.tmO, stg, ocol0, w0, h0, n0);
+          bulk_commit();
         }
-        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
@@ -357,6 +329,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         acc_phase ^= 1u;
       }
     }
+    if (issuer) bulk_wait0();  // all stores complete before the CTA (and its shared memory) goes away
   }
 
   tc_fence_before();
@@ -368,21 +341,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
 }
 
 // ---------------------------------------------------------------------------------------------------- host
-static int pick_bn(int M_tiles, int N, int sm_count, bool geglu) {
-  // Candidates are multiples of 32 (64 for GEGLU pairs).  Score = padded work / SM-wave efficiency.
-  const int cands[] = {256, 192, 160, 128, 96, 64, 32};
-  int best = 128;
+static int pick_bn(int M_tiles, int N, int sm_count, int gran, int num_kb) {
+  // Tile widths are multiples of the epilogue group (`gran` accumulator columns).  Per 64-deep K block a tile costs
+  // max(MMA time, operand fetch time): 128 x w x 64 MACs at 4096 MAC/cycle = 2w cycles for valid width w, and
+  // (128 + bn) x 128 B of L2 -> SM traffic at the ~45 B/cycle/SM measured on single-CTA tiles = 2.84 (128 + bn)
+  // cycles (this term dominates, hence wide tiles), plus a fixed per-tile overhead amortised over the K loop.
+  int best = gran;
   double best_cost = 1e30;
-  for (int bn : cands) {
-    if (geglu && (bn % 128) != 0) continue;
-    if (bn > 32 && bn - 32 >= N) continue;  // tile far wider than N
+  for (int bn = 256; bn >= gran; bn -= gran) {
+    if (bn - gran >= N && bn > gran) continue;  // wider than needed
     const int tn = (N + bn - 1) / bn;
     const long long tiles = static_cast<long long>(M_tiles) * tn;
     const long long waves = (tiles + sm_count - 1) / sm_count;
-    // per-tile time ~ bn (MMA floor) with a fixed per-k-block overhead that favours wide tiles (smem bandwidth
-    // bound below bn ~ 128 for single-CTA UMMA)
-    const double tile_cost = static_cast<double>(bn < 128 ? 128 * 0.75 + bn * 0.25 : bn) + 8.0;
-    const double cost = static_cast<double>(waves) * tile_cost;
+    const double w = static_cast<double>(bn < N ? bn : N);
+    const double per_kb = (2.0 * w > 2.84 * (128.0 + bn) ? 2.0 * w : 2.84 * (128.0 + bn)) + 600.0 / num_kb;
+    const double cost = static_cast<double>(waves) * per_kb;
     if (cost < best_cost - 1e-9) {
       best_cost = cost;
       best = bn;
@@ -392,6 +365,19 @@ static int pick_bn(int M_tiles, int N, int sm_count, bool geglu) {
 }
 
 static bool g_gemm_attr_set = false;
+
+template <bool F, bool G, bool R>
+static int launch_variant(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200SD_CUDA_CHECK(
+        cudaFuncSetAttribute(gemm_conv_kernel<F, G, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 512));
+    attr_set = true;
+  }
+  gemm_conv_kernel<F, G, R><<<grid, kGemmThreads, smem_bytes, stream>>>(d);
+  B200SD_CUDA_CHECK(cudaGetLastError());
+  return B200SD_OK;
+}
 
 }  // namespace b200sd
 
@@ -414,16 +400,21 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   B200SD_REQUIRE(aligned16(h.a0) && aligned16(h.a1) && aligned16(h.w) && aligned16(h.out) && aligned16(h.bias) &&
                      aligned16(h.residual),
                  B200SD_ERR_BAD_ALIGNMENT, "gemm: pointers must be 16-byte aligned");
-  const bool geglu = (h.act == B200SD_ACT_GEGLU);
-  B200SD_REQUIRE(!geglu || (h.n % 128) == 0, B200SD_ERR_BAD_SHAPE, "gemm: GEGLU needs n %% 128 == 0");
-  B200SD_REQUIRE(!geglu || h.out_dtype != B200SD_F32, B200SD_ERR_BAD_ARGUMENT, "gemm: GEGLU output is 16-bit");
-  B200SD_REQUIRE(h.residual == nullptr || (h.out_dtype != B200SD_F32 && (h.ldr % 8) == 0 && (h.n % 8) == 0),
-                 B200SD_ERR_BAD_ARGUMENT, "gemm: residual needs 16-bit output and n, ldr multiples of 8");
-  B200SD_REQUIRE(!geglu || (h.rowbias == nullptr && h.residual == nullptr), B200SD_ERR_BAD_ARGUMENT,
-                 "gemm: GEGLU epilogue takes no rowbias/residual");
   B200SD_REQUIRE(h.act >= 0 && h.act <= 3, B200SD_ERR_BAD_ARGUMENT, "gemm: bad act %d", h.act);
+  const bool geglu = (h.act == B200SD_ACT_GEGLU);
+  const bool f32 = (h.out_dtype == B200SD_F32);
+  const bool res = (h.residual != nullptr);
+  B200SD_REQUIRE(!geglu || (h.n % 128) == 0, B200SD_ERR_BAD_SHAPE, "gemm: GEGLU needs n %% 128 == 0");
+  B200SD_REQUIRE(!geglu || !f32, B200SD_ERR_BAD_ARGUMENT, "gemm: GEGLU output is 16-bit");
+  B200SD_REQUIRE(!geglu || (h.rowbias == nullptr && !res), B200SD_ERR_BAD_ARGUMENT,
+                 "gemm: GEGLU epilogue takes no rowbias/residual");
+  B200SD_REQUIRE(!res || (!f32 && (h.ldr % 8) == 0), B200SD_ERR_BAD_ARGUMENT,
+                 "gemm: residual needs 16-bit output and ldr a multiple of 8");
   const int n_out = geglu ? h.n / 2 : h.n;
+  const int esz = f32 ? 4 : 2;
   B200SD_REQUIRE(h.ldc >= n_out, B200SD_ERR_BAD_SHAPE, "gemm: ldc (%d) < output columns (%d)", h.ldc, n_out);
+  B200SD_REQUIRE((h.ldc * esz) % 16 == 0, B200SD_ERR_BAD_ALIGNMENT,
+                 "gemm: output row pitch (ldc = %d) must be a multiple of 16 bytes", h.ldc);
   const long long M_total = static_cast<long long>(h.nimg) * h.h * h.w_;
   B200SD_REQUIRE(M_total < (1ll << 31), B200SD_ERR_TOO_LARGE, "gemm: M too large");
 
@@ -436,13 +427,14 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.tiles_h = ceil_div(h.h, d.bh);
   d.tiles_n = ceil_div(h.nimg, d.bn);
   d.tiles_m = d.tiles_w * d.tiles_h * d.tiles_n;
+  const int gran = geglu ? 128 : (f32 ? 32 : 64);  // accumulator columns per epilogue group
   int bn_tile = h.bn_hint;
-  if (bn_tile == 0) bn_tile = pick_bn(d.tiles_m, h.n, di.sm_count, geglu);
-  B200SD_REQUIRE(bn_tile >= 32 && bn_tile <= 256 && (bn_tile % 32) == 0 && (!geglu || (bn_tile % 128) == 0),
-                 B200SD_ERR_BAD_ARGUMENT, "gemm: bad bn_hint %d", bn_tile);
+  if (bn_tile == 0)
+    bn_tile = pick_bn(d.tiles_m, h.n, di.sm_count, gran, h.ksize * h.ksize * (ceil_div(h.c0, kBlockK) + ceil_div(h.c1, kBlockK)));
+  B200SD_REQUIRE(bn_tile >= gran && bn_tile <= 256 && (bn_tile % gran) == 0, B200SD_ERR_BAD_ARGUMENT,
+                 "gemm: bad bn_hint %d (must be a multiple of %d, <= 256)", bn_tile, gran);
   d.BN = bn_tile;
   d.tiles_ncol = ceil_div(h.n, d.BN);
-  d.M_total = static_cast<int>(M_total);
   d.N = h.n;
   d.nimg = h.nimg;
   d.H = h.h;
@@ -456,35 +448,25 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   const int smem_budget = di.max_smem_optin - 1024 /*align slack*/ - 512 /*static*/ - kEpiStageBytes;
   d.num_stages = min(kMaxStages, smem_budget / static_cast<int>(stage_bytes));
   B200SD_REQUIRE(d.num_stages >= 2, B200SD_ERR_CUDA, "gemm: not enough shared memory (%d B opt-in)", di.max_smem_optin);
-  d.out = h.out;
   d.bias = h.bias;
   d.rowbias = h.rowbias;
-  d.residual = static_cast<const act_t*>(h.residual);
-  d.ldc = h.ldc;
-  d.ldr = h.ldr;
   d.ld_rowbias = h.ld_rowbias;
   d.act = h.act;
-  d.out_f32 = (h.out_dtype == B200SD_F32);
   d.alpha = h.alpha;
 
-  {
-    const uint64_t dims[4] = {static_cast<uint64_t>(h.c0), static_cast<uint64_t>(h.w_), static_cast<uint64_t>(h.h),
+  const uint32_t boxA[4] = {kBlockK, static_cast<uint32_t>(d.bw), static_cast<uint32_t>(d.bh),
+                            static_cast<uint32_t>(d.bn)};
+  auto nhwc_map = [&](CUtensorMap* tm, const void* ptr, int c, int ld, int elem_bytes, const uint32_t* box,
+                      bool as_f32) -> int {
+    const uint64_t dims[4] = {static_cast<uint64_t>(c), static_cast<uint64_t>(h.w_), static_cast<uint64_t>(h.h),
                               static_cast<uint64_t>(h.nimg)};
-    const uint64_t st[3] = {static_cast<uint64_t>(h.ld0) * 2, static_cast<uint64_t>(h.ld0) * 2 * h.w_,
-                            static_cast<uint64_t>(h.ld0) * 2 * h.w_ * h.h};
-    const uint32_t box[4] = {kBlockK, static_cast<uint32_t>(d.bw), static_cast<uint32_t>(d.bh),
-                             static_cast<uint32_t>(d.bn)};
-    if (int e = encode_tmap_act(&d.tmA0, h.a0, 4, dims, st, box)) return e;
-  }
-  if (h.c1 > 0) {
-    const uint64_t dims[4] = {static_cast<uint64_t>(h.c1), static_cast<uint64_t>(h.w_), static_cast<uint64_t>(h.h),
-                              static_cast<uint64_t>(h.nimg)};
-    const uint64_t st[3] = {static_cast<uint64_t>(h.ld1) * 2, static_cast<uint64_t>(h.ld1) * 2 * h.w_,
-                            static_cast<uint64_t>(h.ld1) * 2 * h.w_ * h.h};
-    const uint32_t box[4] = {kBlockK, static_cast<uint32_t>(d.bw), static_cast<uint32_t>(d.bh),
-                             static_cast<uint32_t>(d.bn)};
-    if (int e = encode_tmap_act(&d.tmA1, h.a1, 4, dims, st, box)) return e;
-  }
+    const uint64_t pix = static_cast<uint64_t>(ld) * elem_bytes;
+    const uint64_t st[3] = {pix, pix * h.w_, pix * h.w_ * h.h};
+    return as_f32 ? encode_tmap_f32(tm, ptr, 4, dims, st, box) : encode_tmap_act(tm, ptr, 4, dims, st, box);
+  };
+  if (int e = nhwc_map(&d.tmA0, h.a0, h.c0, h.ld0, 2, boxA, false)) return e;
+  if (h.c1 > 0)
+    if (int e = nhwc_map(&d.tmA1, h.a1, h.c1, h.ld1, 2, boxA, false)) return e;
   {
     const uint64_t ktot = static_cast<uint64_t>(d.taps) * (d.cblk0 + d.cblk1) * kBlockK;
     const uint64_t dims[2] = {ktot, static_cast<uint64_t>(h.n)};
@@ -492,16 +474,20 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
     const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(d.BN)};
     if (int e = encode_tmap_act(&d.tmB, h.w, 2, dims, st, box)) return e;
   }
+  {
+    const uint32_t boxO[4] = {static_cast<uint32_t>(f32 ? 32 : 64), static_cast<uint32_t>(d.bw),
+                              static_cast<uint32_t>(d.bh), static_cast<uint32_t>(d.bn)};
+    if (int e = nhwc_map(&d.tmO, h.out, n_out, h.ldc, esz, boxO, f32)) return e;
+    if (res)
+      if (int e = nhwc_map(&d.tmR, h.residual, n_out, h.ldr, 2, boxO, false)) return e;
+  }
 
   const int smem_bytes = d.num_stages * stage_bytes + kEpiStageBytes + 1024;
-  if (!g_gemm_attr_set) {
-    B200SD_CUDA_CHECK(
-        cudaFuncSetAttribute(gemm_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, di.max_smem_optin - 512));
-    g_gemm_attr_set = true;
-  }
   const int num_tiles = d.tiles_m * d.tiles_ncol;
   const int grid = min(num_tiles, di.sm_count);
-  gemm_conv_kernel<<<grid, kGemmThreads, smem_bytes, stream>>>(d);
-  B200SD_CUDA_CHECK(cudaGetLastError());
-  return B200SD_OK;
+  (void)g_gemm_attr_set;
+  if (geglu) return launch_variant<false, true, false>(d, grid, smem_bytes, di.max_smem_optin, stream);
+  if (f32) return launch_variant<true, false, false>(d, grid, smem_bytes, di.max_smem_optin, stream);
+  if (res) return launch_variant<false, false, true>(d, grid, smem_bytes, di.max_smem_optin, stream);
+  return launch_variant<false, false, false>(d, grid, smem_bytes, di.max_smem_optin, stream);
 }

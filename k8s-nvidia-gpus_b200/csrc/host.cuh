@@ -39,6 +39,9 @@ int get_device_info(DeviceInfo* out);
 // dims/strides innermost first; strides[i] = byte stride of dim i+1 (rank-1 entries); act_t elements; 128B swizzle.
 int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const uint32_t* box);
+// same, fp32 elements (epilogue output maps)
+int encode_tmap_f32(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box);
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

@@ -38,7 +38,8 @@ def _rand(*shape, scale=1.0):
 
 
 @pytest.mark.parametrize("M,K,N,bn", [(128, 64, 128, 128), (300, 320, 200, 0), (16, 1280, 1280, 0),
-                                      (1232, 768, 640, 0), (4096, 320, 960, 0), (513, 72, 40, 32)])
+                                      (1232, 768, 640, 0), (4096, 320, 960, 0), (513, 72, 40, 64),
+                                      (700, 320, 320, 0), (2048, 640, 200, 128)])
 def test_linear(cuda_lib, b200sd, M, K, N, bn):
     torch.manual_seed(0)
     ops = b200sd.ops
