@@ -187,25 +187,33 @@ def flops_of_call(call):
 
 def profile_plan(plan, blocker=None):
     """Per-launch device time with CUDA events on the launching stream.  A long-running `blocker` plan is enqueued
-    first so the host runs ahead of the GPU and launch latency does not leak into the per-kernel intervals."""
+    first so the host runs ahead of the GPU and launch latency does not leak into the per-kernel intervals; the
+    event-to-event gap of an EMPTY interval (measured the same way, right after) is subtracted from every interval."""
     from b200sd import ops
     s = ops.current_stream()
     n = len(plan.calls)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+    cal = [torch.cuda.Event(enable_timing=True) for _ in range(65)]
     if blocker is not None:
-        blocker.run()
+        for _ in range(8):  # ~0.2 s of queued GPU work: the host stays ahead for the whole instrumented pass
+            blocker.run()
     ev[0].record()
     for i, c in enumerate(plan.calls):
         c(s)
         ev[i + 1].record()
+    for e in cal:
+        e.record()
     torch.cuda.synchronize()
+    gaps = sorted(cal[i].elapsed_time(cal[i + 1]) for i in range(64))
+    gap = gaps[len(gaps) // 2]
     agg = {}
     for i, c in enumerate(plan.calls):
         fl, kind = flops_of_call(c)
         a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0})
         a["launches"] += 1
-        a["ms"] += ev[i].elapsed_time(ev[i + 1])
+        a["ms"] += max(0.0, ev[i].elapsed_time(ev[i + 1]) - gap)
         a["flops"] += fl
+    agg["_event_gap_ms"] = gap
     return agg
 
 
@@ -315,6 +323,8 @@ def run_cuda(args):
     job.reset()
     prof = profile_plan(job.step_plan, blocker=job.vae_plan)
     vprof = profile_plan(job.vae_plan, blocker=job.vae_plan)
+    event_gap_ms = prof.pop("_event_gap_ms")
+    vprof.pop("_event_gap_ms")
     peaks = measured_peaks()
     gm = prof["gemm"]
     achieved_tf = gm["flops"] / (gm["ms"] * 1e-3) / 1e12
@@ -365,6 +375,7 @@ def run_cuda(args):
         "gpu_launches": args.steps * job.launches(evals),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "unet_step_breakdown": breakdown, "vae_breakdown": vae_breakdown,
+        "breakdown_note": f"CUDA-event intervals of an eager pass minus the empty-interval gap ({event_gap_ms * 1e3:.1f} us)",
         "device": {"sm_count": info["sm_count"], "cc": list(info["cc"])},
     }
     print(json.dumps(line))

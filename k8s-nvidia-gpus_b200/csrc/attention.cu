@@ -11,9 +11,10 @@
 //                       consumed in place as an MN-major B operand.  S_t(j+1) is issued as soon as warpgroup t has
 //                       consumed S_t(j), before P_t(j) V(j), so the two warpgroups and the tensor pipe ping-pong.
 //   warp 2            : TMEM allocator.
-//   warps 4..7 / 8..11: softmax warpgroup 0 / 1 (thread = query row).  Pass 1: tcgen05.ld S -> row max.  Pass 2:
-//                       tcgen05.ld S again -> exp2 (packed ex2.f16x2 in the fp16 build; the result IS the packed P)
-//                       -> swizzled shared memory.  Lazy rescale of O in TMEM; final normalisation and store.
+//   warps 4..7 / 8..11: softmax warpgroup 0 / 1 (thread = query row).  One pass per KV tile: tcgen05.ld S (next
+//                       chunk in flight) -> p = exp2(s * scale - ref) against a lazily updated reference (exact row
+//                       max of the first tile; moved, with a rescale of O in TMEM, only when a later score overshoots
+//                       it by 2^8) -> 16-bit P -> swizzled shared memory.  Final normalisation and store.
 //   Row sums: when the head dim leaves a spare UMMA column (d = 40 -> N = 48) column d of every V tile is set to
 //   1.0 after the TMA lands, so the tensor pipe accumulates sum_j P_ij in fp32 as column d of O for free (and it is
 //   rescaled together with O); otherwise the sum is accumulated in registers.
@@ -46,26 +47,6 @@ __device__ __forceinline__ float ex2f(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
-}
-
-// p = 2^(s * scale - mb) for two scores, packed as two act_t (the P operand layout); adds p0 + p1 to `sum` when asked
-template <bool kSum>
-__device__ __forceinline__ uint32_t exp2_pack(float s0, float s1, float scale, float mb, float& sum) {
-  const float x0 = fmaf(s0, scale, -mb), x1 = fmaf(s1, scale, -mb);
-#ifdef B200SD_ACT_BF16
-  const float p0 = ex2f(x0), p1 = ex2f(x1);
-  if (kSum) sum += p0 + p1;
-  return pack_act2(p0, p1);
-#else
-  uint32_t xh, ph;
-  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(xh) : "f"(x1), "f"(x0));
-  asm("ex2.approx.f16x2 %0, %1;" : "=r"(ph) : "r"(xh));
-  if (kSum) {
-    const float2 pf = unpack_act2(ph);
-    sum += pf.x + pf.y;
-  }
-  return ph;
-#endif
 }
 
 template <bool kOnes>
@@ -200,7 +181,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       const uint32_t tO = tO_base + t * 128 + lane_off;
       const uint32_t sPt = sP + t * 2 * kAtomBytes + r * 128;
       constexpr bool ones_col = kOnes;
-      float m_run = -INFINITY;
+      float mb = 0.f;      // reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
       float l_run = 0.f;
       for (int j = 0; j < T; ++j) {
         const int col0 = j * kBKV;
@@ -209,85 +190,79 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
         mbar_wait(smem_u32(&s_full[t]), j & 1);
         tc_fence_after();
-        // ---- pass 1: row max (next chunk's tcgen05.ld is in flight while the current one is reduced)
-        float mx = -INFINITY;
-        {
-          uint32_t sv[2][32];
-          tmem_ld32(tS, sv[0]);
-          tmem_ld_wait();
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (c < 3) tmem_ld32(tS + (c + 1) * 32, sv[(c + 1) & 1]);
-            const uint32_t(&cur)[32] = sv[c & 1];
-            if (need_mask) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < limit) ? __uint_as_float(cur[i]) : -INFINITY);
-            } else {
-              float m0 = mx, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
-#pragma unroll
-              for (int i = 0; i < 32; i += 4) {
-                m0 = fmaxf(m0, __uint_as_float(cur[i]));
-                m1 = fmaxf(m1, __uint_as_float(cur[i + 1]));
-                m2 = fmaxf(m2, __uint_as_float(cur[i + 2]));
-                m3 = fmaxf(m3, __uint_as_float(cur[i + 3]));
-              }
-              mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-            }
-            if (c < 3) tmem_ld_wait();
-          }
-        }
-        const float m_new = fmaxf(m_run, mx);
-        const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-        const float alpha = ex2f((m_run - m_use) * p.scale_log2);  // m_run = -inf -> 0
-        const float mb = m_use * p.scale_log2;
-        m_run = m_new;
-        // P_t(j-1) V(j-1) must have completed before P smem is overwritten / O is rescaled
         if (j > 0) {
+          // P_t(j-1) V(j-1) must have completed before P smem is overwritten / O is rescaled
           mbar_wait(smem_u32(&pv_done[t]), (j - 1) & 1);
           tc_fence_after();
         }
-        // ---- pass 2: exponentials -> P (packed 16-bit) -> swizzled smem (TMEM loads pipelined as in pass 1)
-        float psum = 0.f;
-        {
-          uint32_t sv[2][32];
-          tmem_ld32(tS, sv[0]);
-          tmem_ld_wait();
-#pragma unroll
-          for (int c = 0; c < 4; ++c) {
-            if (c < 3) tmem_ld32(tS + (c + 1) * 32, sv[(c + 1) & 1]);
-            uint32_t(&cur)[32] = sv[c & 1];
+        // Single pass per tile: exponentials against the CURRENT reference while the tile's own max is tracked.  The
+        // reference (0 at the start) only moves - with a rescale of O / l - when the tile max overshoots it by more
+        // than 2^kTau (or, on the first tile, undershoots it by as much); p <= 2^kTau stays far inside fp16 range and
+        // the sums are fp32.  The pass is then redone once.
+        constexpr float kTau = 8.f;
+        for (int attempt = 0; attempt < 2; ++attempt) {
+          float psum = 0.f;
+          float m0 = -INFINITY, m1 = -INFINITY;
+          uint32_t bufA[32], bufB[32];
+          // 32 scores -> exp2 -> 16-bit P -> 4 swizzled 16-byte chunks of my row
+          auto process = [&](uint32_t(&cur)[32], int c) {
             if (need_mask) {
 #pragma unroll
               for (int i = 0; i < 32; ++i)
                 if (c * 32 + i >= limit) cur[i] = __float_as_uint(-INFINITY);
             }
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte chunk
+            for (int g = 0; g < 4; ++g) {
               uint32_t w[4];
 #pragma unroll
-              for (int e = 0; e < 4; ++e)
-                w[e] = exp2_pack<!ones_col>(__uint_as_float(cur[g * 8 + 2 * e]), __uint_as_float(cur[g * 8 + 2 * e + 1]),
-                                            p.scale_log2, mb, psum);
+              for (int e = 0; e < 4; ++e) {
+                const float s0 = __uint_as_float(cur[g * 8 + 2 * e]), s1 = __uint_as_float(cur[g * 8 + 2 * e + 1]);
+                m0 = fmaxf(m0, s0);
+                m1 = fmaxf(m1, s1);
+                const float p0 = ex2f(fmaf(s0, p.scale_log2, -mb)), p1 = ex2f(fmaf(s1, p.scale_log2, -mb));
+                if (!ones_col) psum += p0 + p1;
+                w[e] = pack_act2(p0, p1);
+              }
               const int c16 = c * 4 + g;
               const uint32_t addr = sPt + (c16 >> 3) * kAtomBytes + (((c16 & 7) ^ (r & 7)) << 4);
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]),
                            "r"(w[3])
                            : "memory");
             }
-            if (c < 3) tmem_ld_wait();
-          }
-        }
-        l_run = l_run * alpha + psum;
-        if (j > 0 && __any_sync(0xffffffffu, alpha != 1.f)) {
-          for (int c = 0; c < p.dN; c += 16) {
-            uint32_t o[16];
-            tmem_ld16(tO + c, o);
+          };
+          tmem_ld32(tS, bufA);
+          tmem_ld_wait();
+#pragma unroll 1
+          for (int i = 0; i < 2; ++i) {  // chunk pairs; the next chunk's tcgen05.ld is in flight during the maths
+            tmem_ld32(tS + (2 * i + 1) * 32, bufB);
+            process(bufA, 2 * i);
             tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st16(tO + c, o);
+            if (i == 0) tmem_ld32(tS + 64, bufA);
+            process(bufB, 2 * i + 1);
+            if (i == 0) tmem_ld_wait();
           }
-          tmem_st_wait();
+          const float xmax = fmaf(fmaxf(m0, m1), p.scale_log2, -mb);  // -inf when the whole row is masked
+          const bool exceed = (xmax > kTau) || (j == 0 && xmax < -kTau && xmax != -INFINITY);
+          if (!__any_sync(0xffffffffu, exceed)) {
+            l_run += psum;
+            break;
+          }
+          // rare: move the reference of the rows that over/undershot, rescale their O / l, redo the pass once
+          const float delta = exceed ? xmax : 0.f;
+          const float alpha = ex2f(-delta);
+          mb += delta;
+          l_run *= alpha;
+          if (j > 0) {
+            for (int c = 0; c < p.dN; c += 16) {
+              uint32_t o[16];
+              tmem_ld16(tO + c, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st16(tO + c, o);
+            }
+            tmem_st_wait();
+          }
         }
         if (ones_col && t == 0) {
           // V(j) has landed: set column `sum_col` of kv row r to 1.0 so O[:, sum_col] accumulates the row sums
