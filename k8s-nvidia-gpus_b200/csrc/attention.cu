@@ -1,20 +1,22 @@
 // Flash attention forward on tcgen05 (sm_100a): out = softmax(Q K^T * scale [+ causal]) V per (batch, head).
 // SURVEY §2.1 K5 (self-attention), K6 (cross-attention, nk = 77), K15 (CLIP causal attention).
 //
-// One CTA per (up to two 128-query tiles, head, batch); 12 warps:
+// One CTA per (up to two 128-query tiles, head, batch); keys are walked in tiles of 64; 12 warps:
 //   warp 0 (1 thread) : TMA producer.  Q/K/V are read straight out of the projection GEMM outputs through 4-D
 //                       tensor maps {d, head, token, batch}; the box is 64 wide in d, so head dims that are not a
 //                       multiple of 64 (40, 80, 160) and ragged token counts are zero-filled by the TMA unit —
 //                       no padded copies of Q/K/V exist in HBM.  K/V tiles are shared by both query tiles.
-//   warp 1 (1 thread) : tcgen05.mma issuer.  S_t = Q_t K^T (K-major A and B) into TMEM; O_t += P_t V with P_t
-//                       (16-bit, written by softmax warpgroup t) as the K-major A operand in shared memory and V
-//                       consumed in place as an MN-major B operand.  S_t(j+1) is issued as soon as warpgroup t has
-//                       consumed S_t(j), before P_t(j) V(j), so the two warpgroups and the tensor pipe ping-pong.
+//   warps 1, 3 (1 thread each): tcgen05.mma issuer of query tile 0 / 1.  S_t = Q_t K^T (K-major A and B) into a DOUBLE-BUFFERED TMEM tile per
+//                       query tile; O_t += P_t V with P_t (16-bit, written by softmax warpgroup t, double-buffered in
+//                       shared memory) as the K-major A operand and V consumed in place as an MN-major B operand.
+//                       S_t(j+2) is issued the moment warpgroup t has consumed S_t(j): the softmax warps never wait
+//                       for the tensor pipe's round trip, and the tensor pipe never waits for the softmax of the tile
+//                       it just produced.
 //   warp 2            : TMEM allocator.
 //   warps 4..7 / 8..11: softmax warpgroup 0 / 1 (thread = query row).  One pass per KV tile: tcgen05.ld S (next
-//                       chunk in flight) -> p = exp2(s * scale - ref) against a lazily updated reference (exact row
-//                       max of the first tile; moved, with a rescale of O in TMEM, only when a later score overshoots
-//                       it by 2^8) -> 16-bit P -> swizzled shared memory.  Final normalisation and store.
+//                       chunk in flight) -> p = exp2(s * scale - ref) against a lazily updated reference (moved,
+//                       with a rescale of O in TMEM, only when the tile max overshoots it by 2^8) -> 16-bit P ->
+//                       swizzled shared memory.  Final normalisation and store.
 //   Row sums: when the head dim leaves a spare UMMA column (d = 40 -> N = 48) column d of every V tile is set to
 //   1.0 after the TMA lands, so the tensor pipe accumulates sum_j P_ij in fp32 as column d of O for free (and it is
 //   rescaled together with O); otherwise the sum is accumulated in registers.
@@ -24,9 +26,11 @@
 namespace b200sd {
 
 static constexpr int kAttThreads = 384;
-static constexpr int kBQ = 128;   // query rows per tile (UMMA M)
-static constexpr int kBKV = 128;  // keys per tile
-static constexpr uint32_t kAtomBytes = 128 * 128;  // 128 rows x 64 elements, one swizzle-128B atom column
+static constexpr int kBQ = 128;  // query rows per tile (UMMA M)
+static constexpr int kBKV = 64;  // keys per tile
+static constexpr uint32_t kQAtom = 128 * 128;   // Q / P: 128 rows x 64 elements (one swizzle-128B atom column)
+static constexpr uint32_t kKVAtom = kBKV * 128;  // K / V: 64 rows x 64 elements
+static constexpr int kMaxStages = 4;
 
 struct alignas(64) AttnDev {
   CUtensorMap tmQ, tmK, tmV;
@@ -35,9 +39,10 @@ struct alignas(64) AttnDev {
   int ldo;
   int nd;         // 64-wide d atoms
   int dN;         // UMMA N of the PV product / K extent of QK^T (d rounded up to 16)
-  int stages;     // K/V ring depth (1 or 2)
+  int stages;     // K/V ring depth
   int qtiles;     // query tiles per CTA (1 or 2)
-  int tmem_cols;
+  int o_col;      // first TMEM column of O_0
+  int o_stride;   // TMEM column stride between O_0 and O_1
   int sum_col;    // >= 0: column of O that accumulates the row sums (ones column in V); -1: register sums
   int causal;
   float scale_log2;
@@ -53,8 +58,8 @@ template <bool kOnes>
 __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_constant__ AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t q_full;
-  __shared__ __align__(8) uint64_t s_full[2], p_full[2], pv_done[2];
-  __shared__ __align__(8) uint64_t k_full[2], v_full[2], k_empty[2], v_empty[2];
+  __shared__ __align__(8) uint64_t s_full[2][2], p_full[2][2], pv_done[2][2];  // [query tile][buffer]
+  __shared__ __align__(8) uint64_t k_full[kMaxStages], v_full[kMaxStages], k_empty[kMaxStages], v_empty[kMaxStages];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -63,11 +68,12 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   const int b = blockIdx.z;
   const int ntiles = (p.qtiles == 2 && q0 + kBQ < p.nq) ? 2 : 1;  // query tiles this CTA really has
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t tile_bytes = p.nd * kAtomBytes;
-  const uint32_t sQ = base;                                   // [qtiles][nd atoms]
-  const uint32_t sK = sQ + p.qtiles * tile_bytes;             // [stages][nd atoms]
-  const uint32_t sV = sK + p.stages * tile_bytes;             // [stages][nd atoms]
-  const uint32_t sP = sV + p.stages * tile_bytes;             // [qtiles][2 atoms]
+  const uint32_t q_bytes = p.nd * kQAtom;
+  const uint32_t kv_bytes = p.nd * kKVAtom;
+  const uint32_t sQ = base;                          // [qtiles][nd atoms of 16 KB]
+  const uint32_t sK = sQ + p.qtiles * q_bytes;       // [stages][nd atoms of 8 KB]
+  const uint32_t sV = sK + p.stages * kv_bytes;      // [stages][nd atoms of 8 KB]
+  const uint32_t sP = sV + p.stages * kv_bytes;      // [qtiles][2 buffers][16 KB]
   int kv_end = p.nk;
   if (p.causal) kv_end = min(p.nk, q0 + kBQ * ntiles);  // keys beyond the last query row are fully masked
   const int T = (kv_end + kBKV - 1) / kBKV;
@@ -79,93 +85,111 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   }
   if (warp == 1 && lane == 0) {
     mbar_init(smem_u32(&q_full), 1);
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(smem_u32(&s_full[s]), 1);
-      mbar_init(smem_u32(&p_full[s]), 128);
-      mbar_init(smem_u32(&pv_done[s]), 1);
+    for (int t = 0; t < 2; ++t)
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(smem_u32(&s_full[t][i]), 1);
+        mbar_init(smem_u32(&p_full[t][i]), 128);
+        mbar_init(smem_u32(&pv_done[t][i]), 1);
+      }
+    for (int s = 0; s < kMaxStages; ++s) {
       mbar_init(smem_u32(&k_full[s]), 1);
       mbar_init(smem_u32(&v_full[s]), 1);
-      mbar_init(smem_u32(&k_empty[s]), 1);
-      mbar_init(smem_u32(&v_empty[s]), 1);
+      mbar_init(smem_u32(&k_empty[s]), ntiles);  // one tcgen05.commit per MMA issuer (one issuer per query tile)
+      mbar_init(smem_u32(&v_empty[s]), ntiles);
     }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(smem_u32(&tmem_base_s), p.tmem_cols);
+  if (warp == 2) tmem_alloc(smem_u32(&tmem_base_s), 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
-  // TMEM columns: S_t at t*128; O_t after the S block(s)
-  const uint32_t tO_base = tmem_base + p.qtiles * 128;
+  // TMEM columns: S_t[buf] at (2t + buf) * 64; O_t at o_col + t * o_stride
 
   if (warp == 0) {
     if (lane == 0) {
       // ---------------------------------------------------------------- TMA producer
-      mbar_arrive_expect_tx(smem_u32(&q_full), ntiles * tile_bytes);
+      mbar_arrive_expect_tx(smem_u32(&q_full), ntiles * q_bytes);
       for (int t = 0; t < ntiles; ++t)
         for (int a = 0; a < p.nd; ++a)
-          tma_load_4d(sQ + t * tile_bytes + a * kAtomBytes, &p.tmQ, smem_u32(&q_full), a * 64, head, q0 + t * kBQ, b);
+          tma_load_4d(sQ + t * q_bytes + a * kQAtom, &p.tmQ, smem_u32(&q_full), a * 64, head, q0 + t * kBQ, b);
+      int st = 0;
+      uint32_t ph = 1;
       for (int j = 0; j < T; ++j) {
-        const int st = j % p.stages;
-        const uint32_t ph = ((j / p.stages) & 1) ^ 1u;
         mbar_wait(smem_u32(&k_empty[st]), ph);
-        mbar_arrive_expect_tx(smem_u32(&k_full[st]), tile_bytes);
+        mbar_arrive_expect_tx(smem_u32(&k_full[st]), kv_bytes);
         for (int a = 0; a < p.nd; ++a)
-          tma_load_4d(sK + st * tile_bytes + a * kAtomBytes, &p.tmK, smem_u32(&k_full[st]), a * 64, head, j * kBKV, b);
+          tma_load_4d(sK + st * kv_bytes + a * kKVAtom, &p.tmK, smem_u32(&k_full[st]), a * 64, head, j * kBKV, b);
         mbar_wait(smem_u32(&v_empty[st]), ph);
-        mbar_arrive_expect_tx(smem_u32(&v_full[st]), tile_bytes);
+        mbar_arrive_expect_tx(smem_u32(&v_full[st]), kv_bytes);
         for (int a = 0; a < p.nd; ++a)
-          tma_load_4d(sV + st * tile_bytes + a * kAtomBytes, &p.tmV, smem_u32(&v_full[st]), a * 64, head, j * kBKV, b);
+          tma_load_4d(sV + st * kv_bytes + a * kKVAtom, &p.tmV, smem_u32(&v_full[st]), a * 64, head, j * kBKV, b);
+        if (++st == p.stages) {
+          st = 0;
+          ph ^= 1u;
+        }
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      // ---------------------------------------------------------------- MMA issuer
-      const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 128] = Q (K-major) x K (K-major)
+  } else if (warp == 1 || warp == 3) {
+    const int t = warp >> 1;  // warp 1 issues for query tile 0, warp 3 for query tile 1
+    if (lane == 0 && t < ntiles) {
+      // ---------------------------------------------------------------- MMA issuer of query tile t
+      // Descriptors are built once; the loop only adds 16-byte-unit offsets to their low words.  K and V stages are
+      // consumed strictly in order, so each ring is tracked by a running (stage, phase) pair - no divisions.
+      const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 64] = Q (K-major) x K (K-major)
       const uint32_t idesc_o = make_idesc_f16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
       const int ksteps_s = p.dN / 16;
-      auto issue_s = [&](int t, int j) {  // caller has waited for K_j
-        const int st = j % p.stages;
+      const uint64_t dQ = make_smem_desc_sw128(sQ + t * q_bytes, 16, 1024);
+      const uint64_t dK = make_smem_desc_sw128(sK, 16, 1024);
+      const uint64_t dV = make_smem_desc_sw128(sV, kKVAtom, 1024);  // MN-major: atoms kKVAtom apart
+      const uint64_t dP = make_smem_desc_sw128(sP + 2 * t * kQAtom, 16, 1024);
+      const uint32_t kv_u = kv_bytes >> 4;
+      const uint32_t tS0 = tmem_base + 2 * t * 64;
+      const uint32_t tOt = tmem_base + p.o_col + t * p.o_stride;
+      int kst = 0, vst = 0;
+      uint32_t kph = 0, vph = 0;
+      // S_t(jj) into buffer jj & 1 from the current K stage
+      auto issue_s = [&](int bfs) {
+        const uint64_t b0 = dK + kst * kv_u;
         for (int s = 0; s < ksteps_s; ++s) {
-          const uint32_t off = (s >> 2) * kAtomBytes + (s & 3) * 32;
-          const uint64_t adesc = make_smem_desc_sw128(sQ + t * tile_bytes + off, 16, 1024);
-          const uint64_t bdesc = make_smem_desc_sw128(sK + st * tile_bytes + off, 16, 1024);
-          umma_f16_ss(tmem_base + t * 128, adesc, bdesc, idesc_s, s != 0);
+          const uint32_t in_atom = (s & 3) * 2;
+          umma_f16_ss(tS0 + bfs * 64, dQ + (s >> 2) * (kQAtom >> 4) + in_atom, b0 + (s >> 2) * (kKVAtom >> 4) + in_atom,
+                      idesc_s, s != 0);
         }
-        umma_commit(smem_u32(&s_full[t]));
+        umma_commit(smem_u32(&s_full[t][bfs]));
+        umma_commit(smem_u32(&k_empty[kst]));
+        if (++kst == p.stages) {
+          kst = 0;
+          kph ^= 1u;
+        }
       };
-      mbar_wait(smem_u32(&q_full), 0);
-      mbar_wait(smem_u32(&k_full[0]), 0);
-      tc_fence_after();
-      for (int t = 0; t < ntiles; ++t) issue_s(t, 0);
-      umma_commit(smem_u32(&k_empty[0]));
+      mbar_wait_spin(smem_u32(&q_full), 0);
+      for (int jj = 0; jj < 2 && jj < T; ++jj) {  // prologue: both S buffers
+        mbar_wait_spin(smem_u32(&k_full[kst]), kph);
+        tc_fence_after();
+        issue_s(jj);
+      }
       for (int j = 0; j < T; ++j) {
-        const int st = j % p.stages;
-        for (int t = 0; t < ntiles; ++t) {
-          mbar_wait(smem_u32(&p_full[t]), j & 1);  // S_t(j) consumed, P_t(j) in smem, O_t rescaled
+        const int bf = j & 1;
+        mbar_wait_spin(smem_u32(&p_full[t][bf]), (j >> 1) & 1);  // P_t(j) in smem; S_t buffer bf consumed
+        tc_fence_after();
+        if (j + 2 < T) {
+          mbar_wait_spin(smem_u32(&k_full[kst]), kph);
           tc_fence_after();
-          if (j + 1 < T) {
-            if (t == 0) {
-              mbar_wait(smem_u32(&k_full[(j + 1) % p.stages]), ((j + 1) / p.stages) & 1);
-              tc_fence_after();
-            }
-            issue_s(t, j + 1);
-            if (t == ntiles - 1) umma_commit(smem_u32(&k_empty[(j + 1) % p.stages]));
-          }
-          if (t == 0) {
-            mbar_wait(smem_u32(&v_full[st]), (j / p.stages) & 1);
-            tc_fence_after();
-          }
+          issue_s(bf);
+        }
+        mbar_wait_spin(smem_u32(&v_full[vst]), vph);
+        tc_fence_after();
+        const uint64_t a0 = dP + bf * (kQAtom >> 4);
+        const uint64_t b0 = dV + vst * kv_u;
 #pragma unroll
-          for (int s = 0; s < kBKV / 16; ++s) {
-            const uint64_t adesc =
-                make_smem_desc_sw128(sP + t * 2 * kAtomBytes + (s >> 2) * kAtomBytes + (s & 3) * 32, 16, 1024);
-            // V tile: [kv rows at 128 B pitch][64 d per atom]; 16 kv rows per step = 2048 B; atoms kAtomBytes apart
-            const uint64_t bdesc = make_smem_desc_sw128(sV + st * tile_bytes + s * 2048, kAtomBytes, 1024);
-            umma_f16_ss(tO_base + t * 128, adesc, bdesc, idesc_o, (j | s) != 0);
-          }
-          if (t == ntiles - 1) umma_commit(smem_u32(&v_empty[st]));
-          umma_commit(smem_u32(&pv_done[t]));
+        for (int s = 0; s < kBKV / 16; ++s)  // 16 kv rows per step: +32 B along P's K, +2048 B down V's rows
+          umma_f16_ss(tOt, a0 + s * 2, b0 + s * 128, idesc_o, (j | s) != 0);
+        umma_commit(smem_u32(&v_empty[vst]));
+        umma_commit(smem_u32(&pv_done[t][bf]));
+        if (++vst == p.stages) {
+          vst = 0;
+          vph ^= 1u;
         }
       }
     }
@@ -177,23 +201,25 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       const int r = qd * 32 + lane;  // row in tile == TMEM lane
       const int qrow = q0 + t * kBQ + r;
       const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
-      const uint32_t tS = tmem_base + t * 128 + lane_off;
-      const uint32_t tO = tO_base + t * 128 + lane_off;
-      const uint32_t sPt = sP + t * 2 * kAtomBytes + r * 128;
+      const uint32_t tO = tmem_base + p.o_col + t * p.o_stride + lane_off;
       constexpr bool ones_col = kOnes;
-      float mb = 0.f;      // reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
+      float mb = 0.f;  // reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
+      int vst = 0;     // V ring position (ones-column writer)
+      uint32_t vph = 0;
       float l_run = 0.f;
       for (int j = 0; j < T; ++j) {
+        const int bf = j & 1;
+        const uint32_t tS = tmem_base + (2 * t + bf) * 64 + lane_off;
+        const uint32_t sPt = sP + (2 * t + bf) * kQAtom + r * 128;
         const int col0 = j * kBKV;
         int limit = p.nk - col0;  // valid columns: [0, limit)
         if (p.causal) limit = min(limit, qrow - col0 + 1);
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
-        mbar_wait(smem_u32(&s_full[t]), j & 1);
+        mbar_wait_spin(smem_u32(&s_full[t][bf]), (j >> 1) & 1);
         tc_fence_after();
-        if (j > 0) {
-          // P_t(j-1) V(j-1) must have completed before P smem is overwritten / O is rescaled
-          mbar_wait(smem_u32(&pv_done[t]), (j - 1) & 1);
-          tc_fence_after();
+        if (j >= 2) {
+          // P_t(j-2) V(j-2) has been consumed: P buffer bf may be overwritten
+          mbar_wait_spin(smem_u32(&pv_done[t][bf]), ((j >> 1) - 1) & 1);
         }
         // Single pass per tile: exponentials against the CURRENT reference while the tile's own max is tracked.  The
         // reference (0 at the start) only moves - with a rescale of O / l - when the tile max overshoots it by more
@@ -224,23 +250,17 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
                 w[e] = pack_act2(p0, p1);
               }
               const int c16 = c * 4 + g;
-              const uint32_t addr = sPt + (c16 >> 3) * kAtomBytes + (((c16 & 7) ^ (r & 7)) << 4);
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w[0]), "r"(w[1]), "r"(w[2]),
-                           "r"(w[3])
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((c16 ^ (r & 7)) << 4)), "r"(w[0]),
+                           "r"(w[1]), "r"(w[2]), "r"(w[3])
                            : "memory");
             }
           };
           tmem_ld32(tS, bufA);
           tmem_ld_wait();
-#pragma unroll 1
-          for (int i = 0; i < 2; ++i) {  // chunk pairs; the next chunk's tcgen05.ld is in flight during the maths
-            tmem_ld32(tS + (2 * i + 1) * 32, bufB);
-            process(bufA, 2 * i);
-            tmem_ld_wait();
-            if (i == 0) tmem_ld32(tS + 64, bufA);
-            process(bufB, 2 * i + 1);
-            if (i == 0) tmem_ld_wait();
-          }
+          tmem_ld32(tS + 32, bufB);  // in flight during the first half's maths
+          process(bufA, 0);
+          tmem_ld_wait();
+          process(bufB, 1);
           const float xmax = fmaf(fmaxf(m0, m1), p.scale_log2, -mb);  // -inf when the whole row is masked
           const bool exceed = (xmax > kTau) || (j == 0 && xmax < -kTau && xmax != -INFINITY);
           if (!__any_sync(0xffffffffu, exceed)) {
@@ -253,6 +273,9 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           mb += delta;
           l_run *= alpha;
           if (j > 0) {
+            // O must hold every product up to tile j-1
+            mbar_wait(smem_u32(&pv_done[t][bf ^ 1]), ((j - 1) >> 1) & 1);
+            tc_fence_after();
             for (int c = 0; c < p.dN; c += 16) {
               uint32_t o[16];
               tmem_ld16(tO + c, o);
@@ -264,22 +287,27 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
             tmem_st_wait();
           }
         }
-        if (ones_col && t == 0) {
-          // V(j) has landed: set column `sum_col` of kv row r to 1.0 so O[:, sum_col] accumulates the row sums
-          const int st = j % p.stages;
-          mbar_wait(smem_u32(&v_full[st]), (j / p.stages) & 1);
-          const int sc = p.sum_col;
-          const uint32_t va = sV + st * tile_bytes + (sc >> 6) * kAtomBytes + r * 128 +
-                              (((((sc & 63) >> 3)) ^ (r & 7)) << 4) + (sc & 7) * 2;
-          const act_t one = to_act(1.f);
-          asm volatile("st.shared.b16 [%0], %1;" ::"r"(va), "h"(*reinterpret_cast<const uint16_t*>(&one)) : "memory");
+        if (ones_col) {
+          // V(j) has landed: set column `sum_col` of its 64 kv rows to 1.0 so O[:, sum_col] accumulates the row sums
+          mbar_wait_spin(smem_u32(&v_full[vst]), vph);
+          if (r < kBKV) {
+            const int sc = p.sum_col;
+            const uint32_t va = sV + vst * kv_bytes + (sc >> 6) * kKVAtom + r * 128 +
+                                (((((sc & 63) >> 3)) ^ (r & 7)) << 4) + (sc & 7) * 2;
+            const act_t one = to_act(1.f);
+            asm volatile("st.shared.b16 [%0], %1;" ::"r"(va), "h"(*reinterpret_cast<const uint16_t*>(&one)) : "memory");
+          }
+          if (++vst == p.stages) {
+            vst = 0;
+            vph ^= 1u;
+          }
         }
         fence_proxy_async_smem();
         tc_fence_before();
-        mbar_arrive(smem_u32(&p_full[t]));
+        mbar_arrive(smem_u32(&p_full[t][bf]));
       }
-      // final: O / l -> 16-bit -> global
-      mbar_wait(smem_u32(&pv_done[t]), (T - 1) & 1);
+      // final: O / l -> 16-bit -> global (the last commit covers every earlier MMA)
+      mbar_wait(smem_u32(&pv_done[t][(T - 1) & 1]), ((T - 1) >> 1) & 1);
       tc_fence_after();
       act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
       float inv_l = 1.f / l_run;
@@ -318,7 +346,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, p.tmem_cols);
+    tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -359,26 +387,31 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   d.nd = ceil_div(h.d, 64);
   d.dN = ceil_div(h.d, 16) * 16;
   d.qtiles = (d.dN <= 128 && h.nq > kBQ) ? 2 : 1;
-  d.stages = (d.nd == 1) ? 2 : ((d.qtiles == 1 && d.nd == 2) ? 2 : 1);
-  d.tmem_cols = (d.qtiles == 2) ? 512 : ((128 + d.dN <= 256) ? 256 : 512);
+  // TMEM: S double-buffered per query tile (64 columns each), then the O accumulators
+  d.o_col = d.qtiles * 128;
+  d.o_stride = 128;
   d.sum_col = (d.dN > h.d) ? h.d : -1;
   d.causal = h.causal;
   d.scale_log2 = h.scale * 1.4426950408889634f;
+  // shared memory: Q + 2 P buffers per query tile are fixed; K/V rings take what is left (at most 4 stages)
+  const int fixed = d.qtiles * (d.nd * static_cast<int>(kQAtom) + 2 * static_cast<int>(kQAtom)) + 1024;
+  const int per_stage = 2 * d.nd * static_cast<int>(kKVAtom);
+  d.stages = min(kMaxStages, (di.max_smem_optin - 1024 - fixed) / per_stage);
+  B200SD_REQUIRE(d.stages >= 2, B200SD_ERR_TOO_LARGE, "attention: shared memory budget");
 
-  auto enc = [&](CUtensorMap* tm, const void* ptr, int rows, int ld) -> int {
+  auto enc = [&](CUtensorMap* tm, const void* ptr, int rows, int ld, uint32_t box_rows) -> int {
     const uint64_t dims[4] = {static_cast<uint64_t>(h.d), static_cast<uint64_t>(h.heads), static_cast<uint64_t>(rows),
                               static_cast<uint64_t>(h.batch)};
     const uint64_t st[3] = {static_cast<uint64_t>(h.d) * 2, static_cast<uint64_t>(ld) * 2,
                             static_cast<uint64_t>(ld) * 2 * rows};
-    const uint32_t box[4] = {64, 1, 128, 1};
+    const uint32_t box[4] = {64, 1, box_rows, 1};
     return encode_tmap_act(tm, ptr, 4, dims, st, box);
   };
-  if (int e = enc(&d.tmQ, h.q, h.nq, h.ldq)) return e;
-  if (int e = enc(&d.tmK, h.k, h.nk, h.ldk)) return e;
-  if (int e = enc(&d.tmV, h.v, h.nk, h.ldv)) return e;
+  if (int e = enc(&d.tmQ, h.q, h.nq, h.ldq, kBQ)) return e;
+  if (int e = enc(&d.tmK, h.k, h.nk, h.ldk, kBKV)) return e;
+  if (int e = enc(&d.tmV, h.v, h.nk, h.ldv, kBKV)) return e;
 
-  const int smem_bytes = d.nd * kAtomBytes * (d.qtiles + 2 * d.stages) + d.qtiles * 2 * kAtomBytes + 1024;
-  B200SD_REQUIRE(smem_bytes <= di.max_smem_optin - 512, B200SD_ERR_TOO_LARGE, "attention: shared memory budget");
+  const int smem_bytes = fixed + d.stages * per_stage;
   if (!g_attn_attr_set) {
     B200SD_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            di.max_smem_optin - 512));

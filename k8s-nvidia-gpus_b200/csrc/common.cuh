@@ -50,27 +50,57 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// Cold path of every bounded wait, kept out of line so that wait sites stay a handful of instructions.
+static __device__ __noinline__ void mbar_timeout_trap(uint32_t bar, uint32_t parity) {
+  printf("b200sd: mbarrier wait timeout (block %d,%d,%d thread %d bar 0x%x parity %u)\n", blockIdx.x, blockIdx.y,
+         blockIdx.z, threadIdx.x, bar, parity);
+  __trap();
+}
+// One poll with a suspend-time hint: the hardware may park the thread while the phase is incomplete, so a waiting
+// warp burns almost no issue slots of the SM sub-partition it shares with working warps (long waits).
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
       "selp.b32 %0, 1, 0, p;\n"
       "}\n"
       : "=r"(done)
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(0x989680u)
       : "memory");
   return done != 0;
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
+  uint32_t polls = 0;
+  long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > B200SD_WAIT_TIMEOUT_CYCLES) {
-      printf("b200sd: mbarrier wait timeout (block %d,%d,%d thread %d bar 0x%x parity %u)\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x, bar, parity);
-      __trap();
+    // the wall-clock guard is evaluated once per 1024 polls
+    if (((++polls) & 1023u) == 0u) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > B200SD_WAIT_TIMEOUT_CYCLES) mbar_timeout_trap(bar, parity);
+    }
+  }
+}
+// Latency-critical variant: plain polling (no suspend hint -> no NANOSLEEP wake-up latency), same bounded guard.
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  uint32_t polls = 0;
+  long long t0 = 0;
+  for (;;) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.b32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (((++polls) & 4095u) == 0u) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > B200SD_WAIT_TIMEOUT_CYCLES) mbar_timeout_trap(bar, parity);
     }
   }
 }
