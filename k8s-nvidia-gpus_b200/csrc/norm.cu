@@ -104,6 +104,9 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: apply
+// Same thread -> (octet, pixel stream) mapping as the statistics pass: a thread normalises ONE 8-channel column, so its
+// 8 scales and 8 shifts live in registers for the whole walk (no per-element shared-memory lookups) and the inner
+// loop is load16 -> 8 fma (+SiLU) -> store16 with four pixels in flight.
 __global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const act_t* __restrict__ x0,
                                                                 const act_t* __restrict__ x1,
                                                                 const float* __restrict__ stats,
@@ -111,74 +114,103 @@ __global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const act_t* __r
                                                                 const float* __restrict__ beta, act_t* __restrict__ out,
                                                                 int hw, int c0, int c1, int groups, int pix_per_cta,
                                                                 int silu, float eps) {
-  extern __shared__ float ss[];  // scale[C], shift[C]
   const int n = blockIdx.y;
   const int C = c0 + c1;
   const int octs = C >> 3;
   const int cpg = C / groups;
-  float* scale = ss;
-  float* shift = ss + C;
   const float inv_cnt = 1.f / (static_cast<float>(hw) * static_cast<float>(cpg));
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const int g = c / cpg;
-    const float sum = stats[(static_cast<size_t>(n) * groups + g) * 2];
-    const float sq = stats[(static_cast<size_t>(n) * groups + g) * 2 + 1];
-    const float mean = sum * inv_cnt;
-    const float var = fmaxf(sq * inv_cnt - mean * mean, 0.f);
-    const float rstd = rsqrtf(var + eps);
-    const float sc = gamma[c] * rstd;
-    scale[c] = sc;
-    shift[c] = beta[c] - mean * sc;
-  }
-  __syncthreads();
   const int p_begin = blockIdx.x * pix_per_cta;
   const int p_end = min(hw, p_begin + pix_per_cta);
-  const int total = (p_end - p_begin) * octs;
-  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-    const int p = p_begin + idx / octs;
-    const int oct = idx - (idx / octs) * octs;
+  const int Wd = min(octs, kNormThreads);
+  const int S = kNormThreads / Wd;
+  const int stream = threadIdx.x / Wd;
+  if (stream >= S) return;
+  for (int oct = threadIdx.x % Wd; oct < octs; oct += Wd) {
     const int ch0 = oct * 8;
-    const act_t* src = (ch0 < c0) ? x0 + (static_cast<size_t>(n) * hw + p) * c0 + ch0
-                                 : x1 + (static_cast<size_t>(n) * hw + p) * c1 + (ch0 - c0);
-    float f[8];
-    load8(src, f);
+    float sc[8], sh[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      float y = fmaf(f[e], scale[ch0 + e], shift[ch0 + e]);
-      f[e] = silu ? silu_f(y) : y;
+      const int c = ch0 + e;
+      const int g = c / cpg;
+      const float2 st = *reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * groups + g) * 2);
+      const float mean = st.x * inv_cnt;
+      const float var = fmaxf(st.y * inv_cnt - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      sc[e] = __ldg(gamma + c) * rstd;
+      sh[e] = __ldg(beta + c) - mean * sc[e];
     }
-    store8(out + (static_cast<size_t>(n) * hw + p) * C + ch0, f);
+    const act_t* src;
+    int ld;
+    if (ch0 < c0) {
+      src = x0 + static_cast<size_t>(n) * hw * c0 + ch0;
+      ld = c0;
+    } else {
+      src = x1 + static_cast<size_t>(n) * hw * c1 + (ch0 - c0);
+      ld = c1;
+    }
+    act_t* dst = out + static_cast<size_t>(n) * hw * C + ch0;
+    int p = p_begin + stream;
+    for (; p + 3 * S < p_end; p += 4 * S) {
+      float f[4][8];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) load8(src + static_cast<size_t>(p + u * S) * ld, f[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float y = fmaf(f[u][e], sc[e], sh[e]);
+          f[u][e] = silu ? silu_f(y) : y;
+        }
+        store8(dst + static_cast<size_t>(p + u * S) * C, f[u]);
+      }
+    }
+    for (; p < p_end; p += S) {
+      float f[8];
+      load8(src + static_cast<size_t>(p) * ld, f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float y = fmaf(f[e], sc[e], sh[e]);
+        f[e] = silu ? silu_f(y) : y;
+      }
+      store8(dst + static_cast<size_t>(p) * C, f);
+    }
   }
 }
 
 // ---------------------------------------------------------------------------------------------- LayerNorm
-// one warp per row; the row lives in registers (two-pass mean / variance like the fp32 reference).
-template <int kVecs>
+// kLPR lanes share a row (32 / kLPR rows per warp), each lane holding up to kVecs 8-channel vectors in registers:
+// several rows' loads are in flight per warp and the two reductions take log2(kLPR) shuffles.  Two-pass mean /
+// variance like the fp32 reference.
+template <int kLPR, int kVecs>
 __global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const act_t* __restrict__ x,
                                                                  const float* __restrict__ gamma,
                                                                  const float* __restrict__ beta, act_t* __restrict__ out,
                                                                  int rows, int c, float eps) {
+  constexpr int kRowsPerWarp = 32 / kLPR;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row = blockIdx.x * (kNormThreads / 32) + warp;
-  if (row >= rows) return;
+  const int sub = lane / kLPR, l = lane % kLPR;
+  const int row = (blockIdx.x * (kNormThreads / 32) + warp) * kRowsPerWarp + sub;
+  const bool row_ok = row < rows;
   const int octs = c >> 3;
-  const act_t* xr = x + static_cast<size_t>(row) * c;
+  const act_t* xr = x + static_cast<size_t>(row_ok ? row : 0) * c;
   float f[kVecs][8];
   float sum = 0.f;
 #pragma unroll
   for (int v = 0; v < kVecs; ++v) {
-    const int oct = lane + 32 * v;
+    const int oct = l + kLPR * v;
     if (oct < octs) {
       load8(xr + oct * 8, f[v]);
 #pragma unroll
       for (int e = 0; e < 8; ++e) sum += f[v][e];
     }
   }
-  const float mean = warp_sum(sum) / static_cast<float>(c);
+#pragma unroll
+  for (int o = kLPR / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum / static_cast<float>(c);
   float sq = 0.f;
 #pragma unroll
   for (int v = 0; v < kVecs; ++v) {
-    const int oct = lane + 32 * v;
+    const int oct = l + kLPR * v;
     if (oct < octs) {
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
@@ -187,18 +219,24 @@ __global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const act_t* __
       }
     }
   }
-  const float rstd = rsqrtf(warp_sum(sq) / static_cast<float>(c) + eps);
+#pragma unroll
+  for (int o = kLPR / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq / static_cast<float>(c) + eps);
+  if (!row_ok) return;
   act_t* orow = out + static_cast<size_t>(row) * c;
 #pragma unroll
   for (int v = 0; v < kVecs; ++v) {
-    const int oct = lane + 32 * v;
+    const int oct = l + kLPR * v;
     if (oct < octs) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + oct * 8));
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + oct * 8) + 1);
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + oct * 8));
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta + oct * 8) + 1);
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
       float y[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int ch = oct * 8 + e;
-        y[e] = (f[v][e] - mean) * rstd * __ldg(gamma + ch) + __ldg(beta + ch);
-      }
+      for (int e = 0; e < 8; ++e) y[e] = (f[v][e] - mean) * rstd * gg[e] + bb[e];
       store8(orow + oct * 8, y);
     }
   }
@@ -279,8 +317,13 @@ static int gn_check(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chu
   B200SD_REQUIRE((h.c1 == 0) == (h.x1 == nullptr), B200SD_ERR_BAD_ARGUMENT, "groupnorm: x1 and c1 must agree");
   B200SD_REQUIRE(aligned16(h.x0) && aligned16(h.x1) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
                  "groupnorm: pointers must be 16-byte aligned");
-  // aim for ~4 CTAs per SM over the whole launch, at least 8 pixels per CTA
-  int want = (4 * 148 + h.nimg - 1) / h.nimg;
+  // CTA count: ~128 KB of input per CTA, between 4 and 16 CTAs per SM over the whole launch.  Small tensors (UNet)
+  // want few CTAs (per-thread set-up and the per-CTA atomics dominate), large ones (VAE at 512x512) want many waves.
+  const long long bytes = 2ll * h.nimg * h.hw * C;
+  long long ctas = bytes / (128 << 10);
+  if (ctas < 4 * 148) ctas = 4 * 148;
+  if (ctas > 16 * 148) ctas = 16 * 148;
+  int want = static_cast<int>((ctas + h.nimg - 1) / h.nimg);
   int ppc = (h.hw + want - 1) / want;
   if (ppc < 8) ppc = 8;
   if (ppc > h.hw) ppc = h.hw;
@@ -312,9 +355,9 @@ extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_
   const b200sd_groupnorm_params& h = *hp;
   B200SD_REQUIRE(h.out && h.gamma && h.beta, B200SD_ERR_BAD_ARGUMENT, "groupnorm_apply: out/gamma/beta required");
   const int C = h.c0 + h.c1;
-  B200SD_REQUIRE(C * 2 * sizeof(float) <= 48 * 1024, B200SD_ERR_TOO_LARGE, "groupnorm_apply: C too large");
+  (void)C;
   dim3 grid(chunks, h.nimg);
-  gn_apply_kernel<<<grid, kNormThreads, C * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
+  gn_apply_kernel<<<grid, kNormThreads, 0, static_cast<cudaStream_t>(stream_)>>>(
       static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
       static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
@@ -362,7 +405,7 @@ extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200s
   if (int e = gn_check(h, &ppc, &chunks)) return e;
   B200SD_REQUIRE(h.out && h.gamma && h.beta, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: out/gamma/beta required");
   const int C = h.c0 + h.c1;
-  B200SD_REQUIRE(C * 2 * sizeof(float) <= 48 * 1024, B200SD_ERR_TOO_LARGE, "groupnorm_noalloc: C too large");
+  (void)C;
   cudaStream_t s = static_cast<cudaStream_t>(stream_);
   // the scratch still holds the previous call's sums: the accumulators of this call must start from zero
   B200SD_CUDA_CHECK(cudaMemsetAsync(h.stats, 0, static_cast<size_t>(need) * sizeof(float), s));
@@ -370,7 +413,7 @@ extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200s
   gn_stats_kernel<<<grid, kNormThreads, h.groups * 2 * sizeof(float), s>>>(
       static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
   B200SD_CUDA_CHECK(cudaGetLastError());
-  gn_apply_kernel<<<grid, kNormThreads, C * 2 * sizeof(float), s>>>(
+  gn_apply_kernel<<<grid, kNormThreads, 0, s>>>(
       static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
       static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
@@ -385,15 +428,19 @@ extern "C" int b200sd_layernorm(const b200sd_layernorm_params* hp, b200sd_stream
   B200SD_REQUIRE((h.c % 8) == 0 && h.c <= 4096, B200SD_ERR_BAD_SHAPE, "layernorm: c must be a multiple of 8, <= 4096");
   B200SD_REQUIRE(aligned16(h.x) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT, "layernorm: 16-byte alignment");
   cudaStream_t s = static_cast<cudaStream_t>(stream_);
-  const int grid = ceil_div(h.rows, kNormThreads / 32);
   const act_t* x = static_cast<const act_t*>(h.x);
   act_t* o = static_cast<act_t*>(h.out);
-  if (h.c <= 512)
-    layernorm_kernel<2><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
-  else if (h.c <= 1280)
-    layernorm_kernel<5><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+  const int octs = h.c / 8;
+  const int warps = kNormThreads / 32;
+  B200SD_REQUIRE(aligned16(h.gamma) && aligned16(h.beta), B200SD_ERR_BAD_ALIGNMENT, "layernorm: gamma/beta alignment");
+  if (octs <= 8 * 5)  // <= 320 channels: 8 lanes per row, 4 rows per warp
+    layernorm_kernel<8, 5><<<ceil_div(h.rows, warps * 4), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+  else if (octs <= 16 * 5)  // <= 640
+    layernorm_kernel<16, 5><<<ceil_div(h.rows, warps * 2), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+  else if (octs <= 32 * 5)  // <= 1280
+    layernorm_kernel<32, 5><<<ceil_div(h.rows, warps), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
   else
-    layernorm_kernel<16><<<grid, kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+    layernorm_kernel<32, 16><<<ceil_div(h.rows, warps), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
