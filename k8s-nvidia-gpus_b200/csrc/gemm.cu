@@ -48,14 +48,20 @@ struct alignas(64) GemmDev {
   int ksize, pad, taps;
   int cblk0, cblk1;
   int num_stages;
+  int pair;  // 1: CTA pairs (cta_group::2): M tile 256 across two CTAs, each CTA loads half of B
   int ld_rowbias;
   int act;
   float alpha;
 };
 
-__device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int& n0, int& h0, int& w0, int& col0) {
-  const int mt = tile / p.tiles_ncol;
-  const int nt = tile - mt * p.tiles_ncol;
+// tile -> (M tile, column tile), M fastest: with a persistent grid-stride loop every CTA then sees the same mix of
+// full-width and (narrower) last-column tiles instead of always the same column.  In pair mode `tile` counts PAIR
+// tiles (two consecutive M tiles, one per CTA).
+__device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int rank, int& n0, int& h0, int& w0, int& col0) {
+  const int m_units = p.pair ? (p.tiles_m + 1) / 2 : p.tiles_m;
+  const int nt = tile / m_units;
+  int mt = tile - nt * m_units;
+  if (p.pair) mt = 2 * mt + rank;  // an M tile past the end is all out of bounds: TMA zero-fills / clips it
   const int tw = mt % p.tiles_w;
   const int th = (mt / p.tiles_w) % p.tiles_h;
   const int tn = mt / (p.tiles_w * p.tiles_h);
@@ -65,7 +71,7 @@ __device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int& n0,
   col0 = nt * p.BN;
 }
 
-template <bool kOutF32, bool kGeglu, bool kRes>
+template <bool kOutF32, bool kGeglu, bool kRes, bool kPair>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid_constant__ GemmDev p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[kMaxStages];
@@ -78,9 +84,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t tiles_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t b_bytes = static_cast<uint32_t>(p.BN) * kBlockK * 2;
+  const uint32_t rank = kPair ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs, owns the full barriers)
+  const uint32_t b_bytes = static_cast<uint32_t>(kPair ? p.BN / 2 : p.BN) * kBlockK * 2;  // this CTA's share of B
   const uint32_t stage_bytes = kABytes + b_bytes;
-  const int num_tiles = p.tiles_m * p.tiles_ncol;
+  const int num_tiles = (kPair ? (p.tiles_m + 1) / 2 : p.tiles_m) * p.tiles_ncol;
+  const int tile0 = kPair ? blockIdx.x / 2 : blockIdx.x;
+  const int tile_step = kPair ? gridDim.x / 2 : gridDim.x;
   const int cblk = p.cblk0 + p.cblk1;
   const int num_kb = p.taps * cblk;
 
@@ -98,14 +107,22 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(smem_u32(&tfull_bar[s]), 1);
-      mbar_init(smem_u32(&tempty_bar[s]), 8);  // one arrive per epilogue warp
+      mbar_init(smem_u32(&tempty_bar[s]), kPair ? 16 : 8);  // one arrive per epilogue warp (of both CTAs)
       mbar_init(smem_u32(&res_bar[s]), 1);
     }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(smem_u32(&tmem_base_s), 512);
+  if (warp == 2) {
+    if (kPair)
+      tmem_alloc_pair(smem_u32(&tmem_base_s), 512);
+    else
+      tmem_alloc(smem_u32(&tmem_base_s), 512);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (kPair)
+    cluster_sync_all();  // both CTAs' barriers are initialised before any remote arrive / multicast commit
+  else
+    __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
@@ -114,9 +131,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       // ------------------------------------------------------------ TMA producer
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
         int n0, h0, w0, col0;
-        decode_tile(p, tile, n0, h0, w0, col0);
+        decode_tile(p, tile, rank, n0, h0, w0, col0);
+        // pair mode: this CTA supplies rows [rank * n/2, (rank + 1) * n/2) of the (possibly narrowed) column tile
+        const int ntile = (min(p.BN, p.N - col0) + 15) & ~15;
+        const int bcol = kPair ? col0 + static_cast<int>(rank) * (ntile / 2) : col0;
         for (int kb = 0; kb < num_kb; ++kb) {
           const int tap = kb / cblk;
           const int cb = kb - tap * cblk;
@@ -125,12 +145,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
           const uint32_t bar = smem_u32(&full_bar[stage]);
           const uint32_t sa = tiles_base + stage * stage_bytes;
-          mbar_arrive_expect_tx(bar, stage_bytes);
-          if (cb < p.cblk0)
-            tma_load_4d(sa, &p.tmA0, bar, cb * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-          else
-            tma_load_4d(sa, &p.tmA1, bar, (cb - p.cblk0) * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-          tma_load_2d(sa + kABytes, &p.tmB, bar, kb * kBlockK, col0);
+          if (kPair) {
+            if (rank == 0) mbar_arrive_expect_tx(bar, 2 * stage_bytes);  // both CTAs' loads land on the leader's barrier
+            if (cb < p.cblk0)
+              tma_load_4d_pair(sa, &p.tmA0, bar, cb * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+            else
+              tma_load_4d_pair(sa, &p.tmA1, bar, (cb - p.cblk0) * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+            tma_load_2d_pair(sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+          } else {
+            mbar_arrive_expect_tx(bar, stage_bytes);
+            if (cb < p.cblk0)
+              tma_load_4d(sa, &p.tmA0, bar, cb * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+            else
+              tma_load_4d(sa, &p.tmA1, bar, (cb - p.cblk0) * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+            tma_load_2d(sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+          }
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
@@ -139,16 +168,17 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ------------------------------------------------------------ MMA issuer
+    if (lane == 0 && rank == 0) {
+      // ------------------------------------------------------------ MMA issuer (pair mode: the leader CTA only)
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int col0 = (tile % p.tiles_ncol) * p.BN;
+      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+        const int col0 = (tile / (kPair ? (p.tiles_m + 1) / 2 : p.tiles_m)) * p.BN;
         const int ncols = min(p.BN, p.N - col0);
-        const uint32_t idesc = make_idesc_f16(kBlockM, (ncols + 15) & ~15, 0, 0);  // no MMA work on padding columns
+        // no MMA work on padding columns; pair mode: one M = 256 instruction spans both CTAs
+        const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBlockM : kBlockM, (ncols + 15) & ~15, 0, 0);
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -161,15 +191,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             // advancing K by 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-            umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            if (kPair)
+              umma_f16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            else
+              umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
-          umma_commit(smem_u32(&empty_bar[stage]));
+          if (kPair)
+            umma_commit_pair(smem_u32(&empty_bar[stage]));  // frees the stage in both CTAs
+          else
+            umma_commit(smem_u32(&empty_bar[stage]));
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(smem_u32(&tfull_bar[acc]));
+        if (kPair)
+          umma_commit_pair(smem_u32(&tfull_bar[acc]));
+        else
+          umma_commit(smem_u32(&tfull_bar[acc]));
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1u;
@@ -196,9 +235,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     uint32_t res_phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
       int n0, h0, w0, col0;
-      decode_tile(p, tile, n0, h0, w0, col0);
+      decode_tile(p, tile, rank, n0, h0, w0, col0);
       const int img = min(n0 + in, p.nimg - 1);  // rows beyond the tensor are clipped by the TMA store
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
@@ -323,7 +362,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      if (lane == 0) {
+        if (kPair && rank != 0)
+          mbar_arrive_remote(smem_u32(&tempty_bar[acc]), 0);  // the leader's MMA thread waits for both CTAs
+        else
+          mbar_arrive(smem_u32(&tempty_bar[acc]));
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1u;
@@ -333,32 +377,47 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (kPair)
+    cluster_sync_all();  // neither CTA may retire (or free TMEM) while its peer can still signal / read it
+  else
+    __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (kPair)
+      tmem_dealloc_pair(tmem_base, 512);
+    else
+      tmem_dealloc(tmem_base, 512);
   }
 }
 
 // ---------------------------------------------------------------------------------------------------- host
-static int pick_bn(int M_tiles, int N, int sm_count, int gran, int num_kb) {
-  // Tile widths are multiples of the epilogue group (`gran` accumulator columns).  Per 64-deep K block a tile costs
-  // max(MMA time, operand fetch time): 128 x w x 64 MACs at 4096 MAC/cycle = 2w cycles for valid width w, and
-  // (128 + bn) x 128 B of L2 -> SM traffic at the ~45 B/cycle/SM measured on single-CTA tiles = 2.84 (128 + bn)
-  // cycles (this term dominates, hence wide tiles), plus a fixed per-tile overhead amortised over the K loop.
-  int best = gran;
-  double best_cost = 1e30;
-  for (int bn = 256; bn >= gran; bn -= gran) {
-    if (bn - gran >= N && bn > gran) continue;  // wider than needed
-    const int tn = (N + bn - 1) / bn;
-    const long long tiles = static_cast<long long>(M_tiles) * tn;
-    const long long waves = (tiles + sm_count - 1) / sm_count;
-    const double w = static_cast<double>(bn < N ? bn : N);
-    const double per_kb = (2.0 * w > 2.84 * (128.0 + bn) ? 2.0 * w : 2.84 * (128.0 + bn)) + 600.0 / num_kb;
-    const double cost = static_cast<double>(waves) * per_kb;
-    if (cost < best_cost - 1e-9) {
-      best_cost = cost;
-      best = bn;
+struct TilePlan {
+  int bn;
+  int pair;
+  double cost;
+};
+
+// Tile widths are multiples of the epilogue group (`gran` accumulator columns).  Per 64-deep K block a CTA spends
+// max(MMA time, operand fetch time): 128 x w x 64 MACs at 4096 MAC/cycle = 2w cycles for valid width w, against
+// (128 + rows of B it loads) x 128 B of L2 -> SM traffic at the ~45 B/cycle/SM measured on this part = 2.84 cycles per
+// row.  The fetch term dominates, hence wide tiles, and hence CTA pairs (cta_group::2: M = 256 across two CTAs, each
+// loading only half of B) whenever there are enough M tiles to keep the pairs busy.
+static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_kb) {
+  TilePlan best{gran, 0, 1e30};
+  for (int pair = 0; pair < 2; ++pair) {
+    if (pair && M_tiles < 2) continue;
+    for (int bn = 256; bn >= gran; bn -= gran) {
+      if (bn - gran >= N && bn > gran) continue;  // wider than needed
+      if (pair && (bn % 32) != 0) continue;       // each CTA's half of B must be whole 8-row swizzle groups (and /16)
+      const int tn = (N + bn - 1) / bn;
+      const long long units = static_cast<long long>(pair ? (M_tiles + 1) / 2 : M_tiles) * tn;
+      const int slots = pair ? sm_count / 2 : sm_count;
+      const long long waves = (units + slots - 1) / slots;
+      const double w = static_cast<double>(bn < N ? bn : N);
+      const double fetch = 2.84 * (128.0 + (pair ? bn / 2 : bn));
+      const double per_kb = (2.0 * w > fetch ? 2.0 * w : fetch) + (pair ? 4000.0 : 600.0) / num_kb;  // pairs pay extra per-tile hand-offs
+      const double cost = static_cast<double>(waves) * per_kb;
+      if (cost < best.cost - 1e-9) best = TilePlan{bn, pair, cost};
     }
   }
   return best;
@@ -366,17 +425,35 @@ static int pick_bn(int M_tiles, int N, int sm_count, int gran, int num_kb) {
 
 static bool g_gemm_attr_set = false;
 
-template <bool F, bool G, bool R>
-static int launch_variant(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
+template <bool F, bool G, bool R, bool P>
+static int launch_one(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    B200SD_CUDA_CHECK(
-        cudaFuncSetAttribute(gemm_conv_kernel<F, G, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem - 512));
+    B200SD_CUDA_CHECK(cudaFuncSetAttribute(gemm_conv_kernel<F, G, R, P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           max_smem - 512));
     attr_set = true;
   }
-  gemm_conv_kernel<F, G, R><<<grid, kGemmThreads, smem_bytes, stream>>>(d);
-  B200SD_CUDA_CHECK(cudaGetLastError());
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = P ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200SD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_conv_kernel<F, G, R, P>, d));
   return B200SD_OK;
+}
+
+template <bool F, bool G, bool R>
+static int launch_variant(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
+  return d.pair ? launch_one<F, G, R, true>(d, grid, smem_bytes, max_smem, stream)
+                : launch_one<F, G, R, false>(d, grid, smem_bytes, max_smem, stream);
 }
 
 }  // namespace b200sd
@@ -428,11 +505,17 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.tiles_n = ceil_div(h.nimg, d.bn);
   d.tiles_m = d.tiles_w * d.tiles_h * d.tiles_n;
   const int gran = geglu ? 128 : (f32 ? 32 : 64);  // accumulator columns per epilogue group
-  int bn_tile = h.bn_hint;
-  if (bn_tile == 0)
-    bn_tile = pick_bn(d.tiles_m, h.n, di.sm_count, gran, h.ksize * h.ksize * (ceil_div(h.c0, kBlockK) + ceil_div(h.c1, kBlockK)));
-  B200SD_REQUIRE(bn_tile >= gran && bn_tile <= 256 && (bn_tile % gran) == 0, B200SD_ERR_BAD_ARGUMENT,
-                 "gemm: bad bn_hint %d (must be a multiple of %d, <= 256)", bn_tile, gran);
+  // bn_hint: 0 = automatic; otherwise tile width, +1000 forces single-CTA tiles, +2000 forces CTA pairs
+  int bn_tile = h.bn_hint % 1000;
+  const int force = h.bn_hint / 1000;
+  const TilePlan plan = pick_tiles(d.tiles_m, h.n, di.sm_count, gran,
+                                   h.ksize * h.ksize * (ceil_div(h.c0, kBlockK) + ceil_div(h.c1, kBlockK)));
+  d.pair = plan.pair;
+  if (bn_tile == 0) bn_tile = plan.bn;
+  if (force == 1) d.pair = 0;
+  if (force == 2) d.pair = 1;
+  B200SD_REQUIRE(bn_tile >= gran && bn_tile <= 256 && (bn_tile % gran) == 0 && (!d.pair || (bn_tile % 32) == 0),
+                 B200SD_ERR_BAD_ARGUMENT, "gemm: bad bn_hint %d (must be a multiple of %d, <= 256)", bn_tile, gran);
   d.BN = bn_tile;
   d.tiles_ncol = ceil_div(h.n, d.BN);
   d.N = h.n;
@@ -444,7 +527,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.taps = h.ksize * h.ksize;
   d.cblk0 = ceil_div(h.c0, kBlockK);
   d.cblk1 = ceil_div(h.c1, kBlockK);
-  const uint32_t stage_bytes = kABytes + d.BN * kBlockK * 2;
+  const uint32_t stage_bytes = kABytes + (d.pair ? d.BN / 2 : d.BN) * kBlockK * 2;
   const int smem_budget = di.max_smem_optin - 1024 /*align slack*/ - 512 /*static*/ - kEpiStageBytes;
   d.num_stages = min(kMaxStages, smem_budget / static_cast<int>(stage_bytes));
   B200SD_REQUIRE(d.num_stages >= 2, B200SD_ERR_CUDA, "gemm: not enough shared memory (%d B opt-in)", di.max_smem_optin);
@@ -471,7 +554,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
     const uint64_t ktot = static_cast<uint64_t>(d.taps) * (d.cblk0 + d.cblk1) * kBlockK;
     const uint64_t dims[2] = {ktot, static_cast<uint64_t>(h.n)};
     const uint64_t st[1] = {ktot * 2};
-    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(d.BN)};
+    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(d.pair ? d.BN / 2 : d.BN)};
     if (int e = encode_tmap_act(&d.tmB, h.w, 2, dims, st, box)) return e;
   }
   {
@@ -483,8 +566,8 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   }
 
   const int smem_bytes = d.num_stages * stage_bytes + kEpiStageBytes + 1024;
-  const int num_tiles = d.tiles_m * d.tiles_ncol;
-  const int grid = min(num_tiles, di.sm_count);
+  const int num_tiles = (d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m) * d.tiles_ncol;
+  const int grid = d.pair ? 2 * min(num_tiles, di.sm_count / 2) : min(num_tiles, di.sm_count);
   (void)g_gemm_attr_set;
   if (geglu) return launch_variant<false, true, false>(d, grid, smem_bytes, di.max_smem_optin, stream);
   if (f32) return launch_variant<true, false, false>(d, grid, smem_bytes, di.max_smem_optin, stream);

@@ -39,7 +39,10 @@ def _rand(*shape, scale=1.0):
 
 @pytest.mark.parametrize("M,K,N,bn", [(128, 64, 128, 128), (300, 320, 200, 0), (16, 1280, 1280, 0),
                                       (1232, 768, 640, 0), (4096, 320, 960, 0), (513, 72, 40, 64),
-                                      (700, 320, 320, 0), (2048, 640, 200, 128)])
+                                      (700, 320, 320, 0), (2048, 640, 200, 128),
+                                      # forced tile modes: 1000 + bn = single-CTA tiles, 2000 + bn = CTA pairs
+                                      (300, 320, 200, 2128), (700, 320, 320, 2192), (4096, 1280, 320, 2256),
+                                      (65536, 320, 960, 2256), (65536, 320, 960, 1256), (1000, 64, 64, 2064)])
 def test_linear(cuda_lib, b200sd, M, K, N, bn):
     torch.manual_seed(0)
     ops = b200sd.ops
@@ -109,6 +112,24 @@ def test_conv3x3(cuda_lib, b200sd, nimg, H, W, cin, cout):
     torch.cuda.synchronize()
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=1).permute(0, 2, 3, 1)
     _report(f"conv3x3 {nimg}x{H}x{W} {cin}->{cout}", out, ref, 2e-3)
+
+
+@pytest.mark.parametrize("mode", [1000, 2000])
+def test_conv3x3_forced_tile_modes(cuda_lib, b200sd, mode):
+    """Same conv through single-CTA tiles and through CTA pairs (cta_group::2), odd number of M tiles included."""
+    torch.manual_seed(5)
+    ops = b200sd.ops
+    for nimg, H, W, cin, cout, bn in [(3, 16, 16, 128, 320, 192), (16, 64, 64, 320, 320, 192), (5, 8, 8, 256, 128, 128)]:
+        x = _rand(nimg, H, W, cin)
+        w = _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+        bias = torch.randn(cout, device="cuda")
+        res = _rand(nimg, H, W, cout)
+        out = torch.full((nimg, H, W, cout), float("nan"), device="cuda", dtype=ACT())
+        ops.gemm(x, ops.pack_conv_weight(w.float().cpu()).cuda(), out, nimg=nimg, h=H, w_=W, c0=cin, n=cout, ksize=3,
+                 bias=bias, residual=res, bn_hint=mode + bn)(ops.current_stream())
+        torch.cuda.synchronize()
+        ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=1).permute(0, 2, 3, 1) + res.float()
+        _report(f"conv3x3 mode {mode} {nimg}x{H}x{W} {cin}->{cout}", out, ref, 1e-2)
 
 
 def test_conv3x3_concat_temb_residual(cuda_lib, b200sd):

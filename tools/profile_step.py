@@ -140,3 +140,47 @@ def mode_lin():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "lin":
     mode_lin()
+
+
+def mode_pair():
+    """Single-CTA tiles vs CTA pairs (cta_group::2) on the heaviest UNet / VAE shapes."""
+    import b200sd
+    ops = b200sd.ops
+    dt = b200sd.lib.act_dtype()
+    s = ops.current_stream()
+    n = 16
+    shapes = [("conv", 64, 320, 320, 3), ("conv", 32, 640, 640, 3), ("conv", 16, 1280, 1280, 3), ("conv", 8, 1280, 1280, 3),
+              ("conv", 64, 640, 320, 3), ("lin", 65536, 320, 960, 1), ("lin", 65536, 320, 320, 1),
+              ("lin", 65536, 1280, 320, 1), ("lin", 16384, 640, 1920, 1), ("lin", 4096, 1280, 3840, 1),
+              ("lin", 16384, 2560, 640, 1), ("conv", 256, 128, 128, 3), ("conv", 128, 256, 256, 3)]
+    for kind, a, cin, cout, ks in shapes:
+        if kind == "conv":
+            nn = 8 if a >= 128 else n
+            x = (torch.randn(nn, a, a, cin, device="cuda")).to(dt)
+            geo = dict(nimg=nn, h=a, w_=a)
+            m = nn * a * a
+        else:
+            x = (torch.randn(a, cin, device="cuda")).to(dt)
+            geo = dict(nimg=1, h=1, w_=a)
+            m = a
+        w = (torch.randn(cout, ks * ks, cin, device="cuda") * (ks * ks * cin) ** -0.5).to(dt)
+        out = torch.empty(m, cout, device="cuda", dtype=dt)
+        bias = torch.zeros(cout, device="cuda")
+        res = []
+        for hint in (0, 1000, 2000):
+            call = ops.gemm(x, w, out, c0=cin, n=cout, ksize=ks, bias=bias, bn_hint=hint, **geo)
+            call(s)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                call(s)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 5
+            res.append(f"{ms:.3f} ms {2.0 * m * cout * ks * ks * cin / ms / 1e9:6.0f} TF")
+        print(f"{kind} M={m} K={ks * ks * cin} N={cout}: auto {res[0]} | single {res[1]} | pair {res[2]}")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "pair":
+    mode_pair()
