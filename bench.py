@@ -227,6 +227,9 @@ def run_cuda(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
+        # NCCL prints its version banner on stdout at VERSION/INFO level; stdout carries exactly one JSON line
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     b200sd.lib.load()
     info = b200sd.lib.device_info()
