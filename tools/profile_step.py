@@ -184,3 +184,25 @@ def mode_pair():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "pair":
     mode_pair()
+
+
+def mode_unet1():
+    """Exactly one eager denoise step inside a cudaProfilerStart/Stop range (ncu --profile-from-start off)."""
+    import b200sd
+    pipe = b200sd.StableDiffusionPipeline.from_pretrained("sd15", scheduler="ddim")
+    job = pipe.job(8, 64, 64, 7.5, True)
+    sched = pipe.make_schedule(25)
+    job.step_table[: sched.num_evals].copy_(sched.table)
+    job.init_latents.normal_()
+    job.reset()
+    job.step_plan.run()
+    torch.cuda.synchronize()
+    torch.cuda.profiler.start()
+    job.step_plan.run()
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
+    print("unet1 done:", len(job.step_plan), "launches")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "unet1":
+    mode_unet1()
