@@ -22,6 +22,8 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
 ]
+# extra nvcc flags for experiments (e.g. B200SD_NVCC_EXTRA="-DB200SD_ACT_BF16"); part of the stamp digest
+NVCC_FLAGS += os.environ.get("B200SD_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

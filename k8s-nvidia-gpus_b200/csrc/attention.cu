@@ -1,22 +1,27 @@
 // Flash attention forward on tcgen05 (sm_100a): out = softmax(Q K^T * scale [+ causal]) V per (batch, head).
 // SURVEY §2.1 K5 (self-attention), K6 (cross-attention, nk = 77), K15 (CLIP causal attention).
 //
-// One CTA per (up to two 128-query tiles, head, batch); keys are walked in tiles of 64; 12 warps:
+// One CTA per (up to two 128-query tiles, head, batch); keys are walked in tiles of 64; 20 warps:
 //   warp 0 (1 thread) : TMA producer.  Q/K/V are read straight out of the projection GEMM outputs through 4-D
 //                       tensor maps {d, head, token, batch}; the box is 64 wide in d, so head dims that are not a
 //                       multiple of 64 (40, 80, 160) and ragged token counts are zero-filled by the TMA unit —
 //                       no padded copies of Q/K/V exist in HBM.  K/V tiles are shared by both query tiles.
-//   warps 1, 3 (1 thread each): tcgen05.mma issuer of query tile 0 / 1.  S_t = Q_t K^T (K-major A and B) into a DOUBLE-BUFFERED TMEM tile per
-//                       query tile; O_t += P_t V with P_t (16-bit, written by softmax warpgroup t, double-buffered in
-//                       shared memory) as the K-major A operand and V consumed in place as an MN-major B operand.
-//                       S_t(j+2) is issued the moment warpgroup t has consumed S_t(j): the softmax warps never wait
-//                       for the tensor pipe's round trip, and the tensor pipe never waits for the softmax of the tile
-//                       it just produced.
+//   warps 1, 3 (1 thread each): tcgen05.mma issuer of query tile 0 / 1.  S_t = Q_t K^T (K-major A and B) into a
+//                       DOUBLE-BUFFERED TMEM tile per query tile; O_t += P_t V with P_t (16-bit, written by the
+//                       softmax warpgroups of tile t, double-buffered in shared memory) as the K-major A operand and
+//                       V consumed in place as an MN-major B operand.  S_t(j+2) is issued the moment S_t(j) has been
+//                       consumed: the softmax warps never wait for the tensor pipe's round trip, and the tensor
+//                       pipe never waits for the softmax of the tile it just produced.
 //   warp 2            : TMEM allocator.
-//   warps 4..7 / 8..11: softmax warpgroup 0 / 1 (thread = query row).  One pass per KV tile: tcgen05.ld S (next
-//                       chunk in flight) -> p = exp2(s * scale - ref) against a lazily updated reference (moved,
-//                       with a rescale of O in TMEM, only when the tile max overshoots it by 2^8) -> 16-bit P ->
-//                       swizzled shared memory.  Final normalisation and store.
+//   warps 4..19       : four softmax warpgroups, two per query tile.  A query row (TMEM lane) is owned by TWO threads,
+//                       one per 32-column half of every S tile - the exponentials are MUFU-bound and interleaved with
+//                       latency (tcgen05.ld, pack, swizzled stores, barrier round trips), so four resident warps per
+//                       SM sub-partition instead of two keep the MUFU pipe fed.  One pass per KV tile: tcgen05.ld ->
+//                       p = exp2(s * scale - ref) against a lazily updated reference (moved, with a rescale of O in
+//                       TMEM, only when the row's tile max overshoots it by 2^8) -> 16-bit P -> swizzled shared
+//                       memory.  The two halves agree on the row max through a 4-byte shared-memory slot and a
+//                       64-thread named barrier per warp pair.  Final normalisation and store, O chunks alternating
+//                       between the halves.
 //   Row sums: when the head dim leaves a spare UMMA column (d = 40 -> N = 48) column d of every V tile is set to
 //   1.0 after the TMA lands, so the tensor pipe accumulates sum_j P_ij in fp32 as column d of O for free (and it is
 //   rescaled together with O); otherwise the sum is accumulated in registers.
@@ -25,12 +30,25 @@
 
 namespace b200sd {
 
-static constexpr int kAttThreads = 384;
+static constexpr int kAttThreads = 640;  // 4 control warps + 4 softmax warpgroups
 static constexpr int kBQ = 128;  // query rows per tile (UMMA M)
 static constexpr int kBKV = 64;  // keys per tile
 static constexpr uint32_t kQAtom = 128 * 128;   // Q / P: 128 rows x 64 elements (one swizzle-128B atom column)
 static constexpr uint32_t kKVAtom = kBKV * 128;  // K / V: 64 rows x 64 elements
 static constexpr int kMaxStages = 4;
+// mbarrier indices inside the kernel's barrier block ([t] = query tile, [w] = KV-tile parity / warpgroup)
+enum : int {
+  kBarQFull = 0,
+  kBarSFull = 1,                      // [t][w]  S tile written by the tensor pipe
+  kBarSFree = kBarSFull + 4,          // [t][w]  S tile copied to registers
+  kBarPFull = kBarSFree + 4,          // [t][w]  P tile in shared memory
+  kBarPVDone = kBarPFull + 4,         // [t][w]  P V accumulated
+  kBarKFull = kBarPVDone + 4,         // [stage]
+  kBarVFull = kBarKFull + kMaxStages,
+  kBarKEmpty = kBarVFull + kMaxStages,
+  kBarVEmpty = kBarKEmpty + kMaxStages,
+  kNumBars = kBarVEmpty + kMaxStages
+};
 
 struct alignas(64) AttnDev {
   CUtensorMap tmQ, tmK, tmV;
@@ -41,8 +59,8 @@ struct alignas(64) AttnDev {
   int dN;         // UMMA N of the PV product / K extent of QK^T (d rounded up to 16)
   int stages;     // K/V ring depth
   int qtiles;     // query tiles per CTA (1 or 2)
-  int o_col;      // first TMEM column of O_0
-  int o_stride;   // TMEM column stride between O_0 and O_1
+  int o_col;      // first TMEM column of the O accumulators
+  int o_stride;   // TMEM column stride between accumulators (two per query tile: even / odd KV tiles)
   int sum_col;    // >= 0: column of O that accumulates the row sums (ones column in V); -1: register sums
   int causal;
   float scale_log2;
@@ -57,12 +75,12 @@ __device__ __forceinline__ float ex2f(float x) {
 template <bool kOnes>
 __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_constant__ AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t q_full;
-  __shared__ __align__(8) uint64_t s_full[2][2], p_full[2][2], pv_done[2][2];  // [query tile][buffer]
-  __shared__ __align__(8) uint64_t k_full[kMaxStages], v_full[kMaxStages], k_empty[kMaxStages], v_empty[kMaxStages];
+  // all mbarriers in one block: one base address, every barrier a constant byte offset from it
+  __shared__ __align__(8) uint64_t bars[kNumBars];
   __shared__ uint32_t tmem_base_s;
+  const uint32_t bar0 = smem_u32(bars);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * kBQ * p.qtiles;
   const int head = blockIdx.y;
   const int b = blockIdx.z;
@@ -74,6 +92,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   const uint32_t sK = sQ + p.qtiles * q_bytes;       // [stages][nd atoms of 8 KB]
   const uint32_t sV = sK + p.stages * kv_bytes;      // [stages][nd atoms of 8 KB]
   const uint32_t sP = sV + p.stages * kv_bytes;      // [qtiles][2 buffers][16 KB]
+  const uint32_t sX = sP + p.qtiles * 2 * kQAtom;    // [qtiles][2 warpgroups][ref, sum][128] floats: final merge
   int kv_end = p.nk;
   if (p.causal) kv_end = min(p.nk, q0 + kBQ * ntiles);  // keys beyond the last query row are fully masked
   const int T = (kv_end + kBKV - 1) / kBKV;
@@ -84,18 +103,19 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
     tma_prefetch_desc(&p.tmV);
   }
   if (warp == 1 && lane == 0) {
-    mbar_init(smem_u32(&q_full), 1);
+    mbar_init((bar0 + 8 * kBarQFull), 1);
     for (int t = 0; t < 2; ++t)
       for (int i = 0; i < 2; ++i) {
-        mbar_init(smem_u32(&s_full[t][i]), 1);
-        mbar_init(smem_u32(&p_full[t][i]), 128);
-        mbar_init(smem_u32(&pv_done[t][i]), 1);
+        mbar_init((bar0 + 8 * (kBarSFull + 2 * (t) + (i))), 1);
+        mbar_init((bar0 + 8 * (kBarPFull + 2 * (t) + (i))), 128);
+        mbar_init((bar0 + 8 * (kBarSFree + 2 * (t) + (i))), 128);
+        mbar_init((bar0 + 8 * (kBarPVDone + 2 * (t) + (i))), 1);
       }
     for (int s = 0; s < kMaxStages; ++s) {
-      mbar_init(smem_u32(&k_full[s]), 1);
-      mbar_init(smem_u32(&v_full[s]), 1);
-      mbar_init(smem_u32(&k_empty[s]), ntiles);  // one tcgen05.commit per MMA issuer (one issuer per query tile)
-      mbar_init(smem_u32(&v_empty[s]), ntiles);
+      mbar_init((bar0 + 8 * (kBarKFull + (s))), 1);
+      mbar_init((bar0 + 8 * (kBarVFull + (s))), 1);
+      mbar_init((bar0 + 8 * (kBarKEmpty + (s))), ntiles);  // one tcgen05.commit per MMA issuer (one issuer per query tile)
+      mbar_init((bar0 + 8 * (kBarVEmpty + (s))), ntiles);
     }
     fence_mbar_init();
   }
@@ -103,39 +123,41 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_base_s;
-  // TMEM columns: S_t[buf] at (2t + buf) * 64; O_t at o_col + t * o_stride
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_s, 0);  // warp-uniform for the issue loops
+  // TMEM columns: S_t[buf] at (2t + buf) * 64; accumulator of (query tile t, tile parity w) at o_col + (2t + w) * o_stride
 
+  if (warp < 4) {
   if (warp == 0) {
-    if (lane == 0) {
-      // ---------------------------------------------------------------- TMA producer
-      mbar_arrive_expect_tx(smem_u32(&q_full), ntiles * q_bytes);
-      for (int t = 0; t < ntiles; ++t)
-        for (int a = 0; a < p.nd; ++a)
-          tma_load_4d(sQ + t * q_bytes + a * kQAtom, &p.tmQ, smem_u32(&q_full), a * 64, head, q0 + t * kBQ, b);
-      int st = 0;
-      uint32_t ph = 1;
-      for (int j = 0; j < T; ++j) {
-        mbar_wait(smem_u32(&k_empty[st]), ph);
-        mbar_arrive_expect_tx(smem_u32(&k_full[st]), kv_bytes);
-        for (int a = 0; a < p.nd; ++a)
-          tma_load_4d(sK + st * kv_bytes + a * kKVAtom, &p.tmK, smem_u32(&k_full[st]), a * 64, head, j * kBKV, b);
-        mbar_wait(smem_u32(&v_empty[st]), ph);
-        mbar_arrive_expect_tx(smem_u32(&v_full[st]), kv_bytes);
-        for (int a = 0; a < p.nd; ++a)
-          tma_load_4d(sV + st * kv_bytes + a * kKVAtom, &p.tmV, smem_u32(&v_full[st]), a * 64, head, j * kBKV, b);
-        if (++st == p.stages) {
-          st = 0;
-          ph ^= 1u;
-        }
+    // ------------------------------------------------------------------ TMA producer (whole warp converged, one
+    // elected lane issues - see the "_w" note in common.cuh)
+    const uint32_t leader = elect_one();
+    mbar_arrive_expect_tx_w(leader, (bar0 + 8 * kBarQFull), ntiles * q_bytes);
+    for (int t = 0; t < ntiles; ++t)
+      for (int a = 0; a < p.nd; ++a)
+        tma_load_4d_w(leader, sQ + t * q_bytes + a * kQAtom, &p.tmQ, (bar0 + 8 * kBarQFull), a * 64, head, q0 + t * kBQ, b);
+    int st = 0;
+    uint32_t ph = 1;
+    for (int j = 0; j < T; ++j) {
+      mbar_wait((bar0 + 8 * (kBarKEmpty + (st))), ph);
+      mbar_arrive_expect_tx_w(leader, (bar0 + 8 * (kBarKFull + (st))), kv_bytes);
+      for (int a = 0; a < p.nd; ++a)
+        tma_load_4d_w(leader, sK + st * kv_bytes + a * kKVAtom, &p.tmK, (bar0 + 8 * (kBarKFull + (st))), a * 64, head, j * kBKV, b);
+      mbar_wait((bar0 + 8 * (kBarVEmpty + (st))), ph);
+      mbar_arrive_expect_tx_w(leader, (bar0 + 8 * (kBarVFull + (st))), kv_bytes);
+      for (int a = 0; a < p.nd; ++a)
+        tma_load_4d_w(leader, sV + st * kv_bytes + a * kKVAtom, &p.tmV, (bar0 + 8 * (kBarVFull + (st))), a * 64, head, j * kBKV, b);
+      if (++st == p.stages) {
+        st = 0;
+        ph ^= 1u;
       }
     }
   } else if (warp == 1 || warp == 3) {
     const int t = warp >> 1;  // warp 1 issues for query tile 0, warp 3 for query tile 1
-    if (lane == 0 && t < ntiles) {
+    if (t < ntiles) {
       // ---------------------------------------------------------------- MMA issuer of query tile t
-      // Descriptors are built once; the loop only adds 16-byte-unit offsets to their low words.  K and V stages are
-      // consumed strictly in order, so each ring is tracked by a running (stage, phase) pair - no divisions.
+      // Whole warp converged; descriptors are built once and only their low words (16-byte units) move.  K and V
+      // stages are consumed strictly in order, so each ring is tracked by a running (stage, phase) pair.
+      const uint32_t leader = elect_one();
       const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 64] = Q (K-major) x K (K-major)
       const uint32_t idesc_o = make_idesc_f16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
       const int ksteps_s = p.dN / 16;
@@ -143,138 +165,132 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       const uint64_t dK = make_smem_desc_sw128(sK, 16, 1024);
       const uint64_t dV = make_smem_desc_sw128(sV, kKVAtom, 1024);  // MN-major: atoms kKVAtom apart
       const uint64_t dP = make_smem_desc_sw128(sP + 2 * t * kQAtom, 16, 1024);
+      const uint32_t q_lo = static_cast<uint32_t>(dQ), q_hi = static_cast<uint32_t>(dQ >> 32);
+      const uint32_t k_lo = static_cast<uint32_t>(dK), k_hi = static_cast<uint32_t>(dK >> 32);
+      const uint32_t v_lo = static_cast<uint32_t>(dV), v_hi = static_cast<uint32_t>(dV >> 32);
+      const uint32_t p_lo = static_cast<uint32_t>(dP), p_hi = static_cast<uint32_t>(dP >> 32);
       const uint32_t kv_u = kv_bytes >> 4;
       const uint32_t tS0 = tmem_base + 2 * t * 64;
-      const uint32_t tOt = tmem_base + p.o_col + t * p.o_stride;
+      const uint32_t tOt = tmem_base + p.o_col + 2 * t * p.o_stride;
       int kst = 0, vst = 0;
       uint32_t kph = 0, vph = 0;
-      // S_t(jj) into buffer jj & 1 from the current K stage
+      // S_t(jj) into buffer jj & 1 from the current K stage (MMAs only; the commits follow separately)
       auto issue_s = [&](int bfs) {
-        const uint64_t b0 = dK + kst * kv_u;
+        const uint32_t b0 = k_lo + kst * kv_u;
         for (int s = 0; s < ksteps_s; ++s) {
           const uint32_t in_atom = (s & 3) * 2;
-          umma_f16_ss(tS0 + bfs * 64, dQ + (s >> 2) * (kQAtom >> 4) + in_atom, b0 + (s >> 2) * (kKVAtom >> 4) + in_atom,
-                      idesc_s, s != 0);
+          umma_f16_ss_w(leader, tS0 + bfs * 64, q_lo + (s >> 2) * (kQAtom >> 4) + in_atom, q_hi,
+                        b0 + (s >> 2) * (kKVAtom >> 4) + in_atom, k_hi, idesc_s, s != 0);
         }
-        umma_commit(smem_u32(&s_full[t][bfs]));
-        umma_commit(smem_u32(&k_empty[kst]));
+      };
+      auto commit_s = [&](int bfs) {
+        umma_commit_w(leader, (bar0 + 8 * (kBarSFull + 2 * (t) + (bfs))));
+        umma_commit_w(leader, (bar0 + 8 * (kBarKEmpty + (kst))));
         if (++kst == p.stages) {
           kst = 0;
           kph ^= 1u;
         }
       };
-      mbar_wait_spin(smem_u32(&q_full), 0);
+      mbar_wait_spin((bar0 + 8 * kBarQFull), 0);
       for (int jj = 0; jj < 2 && jj < T; ++jj) {  // prologue: both S buffers
-        mbar_wait_spin(smem_u32(&k_full[kst]), kph);
+        mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
         tc_fence_after();
         issue_s(jj);
+        commit_s(jj);
       }
       for (int j = 0; j < T; ++j) {
         const int bf = j & 1;
-        mbar_wait_spin(smem_u32(&p_full[t][bf]), (j >> 1) & 1);  // P_t(j) in smem; S_t buffer bf consumed
-        tc_fence_after();
         if (j + 2 < T) {
-          mbar_wait_spin(smem_u32(&k_full[kst]), kph);
+          mbar_wait_spin((bar0 + 8 * (kBarSFree + 2 * (t) + (bf))), (j >> 1) & 1);  // S_t(j) is in its owner's registers
+          mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
           tc_fence_after();
           issue_s(bf);
+          commit_s(bf);
         }
-        mbar_wait_spin(smem_u32(&v_full[vst]), vph);
+        mbar_wait_spin((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), (j >> 1) & 1);  // P_t(j) in smem
+        mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
         tc_fence_after();
-        const uint64_t a0 = dP + bf * (kQAtom >> 4);
-        const uint64_t b0 = dV + vst * kv_u;
+        const uint32_t a0 = p_lo + bf * (kQAtom >> 4);
+        const uint32_t b0 = v_lo + vst * kv_u;
+        const uint32_t tOa = tOt + bf * p.o_stride;  // accumulator of the warpgroup that owns tiles of parity bf
 #pragma unroll
         for (int s = 0; s < kBKV / 16; ++s)  // 16 kv rows per step: +32 B along P's K, +2048 B down V's rows
-          umma_f16_ss(tOt, a0 + s * 2, b0 + s * 128, idesc_o, (j | s) != 0);
-        umma_commit(smem_u32(&v_empty[vst]));
-        umma_commit(smem_u32(&pv_done[t][bf]));
+          umma_f16_ss_w(leader, tOa, a0 + s * 2, p_hi, b0 + s * 128, v_hi, idesc_o, (j >= 2) || (s != 0));
+        umma_commit_w(leader, (bar0 + 8 * (kBarVEmpty + (vst))));
+        umma_commit_w(leader, (bar0 + 8 * (kBarPVDone + 2 * (t) + (bf))));
         if (++vst == p.stages) {
           vst = 0;
           vph ^= 1u;
         }
       }
     }
-  } else if (warp >= 4) {
+  }
+  } else {
     // ------------------------------------------------------------------ softmax / correction / epilogue
-    const int t = (warp - 4) >> 2;  // warpgroup = query tile
+    const int g = (warp - 4) >> 2;  // warpgroup 0..3
+    const int t = g >> 1;           // query tile
+    const int wg = g & 1;           // parity of the KV tiles this warpgroup owns (and its S / P buffer, O accumulator)
     if (t < ntiles) {
       const int qd = warp & 3;
       const int r = qd * 32 + lane;  // row in tile == TMEM lane
       const int qrow = q0 + t * kBQ + r;
       const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
-      const uint32_t tO = tmem_base + p.o_col + t * p.o_stride + lane_off;
+      const uint32_t tS = tmem_base + (2 * t + wg) * 64 + lane_off;
+      const uint32_t tO0 = tmem_base + p.o_col + (2 * t) * p.o_stride + lane_off;  // even-tile accumulator
+      const uint32_t tO = tO0 + wg * p.o_stride;                                   // mine
+      const uint32_t sPt = sP + (2 * t + wg) * kQAtom + r * 128;
+      const uint32_t swz = static_cast<uint32_t>(r & 7) << 4;
+      const int pair_bar = 1 + t * 4 + qd;  // named barrier shared by the two warps that own the same 32 rows
       constexpr bool ones_col = kOnes;
-      float mb = 0.f;  // reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
-      int vst = 0;     // V ring position (ones-column writer)
+      float mb = 0.f;     // my reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
+      float l_run = 0.f;  // my row sum (register-sum variant)
+      int vst = wg;       // V ring position of my next tile (ones-column writer); p.stages >= 2
       uint32_t vph = 0;
-      float l_run = 0.f;
-      for (int j = 0; j < T; ++j) {
-        const int bf = j & 1;
-        const uint32_t tS = tmem_base + (2 * t + bf) * 64 + lane_off;
-        const uint32_t sPt = sP + (2 * t + bf) * kQAtom + r * 128;
+      for (int j = wg; j < T; j += 2) {
         const int col0 = j * kBKV;
         int limit = p.nk - col0;  // valid columns: [0, limit)
         if (p.causal) limit = min(limit, qrow - col0 + 1);
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
-        mbar_wait_spin(smem_u32(&s_full[t][bf]), (j >> 1) & 1);
+        mbar_wait_spin((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), (j >> 1) & 1);
         tc_fence_after();
-        if (j >= 2) {
-          // P_t(j-2) V(j-2) has been consumed: P buffer bf may be overwritten
-          mbar_wait_spin(smem_u32(&pv_done[t][bf]), ((j >> 1) - 1) & 1);
-        }
-        // Single pass per tile: exponentials against the CURRENT reference while the tile's own max is tracked.  The
-        // reference (0 at the start) only moves - with a rescale of O / l - when the tile max overshoots it by more
-        // than 2^kTau (or, on the first tile, undershoots it by as much); p <= 2^kTau stays far inside fp16 range and
-        // the sums are fp32.  The pass is then redone once.
-        constexpr float kTau = 8.f;
-        for (int attempt = 0; attempt < 2; ++attempt) {
-          float psum = 0.f;
-          float m0 = -INFINITY, m1 = -INFINITY;
-          uint32_t bufA[32], bufB[32];
-          // 32 scores -> exp2 -> 16-bit P -> 4 swizzled 16-byte chunks of my row
-          auto process = [&](uint32_t(&cur)[32], int c) {
-            if (need_mask) {
+        // the whole row of the tile goes to registers and the S buffer is handed straight back: Q K^T of my next
+        // tile runs on the tensor pipe while I am still busy with this one
+        uint32_t sa[32], sb[32];
+        tmem_ld32(tS, sa);
+        tmem_ld32(tS + 32, sb);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive((bar0 + 8 * (kBarSFree + 2 * (t) + (wg))));
+        if (need_mask) {
 #pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if (c * 32 + i >= limit) cur[i] = __float_as_uint(-INFINITY);
-            }
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              uint32_t w[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float s0 = __uint_as_float(cur[g * 8 + 2 * e]), s1 = __uint_as_float(cur[g * 8 + 2 * e + 1]);
-                m0 = fmaxf(m0, s0);
-                m1 = fmaxf(m1, s1);
-                const float p0 = ex2f(fmaf(s0, p.scale_log2, -mb)), p1 = ex2f(fmaf(s1, p.scale_log2, -mb));
-                if (!ones_col) psum += p0 + p1;
-                w[e] = pack_act2(p0, p1);
-              }
-              const int c16 = c * 4 + g;
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((c16 ^ (r & 7)) << 4)), "r"(w[0]),
-                           "r"(w[1]), "r"(w[2]), "r"(w[3])
-                           : "memory");
-            }
-          };
-          tmem_ld32(tS, bufA);
-          tmem_ld_wait();
-          tmem_ld32(tS + 32, bufB);  // in flight during the first half's maths
-          process(bufA, 0);
-          tmem_ld_wait();
-          process(bufB, 1);
-          const float xmax = fmaf(fmaxf(m0, m1), p.scale_log2, -mb);  // -inf when the whole row is masked
-          const bool exceed = (xmax > kTau) || (j == 0 && xmax < -kTau && xmax != -INFINITY);
-          if (!__any_sync(0xffffffffu, exceed)) {
-            l_run += psum;
-            break;
+          for (int i = 0; i < 32; ++i) {
+            if (i >= limit) sa[i] = __float_as_uint(-INFINITY);
+            if (i + 32 >= limit) sb[i] = __float_as_uint(-INFINITY);
           }
-          // rare: move the reference of the rows that over/undershot, rescale their O / l, redo the pass once
+        }
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          m0 = fmaxf(m0, __uint_as_float(sa[i]));
+          m1 = fmaxf(m1, __uint_as_float(sa[i + 1]));
+          m2 = fmaxf(m2, __uint_as_float(sb[i]));
+          m3 = fmaxf(m3, __uint_as_float(sb[i + 1]));
+        }
+        // Lazily updated reference (0 at the start): it only moves - with a rescale of O / l - when the tile max
+        // overshoots it by more than 2^kTau (or, on my first tile, undershoots it by as much); p <= 2^kTau stays far
+        // inside fp16 range and the sums are fp32.
+        constexpr float kTau = 8.f;
+        const float xmax = fmaf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)), p.scale_log2, -mb);  // -inf: row fully masked
+        const bool exceed = (xmax > kTau) || (j == wg && xmax < -kTau && xmax != -INFINITY);
+        const uint32_t pv_bar = bar0 + 8 * (kBarPVDone + 2 * t + wg);
+        const uint32_t pv_par = ((j >> 1) - 1) & 1;
+        if (__any_sync(0xffffffffu, exceed)) {  // rare
           const float delta = exceed ? xmax : 0.f;
           const float alpha = ex2f(-delta);
           mb += delta;
           l_run *= alpha;
-          if (j > 0) {
-            // O must hold every product up to tile j-1
-            mbar_wait(smem_u32(&pv_done[t][bf ^ 1]), ((j - 1) >> 1) & 1);
+          if (j >= 2) {
+            mbar_wait(pv_bar, pv_par);  // O holds all my earlier tiles
             tc_fence_after();
             for (int c = 0; c < p.dN; c += 16) {
               uint32_t o[16];
@@ -287,53 +303,106 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
             tmem_st_wait();
           }
         }
+        // 64 scores -> exp2 -> 16-bit P (registers)
+        float psum = 0.f;
+        uint32_t w[32];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int i = (q & 3) * 8 + 2 * e;
+            const float p0 = ex2f(fmaf(__uint_as_float(q < 4 ? sa[i] : sb[i]), p.scale_log2, -mb));
+            const float p1 = ex2f(fmaf(__uint_as_float(q < 4 ? sa[i + 1] : sb[i + 1]), p.scale_log2, -mb));
+            if (!ones_col) psum += p0 + p1;
+            w[q * 4 + e] = pack_act2(p0, p1);
+          }
+        }
+        // P(j-2) V(j-2) has read my P buffer (issued a whole tile ago - the wait is normally already satisfied)
+        if (j >= 2) mbar_wait_spin(pv_bar, pv_par);
+#pragma unroll
+        for (int q = 0; q < 8; ++q)  // 8 swizzled 16-byte chunks of my row
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((static_cast<uint32_t>(q) << 4) ^ swz)),
+                       "r"(w[q * 4]), "r"(w[q * 4 + 1]), "r"(w[q * 4 + 2]), "r"(w[q * 4 + 3])
+                       : "memory");
+        l_run += psum;
         if (ones_col) {
           // V(j) has landed: set column `sum_col` of its 64 kv rows to 1.0 so O[:, sum_col] accumulates the row sums
-          mbar_wait_spin(smem_u32(&v_full[vst]), vph);
+          mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
           if (r < kBKV) {
-            const int sc = p.sum_col;
-            const uint32_t va = sV + vst * kv_bytes + (sc >> 6) * kKVAtom + r * 128 +
-                                (((((sc & 63) >> 3)) ^ (r & 7)) << 4) + (sc & 7) * 2;
+            const int scol = p.sum_col;
+            const uint32_t va = sV + vst * kv_bytes + (scol >> 6) * kKVAtom + r * 128 +
+                                (((((scol & 63) >> 3)) ^ (r & 7)) << 4) + (scol & 7) * 2;
             const act_t one = to_act(1.f);
             asm volatile("st.shared.b16 [%0], %1;" ::"r"(va), "h"(*reinterpret_cast<const uint16_t*>(&one)) : "memory");
           }
-          if (++vst == p.stages) {
-            vst = 0;
+          vst += 2;
+          if (vst >= p.stages) {
+            vst -= p.stages;
             vph ^= 1u;
           }
         }
         fence_proxy_async_smem();
         tc_fence_before();
-        mbar_arrive(smem_u32(&p_full[t][bf]));
+        mbar_arrive((bar0 + 8 * (kBarPFull + 2 * (t) + (wg))));
       }
-      // final: O / l -> 16-bit -> global (the last commit covers every earlier MMA)
-      mbar_wait(smem_u32(&pv_done[t][(T - 1) & 1]), ((T - 1) >> 1) & 1);
+      // ---- merge of the two accumulators of my query tile and store.  O = (f_e O_e + f_o O_o) / (f_e l_e + f_o l_o)
+      // with f_x = 2^(mb_x - max(mb_e, mb_o)); both accumulators live in my TMEM lanes, only mb / l travel through smem.
+      const int mine = (T - wg + 1) >> 1;  // tiles I processed
+      const bool has_odd = T >= 2;
+      if (mine > 0) mbar_wait((bar0 + 8 * (kBarPVDone + 2 * (t) + (wg))), (mine - 1) & 1);  // the last commit covers every earlier MMA
+      const uint32_t xa = sX + ((t * 2 + wg) * 2 * kBQ + r) * 4, xb = sX + ((t * 2 + (wg ^ 1)) * 2 * kBQ + r) * 4;
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(xa), "f"(mb) : "memory");
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(xa + kBQ * 4), "f"(l_run) : "memory");
+      tc_fence_before();
+      named_bar_sync(pair_bar, 64);
       tc_fence_after();
-      act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
-      float inv_l = 1.f / l_run;
+      float mb_o, l_o;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(mb_o) : "r"(xb) : "memory");
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(l_o) : "r"(xb + kBQ * 4) : "memory");
+      // (e, o) = (even-tile warpgroup, odd-tile warpgroup) regardless of which one I am
+      const float mb_e = wg ? mb_o : mb, mb_d = wg ? mb : mb_o;
+      float l_e = wg ? l_o : l_run, l_d = wg ? l_run : l_o;
+      const float mref = has_odd ? fmaxf(mb_e, mb_d) : mb_e;
+      const float f_e = ex2f(mb_e - mref), f_d = has_odd ? ex2f(mb_d - mref) : 0.f;
       if (ones_col) {
         uint32_t o[16];
-        tmem_ld16(tO + (p.sum_col & ~15), o);
+        tmem_ld16(tO0 + (p.sum_col & ~15), o);
         tmem_ld_wait();
-        float l = 0.f;
 #pragma unroll
         for (int i = 0; i < 16; ++i)
-          if (i == (p.sum_col & 15)) l = __uint_as_float(o[i]);
-        inv_l = 1.f / l;
+          if (i == (p.sum_col & 15)) l_e = __uint_as_float(o[i]);
+        l_d = 0.f;
+        if (has_odd) {
+          tmem_ld16(tO0 + p.o_stride + (p.sum_col & ~15), o);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (i == (p.sum_col & 15)) l_d = __uint_as_float(o[i]);
+        }
       }
-      for (int c = 0; c < p.dN; c += 16) {
-        uint32_t o[16];
-        tmem_ld16(tO + c, o);
+      const float inv_l = 1.f / (f_e * l_e + f_d * l_d);
+      const float g_e = f_e * inv_l, g_d = f_d * inv_l;
+      act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
+      for (int c = wg * 16; c < p.dN; c += 32) {  // the two warpgroups take alternate 16-column chunks
+        uint32_t oe[16], od[16];
+        tmem_ld16(tO0 + c, oe);
+        if (has_odd) tmem_ld16(tO0 + p.o_stride + c, od);
         tmem_ld_wait();
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          v[i] = __uint_as_float(oe[i]) * g_e;
+          if (has_odd) v[i] = fmaf(__uint_as_float(od[i]), g_d, v[i]);
+        }
         if (qrow < p.nq) {
 #pragma unroll
           for (int h8 = 0; h8 < 2; ++h8) {
             if (c + h8 * 8 < p.d) {  // d is a multiple of 8
               uint4 u;
-              u.x = pack_act2(__uint_as_float(o[h8 * 8 + 0]) * inv_l, __uint_as_float(o[h8 * 8 + 1]) * inv_l);
-              u.y = pack_act2(__uint_as_float(o[h8 * 8 + 2]) * inv_l, __uint_as_float(o[h8 * 8 + 3]) * inv_l);
-              u.z = pack_act2(__uint_as_float(o[h8 * 8 + 4]) * inv_l, __uint_as_float(o[h8 * 8 + 5]) * inv_l);
-              u.w = pack_act2(__uint_as_float(o[h8 * 8 + 6]) * inv_l, __uint_as_float(o[h8 * 8 + 7]) * inv_l);
+              u.x = pack_act2(v[h8 * 8 + 0], v[h8 * 8 + 1]);
+              u.y = pack_act2(v[h8 * 8 + 2], v[h8 * 8 + 3]);
+              u.z = pack_act2(v[h8 * 8 + 4], v[h8 * 8 + 5]);
+              u.w = pack_act2(v[h8 * 8 + 6], v[h8 * 8 + 7]);
               *reinterpret_cast<uint4*>(orow + c + h8 * 8) = u;
             }
           }
@@ -386,15 +455,15 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   d.ldo = h.ldo;
   d.nd = ceil_div(h.d, 64);
   d.dN = ceil_div(h.d, 16) * 16;
-  d.qtiles = (d.dN <= 128 && h.nq > kBQ) ? 2 : 1;
+  d.qtiles = (d.dN <= 64 && h.nq > kBQ) ? 2 : 1;
   // TMEM: S double-buffered per query tile (64 columns each), then the O accumulators
   d.o_col = d.qtiles * 128;
-  d.o_stride = 128;
+  d.o_stride = d.qtiles == 2 ? 64 : 192;  // 2 x (128 + 2 * 64) or 128 + 2 * 192 = 512 columns
   d.sum_col = (d.dN > h.d) ? h.d : -1;
   d.causal = h.causal;
   d.scale_log2 = h.scale * 1.4426950408889634f;
   // shared memory: Q + 2 P buffers per query tile are fixed; K/V rings take what is left (at most 4 stages)
-  const int fixed = d.qtiles * (d.nd * static_cast<int>(kQAtom) + 2 * static_cast<int>(kQAtom)) + 1024;
+  const int fixed = d.qtiles * (d.nd * static_cast<int>(kQAtom) + 2 * static_cast<int>(kQAtom) + 2 * 2 * kBQ * 4) + 1024;
   const int per_stage = 2 * d.nd * static_cast<int>(kKVAtom);
   d.stages = min(kMaxStages, (di.max_smem_optin - 1024 - fixed) / per_stage);
   B200SD_REQUIRE(d.stages >= 2, B200SD_ERR_TOO_LARGE, "attention: shared memory budget");

@@ -206,3 +206,33 @@ def mode_unet1():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "unet1":
     mode_unet1()
+
+
+def mode_att():
+    """Self-attention of the 64x64 level (4096 tokens, 8 heads x 40) alone: quick A/B timing and ncu target."""
+    import b200sd
+    ops = b200sd.ops
+    dt = b200sd.lib.act_dtype()
+    s = ops.current_stream()
+    n = 16
+    for tokens, heads, d in [(4096, 8, 40), (1024, 8, 80)]:
+        c = heads * d
+        qkv = (torch.randn(n, tokens, 3 * c, device="cuda")).to(dt)
+        out = torch.empty(n, tokens, c, device="cuda", dtype=dt)
+        q2 = qkv.view(-1, 3 * c)
+        call = ops.attention(q2, q2[:, c:], q2[:, 2 * c:], out, batch=n, heads=heads, nq=tokens, nk=tokens, d=d,
+                             ldq=3 * c, ldk=3 * c, ldv=3 * c, ldo=c, scale=d ** -0.5)
+        call(s)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            call(s)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        print(f"self-attention {tokens} tok d={d} x{n}: {ms:.3f} ms  {4.0 * n * heads * tokens * tokens * d / ms / 1e9:.1f} TFLOP/s")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "att":
+    mode_att()
