@@ -72,6 +72,17 @@ __device__ __forceinline__ float ex2f(float x) {
   return y;
 }
 
+#ifdef ATT_PARK_CTRL
+#define CTRL_WAIT mbar_wait
+#else
+#define CTRL_WAIT mbar_wait_spin
+#endif
+#ifdef ATT_PARK_SM
+#define SM_WAIT mbar_wait
+#else
+#define SM_WAIT mbar_wait_spin
+#endif
+
 template <bool kOnes>
 __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_constant__ AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
@@ -191,9 +202,9 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           kph ^= 1u;
         }
       };
-      mbar_wait_spin((bar0 + 8 * kBarQFull), 0);
+      CTRL_WAIT((bar0 + 8 * kBarQFull), 0);
       for (int jj = 0; jj < 2 && jj < T; ++jj) {  // prologue: both S buffers
-        mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
+        CTRL_WAIT((bar0 + 8 * (kBarKFull + (kst))), kph);
         tc_fence_after();
         issue_s(jj);
         commit_s(jj);
@@ -201,14 +212,14 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       for (int j = 0; j < T; ++j) {
         const int bf = j & 1;
         if (j + 2 < T) {
-          mbar_wait_spin((bar0 + 8 * (kBarSFree + 2 * (t) + (bf))), (j >> 1) & 1);  // S_t(j) is in its owner's registers
-          mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
+          CTRL_WAIT((bar0 + 8 * (kBarSFree + 2 * (t) + (bf))), (j >> 1) & 1);  // S_t(j) is in its owner's registers
+          CTRL_WAIT((bar0 + 8 * (kBarKFull + (kst))), kph);
           tc_fence_after();
           issue_s(bf);
           commit_s(bf);
         }
-        mbar_wait_spin((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), (j >> 1) & 1);  // P_t(j) in smem
-        mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
+        CTRL_WAIT((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), (j >> 1) & 1);  // P_t(j) in smem
+        CTRL_WAIT((bar0 + 8 * (kBarVFull + (vst))), vph);
         tc_fence_after();
         const uint32_t a0 = p_lo + bf * (kQAtom >> 4);
         const uint32_t b0 = v_lo + vst * kv_u;
@@ -251,7 +262,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         int limit = p.nk - col0;  // valid columns: [0, limit)
         if (p.causal) limit = min(limit, qrow - col0 + 1);
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
-        mbar_wait_spin((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), (j >> 1) & 1);
+        SM_WAIT((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), (j >> 1) & 1);
         tc_fence_after();
         // the whole row of the tile goes to registers and the S buffer is handed straight back: Q K^T of my next
         // tile runs on the tensor pipe while I am still busy with this one
@@ -318,7 +329,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           }
         }
         // P(j-2) V(j-2) has read my P buffer (issued a whole tile ago - the wait is normally already satisfied)
-        if (j >= 2) mbar_wait_spin(pv_bar, pv_par);
+        if (j >= 2) SM_WAIT(pv_bar, pv_par);
 #pragma unroll
         for (int q = 0; q < 8; ++q)  // 8 swizzled 16-byte chunks of my row
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((static_cast<uint32_t>(q) << 4) ^ swz)),
@@ -327,7 +338,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         l_run += psum;
         if (ones_col) {
           // V(j) has landed: set column `sum_col` of its 64 kv rows to 1.0 so O[:, sum_col] accumulates the row sums
-          mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
+          SM_WAIT((bar0 + 8 * (kBarVFull + (vst))), vph);
           if (r < kBKV) {
             const int scol = p.sum_col;
             const uint32_t va = sV + vst * kv_bytes + (scol >> 6) * kKVAtom + r * 128 +

@@ -278,6 +278,67 @@ __device__ __forceinline__ void tma_load_4d_w(uint32_t leader, uint32_t dst, con
       : "memory");
 }
 
+__device__ __forceinline__ void tma_load_2d_w(uint32_t leader, uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0,
+                                               int c1) {
+  asm volatile(
+      "{\n"
+      ".reg .pred e;\n"
+      "setp.ne.b32 e, %5, 0;\n"
+      "@e cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n"
+      "}\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair_w(uint32_t leader, uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                                    int c0, int c1) {
+  asm volatile(
+      "{\n"
+      ".reg .pred e;\n"
+      "setp.ne.b32 e, %5, 0;\n"
+      "@e cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+      "%4}], [%2];\n"
+      "}\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_pair_w(uint32_t leader, uint32_t dst, const CUtensorMap* tm, uint32_t bar,
+                                                    int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "{\n"
+      ".reg .pred e;\n"
+      "setp.ne.b32 e, %7, 0;\n"
+      "@e cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+      "%4, %5, %6}], [%2];\n"
+      "}\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_ss_pair_w(uint32_t leader, uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi,
+                                                    uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p, e;\n"
+      ".reg .b64 da, db;\n"
+      "mov.b64 da, {%1, %2};\n"
+      "mov.b64 db, {%3, %4};\n"
+      "setp.ne.b32 p, %6, 0;\n"
+      "setp.ne.b32 e, %7, 0;\n"
+      "@e tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate), "r"(leader)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair_w(uint32_t leader, uint32_t bar) {
+  asm volatile(
+      "{\n"
+      ".reg .pred e;\n"
+      "setp.ne.b32 e, %1, 0;\n"
+      "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %2;\n"
+      "}\n" ::"r"(bar),
+      "r"(leader), "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+
 // ------------------------------------------------------------------ tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols)

@@ -71,17 +71,25 @@ __device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int rank
   col0 = nt * p.BN;
 }
 
+// mbarrier indices inside the kernel's barrier block
+enum : int {
+  kBarFull = 0,                        // [stage]  A/B tiles landed
+  kBarEmpty = kBarFull + kMaxStages,   // [stage]  MMAs that read the stage have completed
+  kBarTFull = kBarEmpty + kMaxStages,  // [acc]    accumulator complete
+  kBarTEmpty = kBarTFull + 2,          // [acc]    accumulator drained by the epilogue
+  kBarRes = kBarTEmpty + 2,            // [epilogue warpgroup] residual tile landed
+  kNumBars = kBarRes + 2
+};
+
 template <bool kOutF32, bool kGeglu, bool kRes, bool kPair>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid_constant__ GemmDev p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t full_bar[kMaxStages];
-  __shared__ __align__(8) uint64_t empty_bar[kMaxStages];
-  __shared__ __align__(8) uint64_t tfull_bar[2];
-  __shared__ __align__(8) uint64_t tempty_bar[2];
-  __shared__ __align__(8) uint64_t res_bar[2];
+  // all mbarriers in one block: one base address, every barrier a constant byte offset from it
+  __shared__ __align__(8) uint64_t bars[kNumBars];
   __shared__ uint32_t tmem_base_s;
+  const uint32_t bar0 = smem_u32(bars);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = warp_idx_uniform();
   const int lane = threadIdx.x & 31;
   const uint32_t tiles_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t rank = kPair ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs, owns the full barriers)
@@ -102,13 +110,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < p.num_stages; ++s) {
-      mbar_init(smem_u32(&full_bar[s]), 1);
-      mbar_init(smem_u32(&empty_bar[s]), 1);
+      mbar_init((bar0 + 8 * (kBarFull + (s))), 1);
+      mbar_init((bar0 + 8 * (kBarEmpty + (s))), 1);
     }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(smem_u32(&tfull_bar[s]), 1);
-      mbar_init(smem_u32(&tempty_bar[s]), kPair ? 16 : 8);  // one arrive per epilogue warp (of both CTAs)
-      mbar_init(smem_u32(&res_bar[s]), 1);
+      mbar_init((bar0 + 8 * (kBarTFull + (s))), 1);
+      mbar_init((bar0 + 8 * (kBarTEmpty + (s))), kPair ? 16 : 8);  // one arrive per epilogue warp (of both CTAs)
+      mbar_init((bar0 + 8 * (kBarRes + (s))), 1);
     }
     fence_mbar_init();
   }
@@ -124,91 +132,96 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   else
     __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = tmem_base_s;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_s, 0);  // warp-uniform for the issue loop
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ------------------------------------------------------------ TMA producer
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = tile0; tile < num_tiles; tile += tile_step) {
-        int n0, h0, w0, col0;
-        decode_tile(p, tile, rank, n0, h0, w0, col0);
-        // pair mode: this CTA supplies rows [rank * n/2, (rank + 1) * n/2) of the (possibly narrowed) column tile
-        const int ntile = (min(p.BN, p.N - col0) + 15) & ~15;
-        const int bcol = kPair ? col0 + static_cast<int>(rank) * (ntile / 2) : col0;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          const int tap = kb / cblk;
-          const int cb = kb - tap * cblk;
-          const int kh = tap / p.ksize;
-          const int kw = tap - kh * p.ksize;
-          mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
-          const uint32_t bar = smem_u32(&full_bar[stage]);
-          const uint32_t sa = tiles_base + stage * stage_bytes;
-          if (kPair) {
-            if (rank == 0) mbar_arrive_expect_tx(bar, 2 * stage_bytes);  // both CTAs' loads land on the leader's barrier
-            if (cb < p.cblk0)
-              tma_load_4d_pair(sa, &p.tmA0, bar, cb * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-            else
-              tma_load_4d_pair(sa, &p.tmA1, bar, (cb - p.cblk0) * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-            tma_load_2d_pair(sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
-          } else {
-            mbar_arrive_expect_tx(bar, stage_bytes);
-            if (cb < p.cblk0)
-              tma_load_4d(sa, &p.tmA0, bar, cb * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-            else
-              tma_load_4d(sa, &p.tmA1, bar, (cb - p.cblk0) * kBlockK, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-            tma_load_2d(sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+    // -------------------------------------------------------------- TMA producer: whole warp converged, one elected
+    // lane issues (see the "_w" note in common.cuh); the k-block -> (tap, channel block) walk is incremental
+    const uint32_t leader = elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+      int n0, h0, w0, col0;
+      decode_tile(p, tile, rank, n0, h0, w0, col0);
+      // pair mode: this CTA supplies rows [rank * n/2, (rank + 1) * n/2) of the (possibly narrowed) column tile
+      const int ntile = (min(p.BN, p.N - col0) + 15) & ~15;
+      const int bcol = kPair ? col0 + static_cast<int>(rank) * (ntile / 2) : col0;
+      int cb = 0, kw = 0, kh = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(bar0 + 8 * (kBarEmpty + stage), phase ^ 1u);
+        const uint32_t bar = bar0 + 8 * (kBarFull + stage);
+        const uint32_t sa = tiles_base + stage * stage_bytes;
+        const bool first = cb < p.cblk0;
+        const CUtensorMap* tmA = first ? &p.tmA0 : &p.tmA1;
+        const int ch = (first ? cb : cb - p.cblk0) * kBlockK;
+        if (kPair) {
+          if (rank == 0) mbar_arrive_expect_tx_w(leader, bar, 2 * stage_bytes);  // both CTAs' loads land on the leader's barrier
+          tma_load_4d_pair_w(leader, sa, tmA, bar, ch, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+          tma_load_2d_pair_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+        } else {
+          mbar_arrive_expect_tx_w(leader, bar, stage_bytes);
+          tma_load_4d_w(leader, sa, tmA, bar, ch, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+          tma_load_2d_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+        }
+        if (++cb == cblk) {
+          cb = 0;
+          if (++kw == p.ksize) {
+            kw = 0;
+            ++kh;
           }
-          if (++stage == p.num_stages) {
-            stage = 0;
-            phase ^= 1u;
-          }
+        }
+        if (++stage == p.num_stages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
-      // ------------------------------------------------------------ MMA issuer (pair mode: the leader CTA only)
+    if (rank == 0) {
+      // ------------------------------------------------------------ MMA issuer (pair mode: the leader CTA only),
+      // whole warp converged: descriptors stay on the uniform datapath, only the low words move
+      const uint32_t leader = elect_one();
+      const uint64_t desc0 = make_smem_desc_sw128(tiles_base, 16, 1024);
+      const uint32_t d_lo = static_cast<uint32_t>(desc0), d_hi = static_cast<uint32_t>(desc0 >> 32);
+      const uint32_t stage_u = stage_bytes >> 4, b_off = kABytes >> 4;
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      const int m_units = kPair ? (p.tiles_m + 1) / 2 : p.tiles_m;
       for (int tile = tile0; tile < num_tiles; tile += tile_step) {
-        const int col0 = (tile / (kPair ? (p.tiles_m + 1) / 2 : p.tiles_m)) * p.BN;
+        const int col0 = (tile / m_units) * p.BN;
         const int ncols = min(p.BN, p.N - col0);
         // no MMA work on padding columns; pair mode: one M = 256 instruction spans both CTAs
         const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBlockM : kBlockM, (ncols + 15) & ~15, 0, 0);
-        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);
+        mbar_wait(bar0 + 8 * (kBarTEmpty + acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
         for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(smem_u32(&full_bar[stage]), phase);
+          mbar_wait(bar0 + 8 * (kBarFull + stage), phase);
           tc_fence_after();
-          const uint32_t sa = tiles_base + stage * stage_bytes;
-          const uint64_t adesc = make_smem_desc_sw128(sa, 16, 1024);
-          const uint64_t bdesc = make_smem_desc_sw128(sa + kABytes, 16, 1024);
+          const uint32_t a_lo = d_lo + stage * stage_u;
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             // advancing K by 16 elements = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
             if (kPair)
-              umma_f16_ss_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+              umma_f16_ss_pair_w(leader, d_tmem, a_lo + 2 * k, d_hi, a_lo + b_off + 2 * k, d_hi, idesc, (kb | k) != 0);
             else
-              umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+              umma_f16_ss_w(leader, d_tmem, a_lo + 2 * k, d_hi, a_lo + b_off + 2 * k, d_hi, idesc, (kb | k) != 0);
           }
           if (kPair)
-            umma_commit_pair(smem_u32(&empty_bar[stage]));  // frees the stage in both CTAs
+            umma_commit_pair_w(leader, bar0 + 8 * (kBarEmpty + stage));  // frees the stage in both CTAs
           else
-            umma_commit(smem_u32(&empty_bar[stage]));
+            umma_commit_w(leader, bar0 + 8 * (kBarEmpty + stage));
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
         if (kPair)
-          umma_commit_pair(smem_u32(&tfull_bar[acc]));
+          umma_commit_pair_w(leader, bar0 + 8 * (kBarTFull + acc));
         else
-          umma_commit(smem_u32(&tfull_bar[acc]));
+          umma_commit_w(leader, bar0 + 8 * (kBarTFull + acc));
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1u;
@@ -231,7 +244,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     const uint32_t sw = static_cast<uint32_t>(r & 7);
     const bool issuer = (q == 0 && lane == 0);
     const int bar_id = 1 + wg;
-    const uint32_t resb = smem_u32(&res_bar[wg]);
+    const uint32_t resb = (bar0 + 8 * (kBarRes + (wg)));
     uint32_t res_phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -239,7 +252,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       int n0, h0, w0, col0;
       decode_tile(p, tile, rank, n0, h0, w0, col0);
       const int img = min(n0 + in, p.nimg - 1);  // rows beyond the tensor are clipped by the TMA store
-      mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+      mbar_wait((bar0 + 8 * (kBarTFull + (acc))), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
       const int ncols = min(p.BN, p.N - col0);  // valid accumulator columns in this tile
@@ -364,9 +377,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       __syncwarp();
       if (lane == 0) {
         if (kPair && rank != 0)
-          mbar_arrive_remote(smem_u32(&tempty_bar[acc]), 0);  // the leader's MMA thread waits for both CTAs
+          mbar_arrive_remote((bar0 + 8 * (kBarTEmpty + (acc))), 0);  // the leader's MMA thread waits for both CTAs
         else
-          mbar_arrive(smem_u32(&tempty_bar[acc]));
+          mbar_arrive((bar0 + 8 * (kBarTEmpty + (acc))));
       }
       if (++acc == 2) {
         acc = 0;
