@@ -466,9 +466,37 @@ __device__ __forceinline__ float2 unpack_act2(uint32_t u) {
 __device__ __forceinline__ act_t to_act(float x) { return __float2half_rn(x); }
 __device__ __forceinline__ float from_act(act_t x) { return __half2float(x); }
 #endif
-__device__ __forceinline__ float silu_f(float x) { return x / (1.f + __expf(-x)); }
-__device__ __forceinline__ float quick_gelu_f(float x) { return x / (1.f + __expf(-1.702f * x)); }
-__device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
+// Activations for the epilogues: two MUFU ops each, no IEEE division, no branches (these run per output element of
+// the short-K GEMMs and of every GroupNorm, where the epilogue - not the tensor pipe - sets the pace).
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// x * sigmoid(x); x -> -inf: ex2 -> +inf, rcp -> 0, result -0
+__device__ __forceinline__ float silu_f(float x) { return x * rcp_approx(1.f + ex2_approx(-1.4426950408889634f * x)); }
+__device__ __forceinline__ float quick_gelu_f(float x) {
+  return x * rcp_approx(1.f + ex2_approx(-1.702f * 1.4426950408889634f * x));
+}
+// exact (erf) GELU = x * Phi(x) with erfc from Abramowitz & Stegun 7.1.26 (|error| < 1.5e-7 in erf, i.e. < 1e-7 in
+// Phi - far below the 16-bit output rounding): erfc(z) = t (a1 + t (a2 + t (a3 + t (a4 + t a5)))) exp(-z^2),
+// t = 1 / (1 + p z), z = |x| / sqrt(2).
+__device__ __forceinline__ float gelu_erf_f(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  const float t = rcp_approx(fmaf(0.3275911f, z, 1.f));
+  float q = fmaf(1.061405429f, t, -1.453152027f);
+  q = fmaf(q, t, 1.421413741f);
+  q = fmaf(q, t, -0.284496736f);
+  q = fmaf(q, t, 0.254829592f);
+  const float half_erfc = 0.5f * q * t * ex2_approx(-1.4426950408889634f * z * z);
+  const float phi = x >= 0.f ? 1.f - half_erfc : half_erfc;
+  return x * phi;
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
