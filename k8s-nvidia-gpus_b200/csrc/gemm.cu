@@ -48,6 +48,7 @@ struct alignas(64) GemmDev {
   int ksize, pad, taps;
   int cblk0, cblk1;
   int num_stages;
+  int res_bufs;  // staging tiles per epilogue warpgroup: 2 = the residual of the NEXT group is prefetched
   int pair;  // 1: CTA pairs (cta_group::2): M tile 256 across two CTAs, each CTA loads half of B
   int ld_rowbias;
   int act;
@@ -78,7 +79,7 @@ enum : int {
   kBarTFull = kBarEmpty + kMaxStages,  // [acc]    accumulator complete
   kBarTEmpty = kBarTFull + 2,          // [acc]    accumulator drained by the epilogue
   kBarRes = kBarTEmpty + 2,            // [epilogue warpgroup] residual tile landed
-  kNumBars = kBarRes + 2
+  kNumBars = kBarRes + 4              // [epilogue warpgroup][staging buffer]
 };
 
 template <bool kOutF32, bool kGeglu, bool kRes, bool kPair>
@@ -116,7 +117,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     for (int s = 0; s < 2; ++s) {
       mbar_init((bar0 + 8 * (kBarTFull + (s))), 1);
       mbar_init((bar0 + 8 * (kBarTEmpty + (s))), kPair ? 16 : 8);  // one arrive per epilogue warp (of both CTAs)
-      mbar_init((bar0 + 8 * (kBarRes + (s))), 1);
+      mbar_init((bar0 + 8 * (kBarRes + 2 * s)), 1);
+      mbar_init((bar0 + 8 * (kBarRes + 2 * s + 1)), 1);
     }
     fence_mbar_init();
   }
@@ -239,13 +241,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     constexpr int gcols = kOutF32 ? 32 : 64;        // output columns per 128-byte group
     constexpr int acols = kGeglu ? 2 * gcols : gcols;  // accumulator columns per group
     constexpr int nsub = kOutF32 ? 1 : 2;           // 32-column sub-blocks per group
-    const uint32_t stg = tiles_base + p.num_stages * stage_bytes + wg * kEpiTileBytes;
-    const uint32_t my_row = stg + r * 128;
+    // staging: p.res_bufs tiles per warpgroup.  With two, group k of this warpgroup uses tile k & 1 and the residual
+    // of group k + 1 is in flight while group k is computed and stored.
+    const uint32_t stg0 = tiles_base + p.num_stages * stage_bytes + wg * p.res_bufs * kEpiTileBytes;
+    const bool prefetch = kRes && p.res_bufs == 2;
+    uint32_t gk = 0;  // groups this warpgroup has processed
     const uint32_t sw = static_cast<uint32_t>(r & 7);
     const bool issuer = (q == 0 && lane == 0);
     const int bar_id = 1 + wg;
-    const uint32_t resb = (bar0 + 8 * (kBarRes + (wg)));
-    uint32_t res_phase = 0;
+    const uint32_t resb0 = bar0 + 8 * (kBarRes + 2 * wg);
+    // (tile, group) after (tile, g) in this warpgroup's order; tile >= num_tiles when there is none
+    auto next_group = [&](int& tile, int& g) {
+      g += 2;
+      for (;;) {
+        if (tile >= num_tiles) return;
+        const int c0 = (tile / (kPair ? (p.tiles_m + 1) / 2 : p.tiles_m)) * p.BN;
+        const int ng = (min(p.BN, p.N - c0) + acols - 1) / acols;
+        if (g < ng) return;
+        tile += tile_step;
+        g = wg;
+      }
+    };
+    auto load_residual = [&](int tile, int g, uint32_t buf) {  // issuer only
+      int n0, h0, w0, col0;
+      decode_tile(p, tile, rank, n0, h0, w0, col0);
+      const int oc = kGeglu ? (col0 + g * acols) / 2 : col0 + g * acols;
+      mbar_arrive_expect_tx(resb0 + 8 * buf, kEpiTileBytes);
+      tma_load_4d(stg0 + buf * kEpiTileBytes, &p.tmR, resb0 + 8 * buf, oc, w0, h0, n0);
+    };
+    if (prefetch && issuer) {
+      int t0 = tile0, g0 = wg - 2;
+      next_group(t0, g0);
+      if (t0 < num_tiles) load_residual(t0, g0, 0);
+    }
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = tile0; tile < num_tiles; tile += tile_step) {
@@ -292,12 +320,23 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       for (int g = wg; g < ngroups; g += 2) {
         const int ac0 = g * acols;
         const int ocol0 = kGeglu ? (col0 + ac0) / 2 : col0 + ac0;  // first output column of this group
+        const uint32_t buf = prefetch ? (gk & 1u) : 0u;
+        const uint32_t stg = stg0 + buf * kEpiTileBytes;
+        const uint32_t my_row = stg + r * 128;
+        const uint32_t resb = resb0 + 8 * buf;
+        const uint32_t res_phase = prefetch ? ((gk >> 1) & 1u) : (gk & 1u);
         if (kRes) {
-          // the residual tile lands in the staging tile (after the previous store has finished reading it)
+          // the residual tile lands in a staging tile (after the previous store from it has finished reading it)
           if (issuer) {
             bulk_wait_read0();
-            mbar_arrive_expect_tx(resb, kEpiTileBytes);
-            tma_load_4d(stg, &p.tmR, resb, ocol0, w0, h0, n0);
+            if (prefetch) {
+              int tn = tile, gn = g;
+              next_group(tn, gn);
+              if (tn < num_tiles) load_residual(tn, gn, buf ^ 1u);
+            } else {
+              mbar_arrive_expect_tx(resb, kEpiTileBytes);
+              tma_load_4d(stg, &p.tmR, resb, ocol0, w0, h0, n0);
+            }
           }
         }
         uint32_t w[32];  // this row's 128 output bytes
@@ -329,10 +368,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             }
           }
           if (kRes) {
-            if (hh == 0) {
-              mbar_wait(resb, res_phase);
-              res_phase ^= 1u;
-            }
+            if (hh == 0) mbar_wait(resb, res_phase);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {  // my row, 16-byte chunks hh*4 .. hh*4+3
               uint4 u;
@@ -372,6 +408,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           tma_store_4d(&p.tmO, stg, ocol0, w0, h0, n0);
           bulk_commit();
         }
+        ++gk;
       }
       tc_fence_before();
       __syncwarp();
@@ -541,7 +578,16 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.cblk0 = ceil_div(h.c0, kBlockK);
   d.cblk1 = ceil_div(h.c1, kBlockK);
   const uint32_t stage_bytes = kABytes + (d.pair ? d.BN / 2 : d.BN) * kBlockK * 2;
-  const int smem_budget = di.max_smem_optin - 1024 /*align slack*/ - 512 /*static*/ - kEpiStageBytes;
+  // residual prefetch (a second staging tile per epilogue warpgroup) for short reductions, where the epilogue sets
+  // the pace; long reductions keep the shared memory for mainloop stages (measured: they lose with fewer stages)
+  const int budget0 = di.max_smem_optin - 1024 /*align slack*/ - 512 /*static*/;
+  const int num_kb_host = d.taps * (d.cblk0 + d.cblk1);
+  d.res_bufs = 1;
+  if (h.residual != nullptr) {
+    const int st2 = (budget0 - 2 * kEpiStageBytes) / static_cast<int>(stage_bytes);
+    if (st2 >= 2 && num_kb_host <= 24) d.res_bufs = 2;
+  }
+  const int smem_budget = budget0 - d.res_bufs * kEpiStageBytes;
   d.num_stages = min(kMaxStages, smem_budget / static_cast<int>(stage_bytes));
   B200SD_REQUIRE(d.num_stages >= 2, B200SD_ERR_CUDA, "gemm: not enough shared memory (%d B opt-in)", di.max_smem_optin);
   d.bias = h.bias;
@@ -578,7 +624,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
       if (int e = nhwc_map(&d.tmR, h.residual, n_out, h.ldr, 2, boxO, false)) return e;
   }
 
-  const int smem_bytes = d.num_stages * stage_bytes + kEpiStageBytes + 1024;
+  const int smem_bytes = d.num_stages * stage_bytes + d.res_bufs * kEpiStageBytes + 1024;
   const int num_tiles = (d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m) * d.tiles_ncol;
   const int grid = d.pair ? 2 * min(num_tiles, di.sm_count / 2) : min(num_tiles, di.sm_count);
   (void)g_gemm_attr_set;
