@@ -72,16 +72,19 @@ __device__ __forceinline__ float ex2f(float x) {
   return y;
 }
 
-#ifdef ATT_PARK_CTRL
-#define CTRL_WAIT mbar_wait
-#else
-#define CTRL_WAIT mbar_wait_spin
-#endif
-#ifdef ATT_PARK_SM
-#define SM_WAIT mbar_wait
-#else
-#define SM_WAIT mbar_wait_spin
-#endif
+// (x0, x1) = (a0, a1) * s + c as one fma.rn.f32x2
+__device__ __forceinline__ void fma2(float a0, float a1, float s, float c, float& x0, float& x1) {
+  asm("{\n"
+      ".reg .b64 va, vs, vc, vd;\n"
+      "mov.b64 va, {%2, %3};\n"
+      "mov.b64 vs, {%4, %4};\n"
+      "mov.b64 vc, {%5, %5};\n"
+      "fma.rn.f32x2 vd, va, vs, vc;\n"
+      "mov.b64 {%0, %1}, vd;\n"
+      "}\n"
+      : "=f"(x0), "=f"(x1)
+      : "f"(a0), "f"(a1), "f"(s), "f"(c));
+}
 
 template <bool kOnes>
 __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_constant__ AttnDev p) {
@@ -202,9 +205,9 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           kph ^= 1u;
         }
       };
-      CTRL_WAIT((bar0 + 8 * kBarQFull), 0);
+      mbar_wait_spin((bar0 + 8 * kBarQFull), 0);
       for (int jj = 0; jj < 2 && jj < T; ++jj) {  // prologue: both S buffers
-        CTRL_WAIT((bar0 + 8 * (kBarKFull + (kst))), kph);
+        mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
         tc_fence_after();
         issue_s(jj);
         commit_s(jj);
@@ -212,14 +215,14 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       for (int j = 0; j < T; ++j) {
         const int bf = j & 1;
         if (j + 2 < T) {
-          CTRL_WAIT((bar0 + 8 * (kBarSFree + 2 * (t) + (bf))), (j >> 1) & 1);  // S_t(j) is in its owner's registers
-          CTRL_WAIT((bar0 + 8 * (kBarKFull + (kst))), kph);
+          mbar_wait_spin((bar0 + 8 * (kBarSFree + 2 * (t) + (bf))), (j >> 1) & 1);  // S_t(j) is in its owner's registers
+          mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
           tc_fence_after();
           issue_s(bf);
           commit_s(bf);
         }
-        CTRL_WAIT((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), (j >> 1) & 1);  // P_t(j) in smem
-        CTRL_WAIT((bar0 + 8 * (kBarVFull + (vst))), vph);
+        mbar_wait_spin((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), (j >> 1) & 1);  // P_t(j) in smem
+        mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
         tc_fence_after();
         const uint32_t a0 = p_lo + bf * (kQAtom >> 4);
         const uint32_t b0 = v_lo + vst * kv_u;
@@ -262,7 +265,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         int limit = p.nk - col0;  // valid columns: [0, limit)
         if (p.causal) limit = min(limit, qrow - col0 + 1);
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
-        SM_WAIT((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), (j >> 1) & 1);
+        mbar_wait_spin((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), (j >> 1) & 1);
         tc_fence_after();
         // the whole row of the tile goes to registers and the S buffer is handed straight back: Q K^T of my next
         // tile runs on the tensor pipe while I am still busy with this one
@@ -322,14 +325,17 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int i = (q & 3) * 8 + 2 * e;
-            const float p0 = ex2f(fmaf(__uint_as_float(q < 4 ? sa[i] : sb[i]), p.scale_log2, -mb));
-            const float p1 = ex2f(fmaf(__uint_as_float(q < 4 ? sa[i + 1] : sb[i + 1]), p.scale_log2, -mb));
+            // both scores of the pair through one packed fp32x2 FMA (half the FMA-pipe issue slots)
+            float x0, x1;
+            fma2(__uint_as_float(q < 4 ? sa[i] : sb[i]), __uint_as_float(q < 4 ? sa[i + 1] : sb[i + 1]), p.scale_log2,
+                 -mb, x0, x1);
+            const float p0 = ex2f(x0), p1 = ex2f(x1);
             if (!ones_col) psum += p0 + p1;
             w[q * 4 + e] = pack_act2(p0, p1);
           }
         }
         // P(j-2) V(j-2) has read my P buffer (issued a whole tile ago - the wait is normally already satisfied)
-        if (j >= 2) SM_WAIT(pv_bar, pv_par);
+        if (j >= 2) mbar_wait_spin(pv_bar, pv_par);
 #pragma unroll
         for (int q = 0; q < 8; ++q)  // 8 swizzled 16-byte chunks of my row
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((static_cast<uint32_t>(q) << 4) ^ swz)),
@@ -338,7 +344,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         l_run += psum;
         if (ones_col) {
           // V(j) has landed: set column `sum_col` of its 64 kv rows to 1.0 so O[:, sum_col] accumulates the row sums
-          SM_WAIT((bar0 + 8 * (kBarVFull + (vst))), vph);
+          mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
           if (r < kBKV) {
             const int scol = p.sum_col;
             const uint32_t va = sV + vst * kv_bytes + (scol >> 6) * kKVAtom + r * 128 +

@@ -236,3 +236,58 @@ def mode_att():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "att":
     mode_att()
+
+
+def mode_sweep():
+    """Tile-plan sweep: every UNet linear / conv shape class under forced (single | pair) x BN; best vs the heuristic."""
+    import b200sd
+    ops = b200sd.ops
+    L = b200sd.lib
+    dt = L.act_dtype()
+    s = ops.current_stream()
+    # (M, K-per-tap, N, ksize, spatial side or 0, residual, geglu)
+    shapes = [(65536, 320, 320, 1, 0, True, False), (65536, 320, 960, 1, 0, False, False),
+              (65536, 1280, 320, 1, 0, True, False), (65536, 320, 2560, 1, 0, False, True),
+              (16384, 640, 640, 1, 0, True, False), (16384, 640, 5120, 1, 0, False, True),
+              (16384, 2560, 640, 1, 0, True, False), (4096, 1280, 1280, 1, 0, True, False),
+              (4096, 5120, 1280, 1, 0, True, False), (4096, 1280, 10240, 1, 0, False, True),
+              (1024, 1280, 1280, 3, 8, True, False), (4096, 1280, 1280, 3, 16, True, False),
+              (16384, 640, 640, 3, 32, True, False), (65536, 320, 320, 3, 64, True, False)]
+    for m, cin, nn, ks, side, has_res, geglu in shapes:
+        if ks == 3:
+            nimg = m // (side * side)
+            x = torch.randn(nimg, side, side, cin, device="cuda").to(dt)
+            geo = dict(nimg=nimg, h=side, w_=side)
+        else:
+            x = torch.randn(m, cin, device="cuda").to(dt)
+            geo = dict(nimg=1, h=1, w_=m)
+        w = (torch.randn(nn, ks * ks, cin, device="cuda") * (ks * ks * cin) ** -0.5).to(dt)
+        nout = nn // 2 if geglu else nn
+        out = torch.empty(m, nout, device="cuda", dtype=dt)
+        res = torch.randn(m, nout, device="cuda").to(dt) if has_res else None
+        bias = torch.zeros(nn, device="cuda")
+        results = {}
+        for hint in [0] + [md + bn for md in (1000, 2000) for bn in (64, 128, 192, 256)]:
+            try:
+                call = ops.gemm(x, w, out, c0=cin, n=nn, ksize=ks, bias=bias, bn_hint=hint, residual=res,
+                                act=L.ACT_GEGLU if geglu else L.ACT_NONE, **geo)
+                call(s)
+            except L.B200SDError:
+                continue
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                call(s)
+            e1.record()
+            torch.cuda.synchronize()
+            results[hint] = e0.elapsed_time(e1) / 5
+        fl = 2.0 * m * nn * ks * ks * cin
+        best = min((v, k) for k, v in results.items() if k)
+        row = " ".join(f"{k}:{v * 1e3:.0f}" for k, v in results.items())
+        print(f"M={m} K={ks * ks * cin} N={nn}{' res' if has_res else ''}{' geglu' if geglu else ''}: auto {results[0] * 1e3:.0f} us "
+              f"({fl / results[0] / 1e9:.0f} TF) best {best[1]} {best[0] * 1e3:.0f} us ({fl / best[0] / 1e9:.0f} TF) | {row}")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "sweep":
+    mode_sweep()
