@@ -2,26 +2,27 @@
 // SURVEY §2.1 K5 (self-attention), K6 (cross-attention, nk = 77), K15 (CLIP causal attention).
 //
 // One CTA per (up to two 128-query tiles, head, batch); keys are walked in tiles of 64; 20 warps:
-//   warp 0 (1 thread) : TMA producer.  Q/K/V are read straight out of the projection GEMM outputs through 4-D
+//   warp 0            : TMA producer.  Q/K/V are read straight out of the projection GEMM outputs through 4-D
 //                       tensor maps {d, head, token, batch}; the box is 64 wide in d, so head dims that are not a
 //                       multiple of 64 (40, 80, 160) and ragged token counts are zero-filled by the TMA unit —
 //                       no padded copies of Q/K/V exist in HBM.  K/V tiles are shared by both query tiles.
-//   warps 1, 3 (1 thread each): tcgen05.mma issuer of query tile 0 / 1.  S_t = Q_t K^T (K-major A and B) into a
-//                       DOUBLE-BUFFERED TMEM tile per query tile; O_t += P_t V with P_t (16-bit, written by the
-//                       softmax warpgroups of tile t, double-buffered in shared memory) as the K-major A operand and
-//                       V consumed in place as an MN-major B operand.  S_t(j+2) is issued the moment S_t(j) has been
-//                       consumed: the softmax warps never wait for the tensor pipe's round trip, and the tensor
-//                       pipe never waits for the softmax of the tile it just produced.
+//   warps 1, 3        : tcgen05.mma issuer of query tile 0 / 1 (whole warp converged, one elected lane issues).
+//                       S_t(j) = Q_t K(j)^T (K-major A and B) goes to TMEM buffer j & 1 of query tile t;
+//                       O_t,w += P_t(j) V(j) with P_t(j) (16-bit, shared memory) as the K-major A operand and V
+//                       consumed in place as an MN-major B operand, into the accumulator of parity w = j & 1.
+//                       S_t(j+2) is issued as soon as its owner has copied S_t(j) to registers (s_free), i.e. while
+//                       the exponentials of tile j are still being computed.
 //   warp 2            : TMEM allocator.
-//   warps 4..19       : four softmax warpgroups, two per query tile.  A query row (TMEM lane) is owned by TWO threads,
-//                       one per 32-column half of every S tile - the exponentials are MUFU-bound and interleaved with
-//                       latency (tcgen05.ld, pack, swizzled stores, barrier round trips), so four resident warps per
-//                       SM sub-partition instead of two keep the MUFU pipe fed.  One pass per KV tile: tcgen05.ld ->
-//                       p = exp2(s * scale - ref) against a lazily updated reference (moved, with a rescale of O in
-//                       TMEM, only when the row's tile max overshoots it by 2^8) -> 16-bit P -> swizzled shared
-//                       memory.  The two halves agree on the row max through a 4-byte shared-memory slot and a
-//                       64-thread named barrier per warp pair.  Final normalisation and store, O chunks alternating
-//                       between the halves.
+//   warps 4..19       : four softmax warpgroups, two per query tile (thread = query row = TMEM lane).  The two
+//                       warpgroups of a query tile take ALTERNATE KV tiles (even / odd), each with its own S buffer,
+//                       P buffer, lazily updated reference and O accumulator - no per-tile exchange between them -
+//                       and four resident warps per SM sub-partition keep the MUFU pipe fed.  Per tile: tcgen05.ld of
+//                       the 64 scores -> release S -> row max -> p = exp2(s * scale - ref) (reference moved, with a
+//                       rescale of O in TMEM, only when the tile max overshoots it by 2^8) -> 16-bit P -> swizzled
+//                       shared memory.  At the end the two accumulators of a query tile are merged like split-KV
+//                       partials: O = (f_e O_e + f_o O_o) / (f_e l_e + f_o l_o), f_x = 2^(ref_x - max ref).
+//   TMEM (512 columns): d <= 64: 2 query tiles x (2 S buffers x 64 + 2 accumulators x 64); larger head dims: 1 query
+//   tile x (2 x 64 + 2 x 192).
 //   Row sums: when the head dim leaves a spare UMMA column (d = 40 -> N = 48) column d of every V tile is set to
 //   1.0 after the TMA lands, so the tensor pipe accumulates sum_j P_ij in fp32 as column d of O for free (and it is
 //   rescaled together with O); otherwise the sum is accumulated in registers.
@@ -302,8 +303,8 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           const float delta = exceed ? xmax : 0.f;
           const float alpha = ex2f(-delta);
           mb += delta;
-          l_run *= alpha;
           if (j >= 2) {
+            l_run *= alpha;  // (on my first tile there is nothing to rescale, and 2^-delta may overflow)
             mbar_wait(pv_bar, pv_par);  // O holds all my earlier tiles
             tc_fence_after();
             for (int c = 0; c < p.dN; c += 16) {

@@ -93,6 +93,42 @@ def test_attention(cuda_lib, b200sd, batch, heads, nq, nk, d, causal):
     _report(f"attention b{batch} h{heads} {nq}x{nk} d{d} causal={causal}", out, ref, 2e-2)
 
 
+@pytest.mark.parametrize("d,nk", [(40, 1024), (64, 1000), (80, 448), (160, 200), (40, 64), (64, 130)])
+def test_attention_reference_moves_and_accumulator_merge(cuda_lib, b200sd, d, nk):
+    """Scores built so that the softmax reference has to move late and differently in the even- and odd-tile
+    accumulators (spikes in single key tiles, a first tile far below zero), and so that the two partial results are
+    merged with very different weights."""
+    torch.manual_seed(4)
+    ops = b200sd.ops
+    batch, heads, nq = 2, 3, 300
+    C = heads * d
+    q = _rand(batch, nq, C)
+    k = _rand(batch, nk, C)
+    v = _rand(batch, nk, C)
+    kf32 = k.float().view(batch, nk, heads, d)
+    qf32 = q.float().view(batch, nq, heads, d)
+    # keys of tile 0: strongly anti-aligned with every query of head 0 (first-tile undershoot); one key of an odd tile
+    # and one of a late even tile aligned with the mean query (late overshoot, different per accumulator)
+    qm = qf32.mean(dim=1)                                 # [batch, heads, d]
+    kf32[:, : min(64, nk), 0, :] = -6.0 * qm[:, None, 0, :] / qm[:, None, 0, :].norm(dim=-1, keepdim=True) - 2.0
+    if nk > 64 + 7:
+        kf32[:, 64 + 7, 1, :] = 40.0 * qm[:, 1, :] / qm[:, 1, :].norm(dim=-1, keepdim=True)
+    if nk > 5 * 64:
+        kf32[:, 4 * 64 + 3, 1, :] = 25.0 * qm[:, 1, :] / qm[:, 1, :].norm(dim=-1, keepdim=True)
+        kf32[:, 5 * 64 - 1, 2, :] = 60.0
+    k = kf32.reshape(batch, nk, C).to(ACT()).contiguous()
+    out = torch.full((batch, nq, C), float("nan"), device="cuda", dtype=ACT())
+    scale = 1.0  # unscaled scores: spread of several hundred in the log2 domain
+    ops.attention(q, k, v, out, batch=batch, heads=heads, nq=nq, nk=nk, d=d, ldq=C, ldk=C, ldv=C, ldo=C,
+                  scale=scale)(ops.current_stream())
+    torch.cuda.synchronize()
+    qf = q.float().view(batch, nq, heads, d).transpose(1, 2)
+    kf = k.float().view(batch, nk, heads, d).transpose(1, 2)
+    vf = v.float().view(batch, nk, heads, d).transpose(1, 2)
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * scale, dim=-1) @ vf).transpose(1, 2).reshape(batch, nq, C)
+    _report(f"attention spikes d{d} nk{nk}", out, ref, 2e-2)
+
+
 def _table(rows):
     t = torch.zeros(len(rows), 16)
     for i, r in enumerate(rows):
