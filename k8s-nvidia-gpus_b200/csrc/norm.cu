@@ -10,6 +10,10 @@ namespace b200sd {
 
 static constexpr int kNormThreads = 256;
 
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), c = unpack_act2(u.z), d = unpack_act2(u.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
 __device__ __forceinline__ void load8(const act_t* p, float (&f)[8]) {
   const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
   const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), c = unpack_act2(u.z), d = unpack_act2(u.w);
@@ -58,17 +62,20 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
 #pragma unroll
       for (int e = 0; e < 8; ++e) s[e] = q[e] = 0.f;
       int p = p_begin + stream;
-      for (; p + 3 * S < p_end; p += 4 * S) {
-        float f[4][8];
+      for (; p + 7 * S < p_end; p += 8 * S) {
+        uint4 raw[8];  // eight pixels in flight, kept packed until they are used
 #pragma unroll
-        for (int u = 0; u < 4; ++u) load8(src + static_cast<size_t>(p + u * S) * ld, f[u]);
+        for (int u = 0; u < 8; ++u) raw[u] = __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(p + u * S) * ld));
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 8; ++u) {
+          float f[8];
+          unpack8(raw[u], f);
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            s[e] += f[u][e];
-            q[e] = fmaf(f[u][e], f[u][e], q[e]);
+            s[e] += f[e];
+            q[e] = fmaf(f[e], f[e], q[e]);
           }
+        }
       }
       for (; p < p_end; p += S) {
         float f[8];
@@ -107,7 +114,7 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
 // Same thread -> (octet, pixel stream) mapping as the statistics pass: a thread normalises ONE 8-channel column, so its
 // 8 scales and 8 shifts live in registers for the whole walk (no per-element shared-memory lookups) and the inner
 // loop is load16 -> 8 fma (+SiLU) -> store16 with four pixels in flight.
-__global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const act_t* __restrict__ x0,
+__global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* __restrict__ x0,
                                                                 const act_t* __restrict__ x1,
                                                                 const float* __restrict__ stats,
                                                                 const float* __restrict__ gamma,
@@ -151,17 +158,19 @@ __global__ void __launch_bounds__(kNormThreads) gn_apply_kernel(const act_t* __r
     act_t* dst = out + static_cast<size_t>(n) * hw * C + ch0;
     int p = p_begin + stream;
     for (; p + 3 * S < p_end; p += 4 * S) {
-      float f[4][8];
+      uint4 raw[4];  // four pixels in flight, kept packed until they are used
 #pragma unroll
-      for (int u = 0; u < 4; ++u) load8(src + static_cast<size_t>(p + u * S) * ld, f[u]);
+      for (int u = 0; u < 4; ++u) raw[u] = __ldg(reinterpret_cast<const uint4*>(src + static_cast<size_t>(p + u * S) * ld));
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8(raw[u], f);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float y = fmaf(f[u][e], sc[e], sh[e]);
-          f[u][e] = silu ? silu_f(y) : y;
+          const float y = fmaf(f[e], sc[e], sh[e]);
+          f[e] = silu ? silu_f(y) : y;
         }
-        store8(dst + static_cast<size_t>(p + u * S) * C, f[u]);
+        store8(dst + static_cast<size_t>(p + u * S) * C, f);
       }
     }
     for (; p < p_end; p += S) {
