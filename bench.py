@@ -240,7 +240,7 @@ def run_cuda(args):
     B = args.batch
     sched = pipe.make_schedule(args.inference_steps)
     evals = sched.num_evals
-    job = pipe.job(B, h, w, args.guidance_scale, True)
+    job = pipe.job(B, h, w, args.guidance_scale, True, zero_negative=pipe.is_xl)
 
     # synthetic inputs for this rank's shard (global image index = rank * B + i; seed = 1234 + index)
     prompts = synthetic_prompts(B, rank * B)
@@ -248,6 +248,7 @@ def run_cuda(args):
     ids = pipe.tokenize(prompts, [""] * B, True)
     lat = pipe.prepare_latents(B, h, w, gens, sched.init_noise_sigma)
     job.ids_dev.copy_(ids)
+    job.eos_dev.copy_(pipe.eos_rows(ids, job.n_text))
     job.init_latents.copy_(lat.permute(0, 2, 3, 1).reshape(B, h * w, 4))
     job.step_table[:evals].copy_(sched.table)
     gathered = None

@@ -40,7 +40,13 @@ enum b200sd_status {
   B200SD_ERR_TOO_LARGE = -6
 };
 
-enum b200sd_act { B200SD_ACT_NONE = 0, B200SD_ACT_SILU = 1, B200SD_ACT_QUICK_GELU = 2, B200SD_ACT_GEGLU = 3 };
+enum b200sd_act {
+  B200SD_ACT_NONE = 0,
+  B200SD_ACT_SILU = 1,
+  B200SD_ACT_QUICK_GELU = 2,
+  B200SD_ACT_GEGLU = 3,
+  B200SD_ACT_GELU = 4 /* exact (erf) GELU: the MLP of OpenCLIP-bigG, SDXL's second text encoder */
+};
 enum b200sd_dtype { B200SD_ACT16 = 0, B200SD_F32 = 1 }; /* output type selector: act16 (see above) or f32 */
 
 int b200sd_version(void);

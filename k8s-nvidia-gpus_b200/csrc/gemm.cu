@@ -365,6 +365,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             } else if (p.act == B200SD_ACT_QUICK_GELU) {
 #pragma unroll
               for (int k = 0; k < 32; ++k) f[k] = quick_gelu_f(f[k]);
+            } else if (p.act == B200SD_ACT_GELU) {
+#pragma unroll
+              for (int k = 0; k < 32; ++k) f[k] = gelu_erf_f(f[k]);
             }
           }
           if (kRes) {
@@ -527,7 +530,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   B200SD_REQUIRE(aligned16(h.a0) && aligned16(h.a1) && aligned16(h.w) && aligned16(h.out) && aligned16(h.bias) &&
                      aligned16(h.residual),
                  B200SD_ERR_BAD_ALIGNMENT, "gemm: pointers must be 16-byte aligned");
-  B200SD_REQUIRE(h.act >= 0 && h.act <= 3, B200SD_ERR_BAD_ARGUMENT, "gemm: bad act %d", h.act);
+  B200SD_REQUIRE(h.act >= 0 && h.act <= 4, B200SD_ERR_BAD_ARGUMENT, "gemm: bad act %d", h.act);
   const bool geglu = (h.act == B200SD_ACT_GEGLU);
   const bool f32 = (h.out_dtype == B200SD_F32);
   const bool res = (h.residual != nullptr);

@@ -102,6 +102,13 @@ class DeviceWeights:
             return ops.pack_linear_weight(w)
         return self._get(("catlin", tuple(names), key), f)
 
+    def cat_conv(self, names, split):
+        """Row-concatenated linear weights whose K axis is split over several A sources (virtual concat)."""
+        def f():
+            w = torch.cat([self.raw(n + ".weight") for n in names], dim=0)
+            return ops.pack_conv_weight(w[:, :, None, None], tuple(split))
+        return self._get(("catconv", tuple(names), tuple(split)), f)
+
     def cat_bias(self, names, key=None, perm=None):
         def f():
             b = torch.cat([self.raw(n + ".bias") for n in names], dim=0)

@@ -11,7 +11,7 @@ from pathlib import Path
 _LIB_PATH = Path(__file__).resolve().parent / "libb200sd.so"
 _lib = None
 
-ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU = 0, 1, 2, 3
+ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU, ACT_GELU = 0, 1, 2, 3, 4
 ACT16, F32 = 0, 1
 BF16 = ACT16  # historical alias
 GN_NOALLOC_MAX_STATS = 16384  # B200SD_GN_NOALLOC_MAX_STATS

@@ -28,6 +28,16 @@ from .vae import VAEDecoderEngine
 MAX_EVALS = 1024
 
 
+def sinusoid(values: torch.Tensor, dim: int) -> torch.Tensor:
+    """diffusers `Timesteps(dim, flip_sin_to_cos=True, downscale_freq_shift=0)` on the host (fp32): [len(values), dim]
+    = [cos | sin](v * exp(-ln(10000) * i / (dim / 2))).  Used for SDXL's six size / crop ids (StableDiffusionXLPipeline
+    ._get_add_time_ids + UNet2DConditionModel.add_time_proj), which depend on the image size only."""
+    half = dim // 2
+    freqs = torch.exp(-np.log(10000.0) * torch.arange(half, dtype=torch.float32) / half)
+    a = values.to(torch.float32)[:, None] * freqs[None]
+    return torch.cat([torch.cos(a), torch.sin(a)], dim=-1)
+
+
 class PipelineOutput:
     def __init__(self, images, nsfw_content_detected=None, latents=None):
         self.images = images
@@ -54,12 +64,15 @@ class Job:
     `run(num_evals)` enqueues text encoder -> K/V projection -> denoise steps -> VAE decode on the current stream,
     reading token ids / initial latents from `ids_dev` / `init_latents` (already resident in HBM)."""
 
-    def __init__(self, pipe, batch, h, w, guidance_scale, cfg_on):
+    def __init__(self, pipe, batch, h, w, guidance_scale, cfg_on, zero_negative=False):
         self.pipe, self.batch, self.h, self.w = pipe, batch, h, w
         self.cfg_on = cfg_on
         dev = pipe.device
+        nenc = len(pipe.text_encoders)
         self.n_text = batch * (2 if cfg_on else 1)
-        self.ids_dev = torch.zeros(self.n_text * 77, dtype=torch.int32, device=dev)
+        # token ids of every text encoder back to back ([encoder][n_text * 77]); EOS row per sequence for the pooled one
+        self.ids_dev = torch.zeros(nenc * self.n_text * 77, dtype=torch.int32, device=dev)
+        self.eos_dev = torch.zeros(self.n_text, dtype=torch.int32, device=dev)
         self.init_latents = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=dev)
         self.latents = torch.zeros(batch, h * w, 4, dtype=torch.float32, device=dev)
         self.history = torch.zeros(4, batch, h * w, 4, dtype=torch.float32, device=dev)
@@ -67,26 +80,54 @@ class Job:
         self.step_table = torch.zeros(MAX_EVALS, 16, dtype=torch.float32, device=dev)
         self.step_counter = torch.zeros(2, dtype=torch.int32, device=dev)
         # pinned staging for the end-to-end path (host -> device inputs, device -> host images)
-        self.ids_host = torch.zeros(self.n_text * 77, dtype=torch.int32).pin_memory()
+        self.ids_host = torch.zeros(nenc * self.n_text * 77, dtype=torch.int32).pin_memory()
+        self.eos_host = torch.zeros(self.n_text, dtype=torch.int32).pin_memory()
         self.lat_host = torch.zeros(batch, h * w, 4, dtype=torch.float32).pin_memory()
         self.table_host = torch.zeros(MAX_EVALS, 16, dtype=torch.float32).pin_memory()
-        self.text_plan, self.ctx = pipe.text_encoder.build_plan(self.n_text, self.ids_dev)
-        self.kv_plan, self.kv = pipe.unet.build_kv_plan(self.n_text, self.ctx)
+        self.text_plans, ctxs, pooled = [], [], None
+        for e, enc in enumerate(pipe.text_encoders):
+            ids = self.ids_dev[e * self.n_text * 77:(e + 1) * self.n_text * 77]
+            plan, ctx, pl = enc.build_plan(self.n_text, ids, self.eos_dev)
+            self.text_plans.append(plan)
+            ctxs.append(ctx)
+            pooled = pl if pl is not None else pooled
+        self.ctx, self.pooled = ctxs, pooled
+        # SDXL, negative_prompt=None (force_zeros_for_empty_prompt): the unconditional half of every text output is 0
+        self.zero_plan = None
+        if zero_negative and cfg_on:
+            from .engine import Plan
+            self.zero_plan = Plan()
+            for t in ctxs + ([pooled] if pooled is not None else []):
+                self.zero_plan.calls.append(ops.memset_zero(t, batch * (t.numel() // self.n_text) * t.element_size()))
+        time_emb = None
+        if pipe.cfg["unet"].get("addition_embed_type") == "text_time":
+            f = pipe.vae_scale_factor
+            # add_time_ids = original_size + crops_coords_top_left + target_size, same for both CFG halves
+            ids6 = torch.tensor([h * f, w * f, 0, 0, h * f, w * f], dtype=torch.float32)
+            row = sinusoid(ids6, pipe.cfg["unet"]["addition_time_embed_dim"]).reshape(1, -1)
+            time_emb = row.repeat(self.n_text, 1).to(ops.act_dtype()).to(dev).contiguous()
+        self.kv_plan, self.kv, self.aug_emb = pipe.unet.build_kv_plan(self.n_text, ctxs, self.pooled, time_emb)
         self.step_plan, self.dbg = pipe.unet.build_step_plan(
             batch, h, w, self.latents, self.step_table, self.step_counter, self.kv, guidance_scale=guidance_scale,
-            cfg_on=cfg_on, history=self.history, cur_sample=self.cur_sample)
+            cfg_on=cfg_on, history=self.history, cur_sample=self.cur_sample, aug_emb=self.aug_emb)
         self.vae_plan, self.images = pipe.vae_engine.build_plan(batch, h, w, self.latents)
         f = pipe.vae_scale_factor
         self.img_host = torch.zeros(batch, h * f, w * f, 3, dtype=torch.uint8).pin_memory()
         # one eager pass validates every launch configuration before capture
-        self.text_plan.run()
-        self.kv_plan.run()
+        self.run_text()
         self.vae_plan.run()
         if pipe.use_cuda_graph:
             self.step_plan.capture()
         else:
             self.step_plan.run()
         torch.cuda.synchronize()
+
+    def run_text(self):
+        for pl in self.text_plans:
+            pl.run()
+        if self.zero_plan is not None:
+            self.zero_plan.run()
+        self.kv_plan.run()
 
     def reset(self):
         """Start a new generation from `init_latents` (device -> device)."""
@@ -95,8 +136,7 @@ class Job:
         self.history.zero_()
 
     def run(self, num_evals, decode=True, on_step=None):
-        self.text_plan.run()
-        self.kv_plan.run()
+        self.run_text()
         for i in range(num_evals):
             self.step_plan.launch()
             if on_step is not None:
@@ -105,17 +145,21 @@ class Job:
             self.vae_plan.run()
 
     def launches(self, num_evals, decode=True):
-        n = len(self.text_plan) + len(self.kv_plan) + num_evals * len(self.step_plan)
+        n = sum(len(pl) for pl in self.text_plans) + len(self.kv_plan) + num_evals * len(self.step_plan)
+        n += len(self.zero_plan) if self.zero_plan is not None else 0
         return n + (len(self.vae_plan) if decode else 0)
 
 
 class StableDiffusionPipeline:
-    def __init__(self, cfg: dict, unet_sd: dict, vae_sd: dict, text_sd: dict, tokenizer: CLIPTokenizer | None = None,
+    def __init__(self, cfg: dict, unet_sd: dict, vae_sd: dict, text_sd, tokenizer: CLIPTokenizer | None = None,
                  device: str = "cuda", scheduler: str | None = None):
+        """text_sd: one state dict, or a list with one per entry of cfg["text_encoders"] (SDXL: CLIP-L, OpenCLIP-bigG
+        with text_projection)."""
         if not torch.cuda.is_available():
             raise RuntimeError("b200sd needs a CUDA device (sm_100a); there is no CPU path")
-        if len(cfg["text_encoders"]) != 1 or cfg["unet"].get("addition_embed_type"):
-            raise NotImplementedError("dual text encoders / text_time conditioning (SDXL) are not wired yet")
+        text_sds = list(text_sd) if isinstance(text_sd, (list, tuple)) else [text_sd]
+        if len(text_sds) != len(cfg["text_encoders"]) or len(text_sds) > 2:
+            raise ValueError("one state dict per text encoder (at most two)")
         self.cfg = cfg
         dev = torch.device(device)
         if dev.index is None:
@@ -125,8 +169,17 @@ class StableDiffusionPipeline:
         self.unet = UNetEngine(cfg["unet"], unet_sd, self.device)
         self.vae_engine = VAEDecoderEngine(cfg["vae"], vae_sd, self.device)
         self.vae = _VaeHandle(self.vae_engine)
-        self.text_encoder = CLIPTextEngine(cfg["text_encoders"][0], text_sd, self.device)
+        self.text_encoders = [CLIPTextEngine(c, sd, self.device) for c, sd in zip(cfg["text_encoders"], text_sds)]
+        self.text_encoder = self.text_encoders[0]
         self.tokenizer = tokenizer or CLIPTokenizer.from_pretrained_or_synthetic(cfg["text_encoders"][0]["vocab_size"])
+        self.tokenizers = [self.tokenizer]
+        if len(self.text_encoders) == 2:
+            # SDXL's tokenizer_2: same vocabulary and merges, but pads with "!" (id 0) instead of <|endoftext|>
+            import copy
+            tok2 = copy.copy(self.tokenizer)
+            tok2.pad_token_id = 0
+            self.tokenizers.append(tok2)
+        self.is_xl = cfg["unet"].get("addition_embed_type") == "text_time"
         self.scheduler_kind = (scheduler or cfg["scheduler"]["type"]).lower()
         self.vae_scale_factor = self.vae_engine.scale_factor
         self.use_cuda_graph = os.environ.get("B200SD_NO_GRAPH", "0") != "1"
@@ -149,7 +202,8 @@ class StableDiffusionPipeline:
         kw = dict(round_dtype=ops.act_dtype(), device=device, store_dtype=ops.act_dtype())  # drawn on the GPU
         unet_sd = Wt.random_state_dict(Wt.unet_schema(cfg["unet"]), seed, **kw)
         vae_sd = Wt.random_state_dict(Wt.vae_decoder_schema(cfg["vae"]), seed + 1, **kw)
-        text_sd = Wt.random_state_dict(Wt.clip_text_schema(cfg["text_encoders"][0]), seed + 2, **kw)
+        text_sd = [Wt.random_state_dict(Wt.clip_text_schema(c), seed + 2 + i, **kw)
+                   for i, c in enumerate(cfg["text_encoders"])]
         pipe = cls(cfg, unet_sd, vae_sd, text_sd, device=device, scheduler=scheduler)
         pipe.model_id = model_id
         return pipe
@@ -165,10 +219,10 @@ class StableDiffusionPipeline:
         return self
 
     # ------------------------------------------------------------------ stages
-    def job(self, batch, h, w, guidance_scale, cfg_on) -> Job:
-        key = (batch, h, w, float(guidance_scale), cfg_on)
+    def job(self, batch, h, w, guidance_scale, cfg_on, zero_negative=False) -> Job:
+        key = (batch, h, w, float(guidance_scale), cfg_on, bool(zero_negative))
         if key not in self._jobs:
-            self._jobs[key] = Job(self, batch, h, w, guidance_scale, cfg_on)
+            self._jobs[key] = Job(self, batch, h, w, guidance_scale, cfg_on, zero_negative)
         return self._jobs[key]
 
     def make_schedule(self, num_inference_steps, scheduler=None):
@@ -177,9 +231,16 @@ class StableDiffusionPipeline:
                                **{k: v for k, v in self.cfg["scheduler"].items() if k != "type"})
 
     def tokenize(self, prompts, negative, cfg_on):
-        """int32 [n_text * 77] in encode_prompt order: [negative...; positive...]."""
+        """int32 [n_encoders * n_text * 77], per encoder in encode_prompt order: [negative...; positive...]."""
         texts = (list(negative) if cfg_on else []) + list(prompts)
-        return torch.tensor(self.tokenizer(texts), dtype=torch.int32).reshape(-1)
+        return torch.cat([torch.tensor(tok(texts), dtype=torch.int32).reshape(-1) for tok in self.tokenizers])
+
+    def eos_rows(self, ids: torch.Tensor, n_text: int) -> torch.Tensor:
+        """Flat row index (n * 77 + position) of the first EOS token of every sequence of the LAST encoder - where
+        CLIPTextModelWithProjection pools (transformers modeling_clip.py: first position equal to eos_token_id)."""
+        last = ids.reshape(len(self.tokenizers), n_text, 77)[-1]
+        pos = (last == self.tokenizers[-1].eos_token_id).to(torch.int32).argmax(dim=-1)
+        return (torch.arange(n_text, dtype=torch.int32) * 77 + pos.to(torch.int32)).to(torch.int32)
 
     def prepare_latents(self, batch, h, w, generator, init_sigma):
         """randn_tensor semantics: one draw of the full batch for a single generator, one [1,4,h,w] draw per image for
@@ -229,10 +290,14 @@ class StableDiffusionPipeline:
         sched = self.make_schedule(num_inference_steps, scheduler)
         if sched.num_evals > MAX_EVALS:
             raise ValueError("too many inference steps")
-        job = self.job(batch, h, w, guidance_scale, cfg_on)
+        # StableDiffusionXLPipeline (force_zeros_for_empty_prompt): no negative prompt -> zero embeddings, not ""
+        zero_negative = self.is_xl and negative_prompt is None
+        job = self.job(batch, h, w, guidance_scale, cfg_on, zero_negative)
 
         # host side: tokenise, draw latents (NCHW, upstream RNG order) -> NHWC pinned staging
-        job.ids_host.copy_(self.tokenize(prompts, negative, cfg_on))
+        ids = self.tokenize(prompts, negative, cfg_on)
+        job.ids_host.copy_(ids)
+        job.eos_host.copy_(self.eos_rows(ids, job.n_text))
         if latents is None:
             lat = self.prepare_latents(batch, h, w, generator, sched.init_noise_sigma)
         else:
@@ -243,6 +308,7 @@ class StableDiffusionPipeline:
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         ev[0].record()
         job.ids_dev.copy_(job.ids_host, non_blocking=True)
+        job.eos_dev.copy_(job.eos_host, non_blocking=True)
         job.init_latents.copy_(job.lat_host, non_blocking=True)
         job.step_table.copy_(job.table_host, non_blocking=True)
         job.reset()
@@ -272,6 +338,17 @@ class StableDiffusionPipeline:
         else:
             raise ValueError(f"unknown output_type {output_type!r}")
         return PipelineOutput(images=images, nsfw_content_detected=None)
+
+
+class StableDiffusionXLPipeline(StableDiffusionPipeline):
+    """`diffusers.StableDiffusionXLPipeline` surface (BASELINE.json configs[3]): two text encoders (penultimate hidden
+    states concatenated, pooled + projected output of the second), `text_time` size conditioning with
+    original_size = target_size = (height, width) and no crop, Euler-discrete by default, and zero (not "")
+    unconditional embeddings when no negative prompt is given."""
+
+    @classmethod
+    def from_pretrained(cls, model_id: str = "sdxl", **kw):
+        return super().from_pretrained(model_id, **kw)
 
 
 def make_generator(seed: int, device: str = "cpu") -> torch.Generator:

@@ -57,20 +57,50 @@ class UNetEngine:
         self.seq = 77
 
     # ------------------------------------------------------------------ prompt-dependent precompute
-    def build_kv_plan(self, nctx: int, ctx: torch.Tensor):
-        """ctx: bf16 [nctx, 77, cross_dim] -> per attention block bf16 [nctx, 77, 2C] (K | V), computed once."""
+    def build_kv_plan(self, nctx: int, ctx, text_embeds: torch.Tensor | None = None,
+                      time_ids_emb: torch.Tensor | None = None):
+        """ctx: 16-bit [nctx, 77, cross_dim], or one such tensor per text encoder (widths adding up to cross_dim) ->
+        per attention block 16-bit [nctx, 77, 2C] (K | V), computed once per
+        prompt batch.  SDXL (`addition_embed_type == "text_time"`): also aug_emb fp32 [nctx, 4*C0] =
+        add_embedding(concat(text_embeds [nctx, P], time_ids_emb [nctx, 6*D])) - the concat is virtual (two A sources
+        of one GEMM).  Returns (plan, kv dict, aug_emb or None)."""
         bld = Builder(self.device)
         W = self.W
-        ctx_act = Act(ctx, nctx, 1, ctx.shape[1], ctx.shape[2])
+        ctxs = list(ctx) if isinstance(ctx, (list, tuple)) else [ctx]
+        if len(ctxs) > 2:
+            raise ValueError("at most two text encoders")
+        seq = ctxs[0].shape[1]
+        dims = tuple(int(t.shape[2]) for t in ctxs)
+        if sum(dims) != self.cfg["cross_attention_dim"]:
+            raise ValueError(f"text encoder widths {dims} do not add up to cross_attention_dim")
+        self.seq = seq
         kv = {}
         for p, c, heads, depth in _attn_blocks(self.cfg):
             for l in range(depth):
                 b = f"{p}.transformer_blocks.{l}.attn2"
-                w = W.cat_linear([b + ".to_k", b + ".to_v"])
-                out = bld.persistent((nctx, 1, ctx.shape[1], 2 * c), zero=False)
-                bld.add(ops.gemm(ctx, w, out, nimg=1, h=1, w_=ctx_act.rows, c0=ctx_act.c, n=2 * c, ksize=1))
+                # the channel concat of the encoders' outputs is virtual: two A sources walked along K
+                w = W.cat_conv([b + ".to_k", b + ".to_v"], dims)
+                out = bld.persistent((nctx, 1, seq, 2 * c), zero=False)
+                bld.add(ops.gemm(ctxs[0], w, out, nimg=1, h=1, w_=nctx * seq, c0=dims[0],
+                                 a1=ctxs[1] if len(ctxs) > 1 else None, c1=dims[1] if len(ctxs) > 1 else 0, n=2 * c,
+                                 ksize=1))
                 kv[b] = out
-        return bld.finish(), kv
+        aug = None
+        if self.cfg.get("addition_embed_type") == "text_time":
+            if text_embeds is None or time_ids_emb is None:
+                raise ValueError("text_time conditioning needs text_embeds and the time-id embedding")
+            temb_dim = self.cfg["block_out_channels"][0] * 4
+            c0, c1 = text_embeds.shape[1], time_ids_emb.shape[1]
+            if c0 + c1 != self.cfg["projection_class_embeddings_input_dim"]:
+                raise ValueError(f"text_embeds ({c0}) + time ids ({c1}) != projection_class_embeddings_input_dim")
+            h1 = bld.alloc((nctx, 1, 1, temb_dim))
+            bld.add(ops.gemm(text_embeds, W.conv("add_embedding.linear_1", (c0, c1)), h1, nimg=1, h=1, w_=nctx, c0=c0,
+                             a1=time_ids_emb, c1=c1, n=temb_dim, ksize=1, bias=W.vec("add_embedding.linear_1.bias"),
+                             act=L.ACT_SILU))
+            aug = bld.persistent((nctx, temb_dim), dtype=torch.float32, zero=False)
+            bld.add(ops.gemm(h1, W.conv("add_embedding.linear_2"), aug, nimg=1, h=1, w_=nctx, c0=temb_dim, n=temb_dim,
+                             ksize=1, bias=W.vec("add_embedding.linear_2.bias")))
+        return bld.finish(), kv, aug
 
     # ------------------------------------------------------------------ one denoise step
     def build_step_plan(self, batch: int, h: int, w: int, latents, step_table, step_counter, kv: dict, *,

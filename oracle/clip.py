@@ -85,10 +85,33 @@ class _TextTransformer(nn.Module):
 
 
 class CLIPTextModel(nn.Module):
+    """CLIPTextModel, or CLIPTextModelWithProjection when cfg has "projection_dim" (SDXL's second encoder: state-dict
+    key `text_projection.weight`, no bias)."""
+
     def __init__(self, cfg):
         super().__init__()
         self.cfg = cfg
         self.text_model = _TextTransformer(cfg)
+        if cfg.get("projection_dim"):
+            self.text_projection = nn.Linear(cfg["hidden_size"], cfg["projection_dim"], bias=False)
+
+    def encode_xl(self, ids, eos_token_id):
+        """StableDiffusionXLPipeline.encode_prompt's use of one encoder: (hidden_states[-2], text_embeds or None).
+        text_embeds = text_projection(pooled), pooled = final_layer_norm(last hidden state) at the first EOS token
+        (transformers 4.44.2 modeling_clip.py CLIPTextTransformer.forward, eos_token_id != 2 branch; with CLIP's
+        vocabulary the legacy argmax branch picks the same position because EOS is the largest id)."""
+        tm = self.text_model
+        x = tm.embeddings(ids)
+        hidden = [x]
+        for layer in tm.encoder.layers:
+            x = layer(x)
+            hidden.append(x)
+        embeds = None
+        if self.cfg.get("projection_dim"):
+            last = tm.final_layer_norm(x)
+            pos = (ids == eos_token_id).int().argmax(dim=-1)
+            embeds = self.text_projection(last[torch.arange(ids.shape[0]), pos])
+        return hidden[-2], embeds
 
     def forward(self, ids, output="last_hidden_state"):
         """ids int64 [B,77] -> [B,77,C].  "last_hidden_state" (SD1.5: post final LN) or "penultimate" (SDXL:

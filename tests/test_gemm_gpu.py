@@ -83,6 +83,10 @@ def test_linear_epilogues(cuda_lib, b200sd):
     torch.cuda.synchronize()
     z = acc + bias
     _report("quick_gelu", out, z * torch.sigmoid(1.702 * z), 1e-2)
+    # exact (erf) gelu, fp32 out so the activation itself is checked to ~1e-6
+    ops.gemm(x, wp, out32, nimg=1, h=1, w_=M, c0=K, n=N, bias=bias, act=L.ACT_GELU)(s)
+    torch.cuda.synchronize()
+    _report("gelu fp32", out32, F.gelu(z), 1e-5)
     # GEGLU: weight [2F, K] -> packed; out [M, F]
     Fh = 256
     w2 = _rand(2 * Fh, K, scale=K ** -0.5)

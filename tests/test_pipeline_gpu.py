@@ -48,13 +48,13 @@ def test_text_encoder_parity(tiny):
     ids = pipe.tokenize(PROMPTS, [""] * len(PROMPTS), True)
     job = pipe.job(len(PROMPTS), 32, 32, 7.5, True)
     job.ids_dev.copy_(ids)
-    job.text_plan.run()
+    job.text_plans[0].run()
     torch.cuda.synchronize()
     ref_ids = oracle.tokenize([""] * len(PROMPTS) + PROMPTS)
     assert ids.view(-1, 77).tolist() == ref_ids  # bit-exact tokenisation
     with torch.no_grad():
         ref = oracle.text_encoder(torch.tensor(ref_ids, dtype=torch.long))
-    r = _rel(job.ctx.cpu(), ref)
+    r = _rel(job.ctx[0].cpu(), ref)
     print("text encoder rel err", r)
     assert r < 1e-2
 
