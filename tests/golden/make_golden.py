@@ -6,6 +6,8 @@
                     a prompt corpus, for the deterministic synthetic vocabularies of size 49408 and 1000
   clip_tiny.pt    — transformers.CLIPTextModel (tiny config, weights from weights.random_state_dict seed 2)
                     last_hidden_state for two token rows
+  clip_xl2_tiny.pt — transformers.CLIPTextModelWithProjection (tiny_xl second encoder, seed 3): hidden_states[-2] and
+                    text_embeds for two token rows padded with id 0
 
 Run from the repo root:  python tests/golden/make_golden.py     (needs `transformers`; not needed to run the tests)
 """
@@ -54,6 +56,26 @@ def main():
     with torch.no_grad():
         out = hf(input_ids=ids).last_hidden_state
     torch.save({"ids": ids, "last_hidden_state": out, "weights_seed": 2}, os.path.join(HERE, "clip_tiny.pt"))
+
+    # SDXL's second encoder: CLIPTextModelWithProjection (gelu MLP), hidden_states[-2] and text_embeds, with the
+    # second tokenizer's padding (id 0) so that the EOS position - not the padding - decides the pooled row
+    from transformers import CLIPTextModelWithProjection
+    cfg2 = W.load_config("tiny_xl")["text_encoders"][1]
+    sd2 = W.random_state_dict(W.clip_text_schema(cfg2), 3)
+    hf2 = CLIPTextModelWithProjection(CLIPTextConfig(
+        vocab_size=cfg2["vocab_size"], hidden_size=cfg2["hidden_size"], intermediate_size=cfg2["intermediate_size"],
+        num_hidden_layers=cfg2["num_layers"], num_attention_heads=cfg2["num_heads"], max_position_embeddings=77,
+        hidden_act="gelu", layer_norm_eps=cfg2["eps"], projection_dim=cfg2["projection_dim"], bos_token_id=998,
+        eos_token_id=999, pad_token_id=0)).eval()
+    print(hf2.load_state_dict(sd2, strict=False))
+    ids2 = ids.clone()
+    for r in range(ids2.shape[0]):
+        eos = int((ids2[r] == 999).int().argmax())
+        ids2[r, eos + 1:] = 0
+    with torch.no_grad():
+        o2 = hf2(input_ids=ids2, output_hidden_states=True)
+    torch.save({"ids": ids2, "penultimate": o2.hidden_states[-2], "text_embeds": o2.text_embeds, "weights_seed": 3},
+               os.path.join(HERE, "clip_xl2_tiny.pt"))
     print("wrote", os.listdir(HERE))
 
 

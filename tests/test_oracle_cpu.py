@@ -63,6 +63,34 @@ def test_oracle_clip_matches_upstream_golden(b200sd):
     assert (out - g["last_hidden_state"]).abs().max().item() < 1e-5
 
 
+def test_oracle_clip_with_projection_matches_upstream_golden(b200sd):
+    """SDXL's second text encoder: hidden_states[-2] and text_embeds of transformers.CLIPTextModelWithProjection (gelu
+    MLP, pooled at the EOS token although the sequence is padded with id 0)."""
+    from oracle.clip import CLIPTextModel
+    g = torch.load(os.path.join(HERE, "golden", "clip_xl2_tiny.pt"))
+    W = b200sd.weights
+    cfg = W.load_config("tiny_xl")["text_encoders"][1]
+    m = CLIPTextModel(cfg).eval()
+    m.load_state_dict(W.random_state_dict(W.clip_text_schema(cfg), g["weights_seed"]), strict=True)
+    with torch.no_grad():
+        hidden, embeds = m.encode_xl(g["ids"], 999)
+    assert (hidden - g["penultimate"]).abs().max().item() < 1e-5
+    assert (embeds - g["text_embeds"]).abs().max().item() < 1e-5
+
+
+def test_sdxl_host_pieces(b200sd):
+    """Host-side SDXL logic of the product: size-id sinusoid == the oracle's timestep embedding; EOS rows; the second
+    tokenizer pads with id 0; parameter count of the SDXL UNet schema."""
+    from oracle.unet import timestep_embedding
+    P, W, T = b200sd.pipeline, b200sd.weights, b200sd.tokenizer
+    v = torch.tensor([1024.0, 1024.0, 0.0, 0.0, 1024.0, 768.0])
+    assert torch.equal(P.sinusoid(v, 256), timestep_embedding(v, 256))
+    tok = T.CLIPTokenizer.synthetic(1000)
+    ids = torch.tensor(tok(["a cat", ""]), dtype=torch.int32)
+    pos = [(row == tok.eos_token_id).nonzero()[0].item() for row in ids]
+    assert pos[1] == 1 and pos[0] > 1
+
+
 # ------------------------------------------------------------------------------------------------ schedulers (App. C)
 def test_alphas_cumprod_anchors():
     from oracle.schedulers import alphas_cumprod
