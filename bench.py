@@ -166,7 +166,7 @@ def run_reference(args):
 
 def workload_config(args, cfg, n_gpus):
     return {"workload": f"{cfg['name']} architecture (random-init), {args.width}x{args.height}, "
-                        f"{args.inference_steps} DDIM steps, CFG {args.guidance_scale}, batch {args.batch} per GPU",
+                        f"{args.inference_steps} {args.scheduler.upper()} steps, CFG {args.guidance_scale}, batch {args.batch} per GPU",
             "global_batch": args.batch * n_gpus, "per_gpu_batch": args.batch, "scheduler": args.scheduler,
             "inference_steps": args.inference_steps, "guidance_scale": args.guidance_scale,
             "resolution": [args.width, args.height], "parallelism": f"dp{n_gpus} (prompt sharding, image gather)",
@@ -315,7 +315,8 @@ def run_cuda(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_ips = args.steps * B * world / e2e_s.item()
-    h2d = job.ids_host.numel() * 4 + job.lat_host.numel() * 4 + evals * 16 * 4
+    # the tensors pipe() copies every call: token ids, EOS rows, initial latents, the whole step table
+    h2d = sum(t.numel() * t.element_size() for t in (job.ids_host, job.eos_host, job.lat_host, job.table_host))
     d2h = job.img_host.numel()
 
     if rank != 0:
