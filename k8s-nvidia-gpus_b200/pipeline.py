@@ -265,6 +265,7 @@ class StableDiffusionPipeline:
                  height: int | None = None, generator=None, latents: torch.Tensor | None = None,
                  negative_prompt=None, output_type: str = "pil", scheduler: str | None = None,
                  callback_on_step_end=None, **_ignored):
+        torch.cuda.set_device(self.device)  # calls may come from any thread (the server's batching worker)
         f = self.vae_scale_factor
         height = height or self.cfg["unet"]["sample_size"] * f
         width = width or self.cfg["unet"]["sample_size"] * f

@@ -7,9 +7,12 @@ Same surface as the FastAPI app embedded in cluster-config/apps/sd15-api/configm
   GET  /healthz   {"ok": true}                                   (configmap.yaml:60-62; the Deployment's readinessProbe)
   GET  /last      last PNG or 404                                (configmap.yaml:80-84)
   GET  /          HTML preview of the last image                 (configmap.yaml:64-78)
-Differences, all deliberate: the pipeline is b200sd's; access to it is serialised with a lock (the reference calls its
-stateful pipeline from Starlette's thread pool unguarded, configmap.yaml:105-112); the seed drives a CPU generator —
-the reference's CPU branch (configmap.yaml:92) — so a seed reproduces the oracle's image.
+Differences, all deliberate: the pipeline is b200sd's; concurrent requests of the same shape are coalesced into one
+batched pipeline call by a single worker thread (batcher.py; B200SD_MAX_BATCH, default 8, and B200SD_BATCH_WAIT_MS,
+default 10 - the reference calls its stateful pipeline from Starlette's thread pool unguarded, one image per call,
+configmap.yaml:105-112); PNG encoding stays on the request threads, off the GPU path; the seed drives a CPU
+generator — the reference's CPU branch (configmap.yaml:92) — so a seed reproduces the oracle's image whether or not
+the request was batched.
 
     uvicorn app:app --host 0.0.0.0 --port 8000      # from the repo root, exactly the command of deployment.yaml:42
                                                     # (env MODEL_ID as in deployment.yaml:45-46)
@@ -23,7 +26,6 @@ import os
 import time
 from threading import Lock
 
-import torch
 from fastapi import FastAPI, HTTPException
 from fastapi.responses import HTMLResponse, Response
 from pydantic import BaseModel
@@ -42,11 +44,14 @@ class GenReq(BaseModel):
     height: int | None = DEFAULT_SIZE
 
 
-def create_app(pipe=None, pipe_factory=None) -> FastAPI:
+def create_app(pipe=None, pipe_factory=None, max_batch: int | None = None, max_wait_ms: float | None = None) -> FastAPI:
     """pipe: an object with the StableDiffusionPipeline call surface; pipe_factory: built lazily on first use."""
+    from .batcher import DynamicBatcher
     app = FastAPI(title="SD15 Minimal API (b200sd)")
     state = {"pipe": pipe, "last": None}
     last_lock, pipe_lock = Lock(), Lock()
+    max_batch = int(os.getenv("B200SD_MAX_BATCH", "8")) if max_batch is None else max_batch
+    max_wait_ms = float(os.getenv("B200SD_BATCH_WAIT_MS", "10")) if max_wait_ms is None else max_wait_ms
 
     def get_pipe():
         if state["pipe"] is None:
@@ -54,6 +59,9 @@ def create_app(pipe=None, pipe_factory=None) -> FastAPI:
                 if state["pipe"] is None:
                     state["pipe"] = (pipe_factory or _default_factory)()
         return state["pipe"]
+
+    batcher = DynamicBatcher(get_pipe, max_batch=max_batch, max_wait_ms=max_wait_ms)
+    app.state.batcher = batcher
 
     @app.get("/healthz")
     def healthz():
@@ -82,14 +90,11 @@ def create_app(pipe=None, pipe_factory=None) -> FastAPI:
         steps = req.steps or DEFAULT_STEPS
         gs = req.guidance_scale or DEFAULT_GUIDANCE
         width, height = req.width or DEFAULT_SIZE, req.height or DEFAULT_SIZE
-        gen = torch.Generator(device="cpu").manual_seed(req.seed) if req.seed is not None else None
         t0 = time.time()
         logger.info("Generating prompt='%s' steps=%s guidance=%.2f seed=%s size=%sx%s", req.prompt, steps, gs,
                     req.seed if req.seed is not None else "auto", width, height)
-        p = get_pipe()
-        with pipe_lock:  # one generation at a time per GPU; pipeline errors surface as 500 like the reference's
-            image = p(req.prompt, num_inference_steps=steps, guidance_scale=gs, width=width, height=height,
-                      generator=gen).images[0]
+        # joins the batch of same-shaped requests in flight; pipeline errors surface as 500 like the reference's
+        image = batcher.generate(req.prompt, steps, gs, width, height, req.seed)
         buf = io.BytesIO()
         image.save(buf, format="PNG")
         png = buf.getvalue()

@@ -138,6 +138,63 @@ def test_http_contract_matches_reference(b200sd):
     assert "data:image/png;base64," in c.get("/").text
 
 
+def test_dynamic_batcher_coalesces_routes_and_pads(b200sd):
+    """concurrent same-shape requests become one batched pipe() call (padded to a bucket size),
+    each waiter gets ITS image (same as a lone request with that seed), other shapes are not mixed in, and a pipeline
+    failure reaches every waiter of the batch."""
+    import importlib
+    import threading
+    B = importlib.import_module("k8s-nvidia-gpus_b200.batcher")
+    fake = FakePipe()
+    gate = threading.Event()
+
+    def slow_pipe(*a, **kw):
+        gate.wait(5)  # holds the worker so that the following requests pile up in the queue
+        return fake(*a, **kw)
+
+    bt = B.DynamicBatcher(lambda: slow_pipe, max_batch=4, max_wait_ms=1, buckets=(1, 2, 4, 8), output_type="u8")
+    first = bt.submit("warm", 5, 7.5, 8, 8, seed=1)          # occupies the worker
+    import time
+    time.sleep(0.05)
+    futs = [bt.submit(f"prompt {i}", 5, 7.5, 8, 8, seed=10 + i) for i in range(3)]
+    other = bt.submit("other shape", 9, 7.5, 8, 8, seed=3)
+    gate.set()
+    imgs = [f.result(10) for f in futs]
+    first.result(10), other.result(10)
+    solo = FakePipe()
+    for i, im in enumerate(imgs):  # same image as an unbatched call with that prompt and seed
+        ref = solo(f"prompt {i}", num_inference_steps=5, width=8, height=8,
+                   generator=torch.Generator().manual_seed(10 + i), output_type="u8").images[0]
+        assert np.array_equal(im, ref)
+    sizes = [len(c["prompts"]) for c in fake.calls]
+    assert sizes == [1, 4, 1]                               # 3 requests padded to the bucket of 4; the odd shape alone
+    assert fake.calls[1]["prompts"][:3] == [f"prompt {i}" for i in range(3)] and fake.calls[2]["steps"] == 9
+    assert bt.stats["requests"] == 5 and bt.stats["batches"] == 3 and bt.stats["padded"] == 1
+
+    def broken(*a, **kw):
+        raise RuntimeError("device fell over")
+    bt2 = B.DynamicBatcher(lambda: broken, max_batch=2, max_wait_ms=20, output_type="u8")
+    fa, fb = bt2.submit("a", 5, 7.5, 8, 8, 1), bt2.submit("b", 5, 7.5, 8, 8, 2)
+    for f in (fa, fb):
+        with pytest.raises(RuntimeError, match="fell over"):
+            f.result(10)
+    bt.shutdown(), bt2.shutdown()
+
+
+def test_http_server_batches_concurrent_requests(b200sd):
+    from fastapi.testclient import TestClient
+    from concurrent.futures import ThreadPoolExecutor
+    import importlib
+    server = importlib.import_module("k8s-nvidia-gpus_b200.server")
+    fake = FakePipe()
+    c = TestClient(server.create_app(pipe=fake, max_batch=8, max_wait_ms=200))
+    with ThreadPoolExecutor(6) as ex:
+        rs = list(ex.map(lambda i: c.post("/generate", json={"prompt": f"p{i}", "seed": i, "width": 16, "height": 16,
+                                                             "steps": 4}), range(6)))
+    assert all(r.status_code == 200 and r.content[:4] == b"\x89PNG" for r in rs)
+    assert len(fake.calls) < 6 and sum(len(c_["prompts"]) for c_ in fake.calls) >= 6   # coalesced
+
+
 # ------------------------------------------------------------------------------------------------ B1: CLI
 class _Stub(BaseHTTPRequestHandler):
     bodies = []

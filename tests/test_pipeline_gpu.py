@@ -100,3 +100,30 @@ def test_rejects_bad_size(tiny):
     _, _, pipe = tiny
     with pytest.raises(ValueError, match="divisible by 8"):
         pipe("x", num_inference_steps=1, width=60, height=64)
+
+
+def test_dynamic_batching_is_transparent(tiny, b200sd):
+    """requests coalesced by the server's batcher (3 requests -> one padded batch of 4, run on the
+    batcher's worker thread) get exactly the image a lone `pipe(prompt, generator=seeded)` call gives."""
+    import importlib
+    import threading
+    B = importlib.import_module("k8s-nvidia-gpus_b200.batcher")
+    cfg, oracle, pipe = tiny
+    prompts = PROMPTS + ["a lighthouse on a cliff"]
+    solo = [pipe(p, num_inference_steps=3, guidance_scale=7.5, width=64, height=64,
+                 generator=torch.Generator().manual_seed(50 + i), output_type="u8").images[0]
+            for i, p in enumerate(prompts)]
+    gate = threading.Event()
+
+    def get_pipe():
+        gate.wait(10)
+        return pipe
+    bt = B.DynamicBatcher(get_pipe, max_batch=4, max_wait_ms=5, output_type="u8")
+    futs = [bt.submit(p, 3, 7.5, 64, 64, seed=50 + i) for i, p in enumerate(prompts)]
+    gate.set()
+    got = [f.result(120) for f in futs]
+    bt.shutdown()
+    assert bt.stats["largest"] >= 2
+    for a, b in zip(got, solo):
+        d = np.abs(a.astype(np.int32) - b.astype(np.int32))
+        assert d.max() <= 2, d.max()  # GroupNorm atomics order only
