@@ -8,6 +8,7 @@ from . import lib  # noqa: F401
 from . import ops  # noqa: F401
 from . import tokenizer  # noqa: F401
 from . import weights  # noqa: F401
+from . import checkpoint  # noqa: F401
 from . import schedulers  # noqa: F401
 from . import engine  # noqa: F401
 from . import clip  # noqa: F401

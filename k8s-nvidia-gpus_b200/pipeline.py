@@ -19,6 +19,7 @@ import torch
 
 from . import ops
 from . import schedulers as S
+from . import checkpoint as Ck
 from . import weights as Wt
 from .clip import CLIPTextEngine
 from .tokenizer import CLIPTokenizer
@@ -191,10 +192,19 @@ class StableDiffusionPipeline:
     @classmethod
     def from_pretrained(cls, model_id: str = "sd15", torch_dtype=None, device: str = "cuda", seed: int = 0,
                         scheduler: str | None = None, **_ignored):
-        """model_id: a config name under configs/ ("sd15", "tiny"), a config .json path, or a hub-style id such as
-        "runwayml/stable-diffusion-v1-5" (mapped to the sd15 architecture).  No checkpoints exist offline, so
-        weights are random-init (seeded) in the diffusers key layout; `torch_dtype` is accepted for signature
+        """model_id: a checkpoint directory in diffusers layout (model_index.json, */config.json, *.safetensors,
+        tokenizer/, scheduler/ - loaded as is), a config name under configs/ ("sd15", "tiny", "sdxl"), a config .json
+        path, or a hub-style id such as "runwayml/stable-diffusion-v1-5" (mapped to the sd15 architecture).  Without a
+        checkpoint directory the weights are random-init (seeded) in the diffusers key layout; `torch_dtype` is accepted for signature
         compatibility (compute is 16-bit operands with fp32 accumulation and statistics; lib.act_dtype())."""
+        if Ck.is_checkpoint_dir(model_id):
+            # a real checkpoint in diffusers layout (SURVEY §8(f) rank 3): configs, safetensors weights, scheduler
+            # default (PNDM for SD1.5, Euler for SDXL) and the tokenizer's vocab.json / merges.txt
+            cfg, unet_sd, vae_sd, text_sds, tok_dir = Ck.load_diffusers_dir(model_id)
+            tok = CLIPTokenizer.from_files(tok_dir) if tok_dir else None
+            pipe = cls(cfg, unet_sd, vae_sd, text_sds, tokenizer=tok, device=device, scheduler=scheduler)
+            pipe.model_id = model_id
+            return pipe
         name = model_id
         if not os.path.exists(model_id) and not os.path.exists(os.path.join(Wt.CONFIG_DIR, f"{model_id}.json")):
             name = "sdxl" if "xl" in model_id.lower() else "sd15"

@@ -195,6 +195,58 @@ def test_http_server_batches_concurrent_requests(b200sd):
     assert len(fake.calls) < 6 and sum(len(c_["prompts"]) for c_ in fake.calls) >= 6   # coalesced
 
 
+# ------------------------------------------------------------------------------------------------ real checkpoints
+@pytest.mark.parametrize("name,sched", [("tiny", "PNDMScheduler"), ("tiny_xl", "EulerDiscreteScheduler")])
+def test_diffusers_checkpoint_directory_loads(b200sd, tmp_path, name, sched):
+    """a checkpoint directory in diffusers layout (written with the upstream safetensors
+    library, upstream config key names, legacy VAE attention names, fp16 storage, encoder-side and position_ids
+    extras) comes back as this repo's config + exactly the stored tensors."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    from ckpt_util import write_diffusers_dir
+    W, T, C = b200sd.weights, b200sd.tokenizer, b200sd.checkpoint
+    cfg = W.load_config(name)
+    usd = W.random_state_dict(W.unet_schema(cfg["unet"]), 0)
+    vsd = W.random_state_dict(W.vae_decoder_schema(cfg["vae"]), 1)
+    tsd = [W.random_state_dict(W.clip_text_schema(c), 2 + i) for i, c in enumerate(cfg["text_encoders"])]
+    root = write_diffusers_dir(str(tmp_path / "ckpt"), cfg, usd, vsd, tsd, T, scheduler_class=sched)
+    assert C.is_checkpoint_dir(root)
+    cfg2, usd2, vsd2, tsd2, tok_dir = C.load_diffusers_dir(root)
+    for key in ("unet", "vae", "text_encoders"):
+        a, b = cfg[key], cfg2[key]
+        if key == "unet":
+            a = {k: v for k, v in a.items()}
+            b = {k: v for k, v in b.items() if k in a}
+        assert a == b, key
+    assert cfg2["scheduler"]["type"] == {"PNDMScheduler": "pndm", "EulerDiscreteScheduler": "euler"}[sched]
+    assert cfg2["scheduler"]["steps_offset"] == 1
+    for ref, got in [(usd, usd2), (vsd, vsd2)] + list(zip(tsd, tsd2)):
+        assert list(ref) == list(got)
+        for k in ref:  # random_state_dict values are fp16-representable: the fp16 file holds them exactly
+            assert got[k].dtype == torch.float16 and torch.equal(got[k].float(), ref[k]), k
+    tok = T.CLIPTokenizer.from_files(tok_dir)
+    assert tok(["a panda"]) == T.CLIPTokenizer.synthetic(cfg["text_encoders"][0]["vocab_size"])(["a panda"])
+    # a file that does not match the architecture is refused with the offending keys named
+    bad = dict(usd)
+    bad.pop("conv_in.weight")
+    from safetensors.torch import save_file
+    save_file({k: v.half() for k, v in bad.items()}, os.path.join(root, "unet", "diffusion_pytorch_model.safetensors"))
+    with pytest.raises(ValueError, match="conv_in.weight"):
+        C.load_diffusers_dir(root)
+
+
+def test_safetensors_reader_matches_upstream(b200sd, tmp_path):
+    from safetensors.torch import save_file
+    t = {"a": torch.randn(3, 5), "b": torch.randn(7).to(torch.bfloat16), "c": torch.randn(2, 2, 2).half(),
+         "d": torch.arange(6).reshape(2, 3), "e": torch.tensor(3.5)}
+    path = str(tmp_path / "x.safetensors")
+    save_file(t, path, metadata={"format": "pt"})
+    got = b200sd.checkpoint.read_safetensors(path)
+    assert set(got) == set(t)
+    for k in t:
+        assert got[k].dtype == t[k].dtype and got[k].shape == t[k].shape and torch.equal(got[k], t[k])
+    assert set(b200sd.checkpoint.read_safetensors(path, keep=lambda k: k in "ab")) == {"a", "b"}
+
+
 # ------------------------------------------------------------------------------------------------ B1: CLI
 class _Stub(BaseHTTPRequestHandler):
     bodies = []

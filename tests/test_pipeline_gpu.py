@@ -127,3 +127,31 @@ def test_dynamic_batching_is_transparent(tiny, b200sd):
     for a, b in zip(got, solo):
         d = np.abs(a.astype(np.int32) - b.astype(np.int32))
         assert d.max() <= 2, d.max()  # GroupNorm atomics order only
+
+
+def test_from_pretrained_checkpoint_directory(tiny, b200sd, tmp_path):
+    """`StableDiffusionPipeline.from_pretrained(<diffusers-layout directory>)` - safetensors
+    weights (fp16), config.json files, tokenizer files, PNDM scheduler_config - gives the oracle's image."""
+    import sys
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from ckpt_util import write_diffusers_dir
+    W, T, P = b200sd.weights, b200sd.tokenizer, b200sd.pipeline
+    cfg, oracle, _ = tiny
+    usd = W.random_state_dict(W.unet_schema(cfg["unet"]), 0)
+    vsd = W.random_state_dict(W.vae_decoder_schema(cfg["vae"]), 1)
+    tsd = W.random_state_dict(W.clip_text_schema(cfg["text_encoders"][0]), 2)
+    root = write_diffusers_dir(str(tmp_path / "sd"), cfg, usd, vsd, [tsd], T)
+    pipe = P.StableDiffusionPipeline.from_pretrained(root)
+    assert pipe.scheduler_kind == "pndm"  # the checkpoint's scheduler_config decides (SD1.5 ships PNDM)
+    out = pipe(PROMPTS, num_inference_steps=4, guidance_scale=7.5, width=64, height=64, generator=_gens(),
+               output_type="u8")
+    import copy
+    ocfg = copy.deepcopy(cfg)
+    ocfg["scheduler"]["steps_offset"] = 1  # what the checkpoint's scheduler_config says
+    from oracle.pipeline import OraclePipeline
+    ref = OraclePipeline(ocfg, usd, vsd, tsd, oracle.tokenize, scheduler="pndm")(
+        PROMPTS, num_inference_steps=4, guidance_scale=7.5, width=64, height=64, generator=_gens())
+    psnr = [_psnr(out.images[i], ref["images"][i]) for i in range(len(PROMPTS))]
+    print("checkpoint-dir PNDM PSNR", psnr)
+    assert min(psnr) >= 30.0
