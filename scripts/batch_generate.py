@@ -12,7 +12,9 @@ request there dies with NameError instead of continuing, :30-35); the `--steps` 
 
 Additions (supersets, all optional): `--local` generates in-process on the local B200(s) through
 b200sd.StableDiffusionPipeline instead of HTTP — batched (`--batch-size`), seeded per image (`--seed` + index),
-with `--guidance-scale/--width/--height/--scheduler/--model`, and `--prompts-file` (one prompt per line, cycled).
+with `--guidance-scale/--width/--height/--scheduler/--model`, `--prompts-file` (one prompt per line, cycled) and PNG
+encoding on `--png-threads` threads overlapped with the next batch; `--concurrency N` keeps N HTTP requests in flight
+so that b200sd's batching server can coalesce them (default 1: the reference's sequential loop).
 """
 import argparse
 import os
@@ -29,13 +31,17 @@ def _target(out_dir: Path, prefix: str, idx: int) -> Path:
     return out_dir / f"{prefix}_{idx:02d}.png"
 
 
-def generate(prompt: str, steps: int, url: str, out_dir: Path, prefix: str, count: int, delay: float) -> None:
-    """HTTP mode: `count` sequential POSTs, one PNG per response; failures are reported and the loop goes on."""
+def generate(prompt: str, steps: int, url: str, out_dir: Path, prefix: str, count: int, delay: float,
+             concurrency: int = 1) -> None:
+    """HTTP mode: `count` POSTs, one PNG per response; failures are reported and the loop goes on.  concurrency = 1 is
+    the reference's strictly sequential loop; more keeps that many requests in flight so that a batching server
+    (b200sd's) can coalesce them."""
     import requests
 
     out_dir.mkdir(parents=True, exist_ok=True)
     http = requests.Session()
-    for idx in range(1, count + 1):
+
+    def one(idx: int) -> None:
         target = _target(out_dir, prefix, idx)
         print(f"[*] Generating {target.name} -> {target}")
         try:
@@ -49,13 +55,22 @@ def generate(prompt: str, steps: int, url: str, out_dir: Path, prefix: str, coun
         except Exception as exc:  # noqa: BLE001 — keep going, like the reference intends
             print(f"    ✖ Unexpected error for {target.name}: {exc}")
             traceback.print_exc()
-        if delay > 0 and idx != count:
-            time.sleep(delay)
+
+    if concurrency > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(concurrency) as pool:
+            list(pool.map(one, range(1, count + 1)))
+    else:
+        for idx in range(1, count + 1):
+            one(idx)
+            if delay > 0 and idx != count:
+                time.sleep(delay)
     print("[*] Generation loop finished (with possible errors).")
 
 
 def generate_local(prompts, steps, out_dir: Path, prefix: str, count: int, *, batch_size: int, seed: int,
-                   guidance_scale: float, width: int, height: int, scheduler, model: str, pipe=None) -> None:
+                   guidance_scale: float, width: int, height: int, scheduler, model: str, pipe=None,
+                   png_threads: int = 4) -> None:
     """Local mode: the same files, produced by b200sd on this machine's GPU in batches of `batch_size`."""
     import torch
 
@@ -66,6 +81,15 @@ def generate_local(prompts, steps, out_dir: Path, prefix: str, count: int, *, ba
         import b200sd
         pipe = b200sd.StableDiffusionPipeline.from_pretrained(model, scheduler=scheduler)
     out_dir.mkdir(parents=True, exist_ok=True)
+    # PNG encoding (zlib, releases the GIL) runs on a small thread pool while the GPU works on the next batch
+    from concurrent.futures import ThreadPoolExecutor
+    from PIL import Image
+    pool = ThreadPoolExecutor(max_workers=png_threads)
+    pending = []
+
+    def save(arr, path):
+        Image.fromarray(arr).save(path, format="PNG")
+
     for start in range(1, count + 1, batch_size):
         idxs = list(range(start, min(count, start + batch_size - 1) + 1))
         batch_prompts = [prompts[(i - 1) % len(prompts)] for i in idxs]
@@ -75,15 +99,20 @@ def generate_local(prompts, steps, out_dir: Path, prefix: str, count: int, *, ba
         t0 = time.time()
         try:
             images = pipe(batch_prompts, num_inference_steps=steps, guidance_scale=guidance_scale, width=width,
-                          height=height, generator=gens).images
-            for i, img in zip(idxs, images):
-                img.save(_target(out_dir, prefix, i), format="PNG")
+                          height=height, generator=gens, output_type="u8").images
+            pending += [pool.submit(save, img, _target(out_dir, prefix, i)) for i, img in zip(idxs, images)]
             dt = time.time() - t0
             for _ in idxs:
                 print(f"    ✔ done in {dt / len(idxs):.2f}s")
         except Exception as exc:  # noqa: BLE001
             print(f"    ✖ Unexpected error for {_target(out_dir, prefix, idxs[0]).name}: {exc}")
             traceback.print_exc()
+    for f in pending:
+        try:
+            f.result()
+        except Exception as exc:  # noqa: BLE001
+            print(f"    ✖ Unexpected error while writing a PNG: {exc}")
+    pool.shutdown()
     print("[*] Generation loop finished (with possible errors).")
 
 
@@ -96,6 +125,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--steps", type=int, default=40, help="diffusion steps per image (default: 40)")
     ap.add_argument("--url", default=DEFAULT_URL, help=f"API endpoint (default: {DEFAULT_URL})")
     ap.add_argument("--delay", type=float, default=0, help="seconds to sleep between requests")
+    ap.add_argument("--concurrency", type=int, default=1,
+                    help="requests kept in flight (default 1 = the reference's sequential loop; an addition)")
     loc = ap.add_argument_group("local generation (additions to the reference CLI)")
     loc.add_argument("--local", action="store_true", help="generate in-process on the local GPU instead of HTTP")
     loc.add_argument("--batch-size", type=int, default=8)
@@ -105,6 +136,7 @@ def build_parser() -> argparse.ArgumentParser:
     loc.add_argument("--height", type=int, default=512)
     loc.add_argument("--scheduler", default=None, choices=[None, "ddim", "pndm", "euler"])
     loc.add_argument("--model", default="sd15")
+    loc.add_argument("--png-threads", type=int, default=4, help="PNG encoder threads overlapping the GPU work")
     loc.add_argument("--prompts-file", default=None, help="one prompt per line; overrides PROMPT, cycled over COUNT")
     return ap
 
@@ -118,9 +150,9 @@ def main(argv: list) -> int:
             prompts = [l.strip() for l in Path(args.prompts_file).read_text().splitlines() if l.strip()] or prompts
         generate_local(prompts, args.steps, out_dir, args.prefix, args.count, batch_size=args.batch_size,
                        seed=args.seed, guidance_scale=args.guidance_scale, width=args.width, height=args.height,
-                       scheduler=args.scheduler, model=args.model)
+                       scheduler=args.scheduler, model=args.model, png_threads=args.png_threads)
     else:
-        generate(args.prompt, args.steps, args.url, out_dir, args.prefix, args.count, args.delay)
+        generate(args.prompt, args.steps, args.url, out_dir, args.prefix, args.count, args.delay, args.concurrency)
     print(f"All done. Images saved under {out_dir.resolve()}")
     return 0
 
