@@ -88,6 +88,16 @@ typedef struct {
   int32_t out_dtype; /* b200sd_dtype */
   int32_t bn_hint;   /* 0 = auto; else tile N (multiple of 32, <= 256) */
   float alpha;       /* accumulator scale (1.0 for plain layers) */
+  /* Optional fused GroupNorm statistics of the OUTPUT (the next layer's GroupNorm, torch.nn.GroupNorm inside
+   * ResnetBlock2D / Transformer2DModel): the epilogue adds sum and sum of squares of out[., g * n/gn_groups ...] per
+   * (image, group) to gn_stats [images, gn_groups, 2] with atomics - the caller zeroes it; b200sd_groupnorm_apply then
+   * needs no b200sd_groupnorm_stats pass.  16-bit, non-GEGLU outputs only; n / gn_groups whole and even.  The sums are
+   * taken over the ROUNDED 16-bit outputs (what the apply pass reads).  Every 32-row slab of
+   * a tile must lie in one image: gn_rows_per_img = 0 takes images from the NHWC geometry (needs
+   * pow2ceil(w) * pow2ceil(h) >= 32); for a flattened geometry (nimg = 1, h = 1) pass the rows per image (% 32 == 0). */
+  float* gn_stats;
+  int32_t gn_groups;
+  int32_t gn_rows_per_img;
 } b200sd_gemm_params;
 int b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream stream);
 

@@ -41,6 +41,8 @@ struct alignas(64) GemmDev {
   CUtensorMap tmR;  // residual (16-bit), same box
   const float* bias;
   const float* rowbias;
+  float* gn_stats;  // fused GroupNorm statistics of the output, or nullptr
+  int gn_groups, gn_cpg, gn_rows_per_img;
   int N, BN;
   int nimg, H, W;
   int bw, bh, bn;
@@ -280,6 +282,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       int n0, h0, w0, col0;
       decode_tile(p, tile, rank, n0, h0, w0, col0);
       const int img = min(n0 + in, p.nimg - 1);  // rows beyond the tensor are clipped by the TMA store
+      // fused GroupNorm statistics: image of my warp's row slab, and whether my row exists at all
+      const bool gn_row_ok = (n0 + in < p.nimg) && (h0 + ih < p.H) && (w0 + iw < p.W);
+      const int gn_img = p.gn_rows_per_img > 0 ? (w0 + q * 32) / p.gn_rows_per_img : img;
       mbar_wait((bar0 + 8 * (kBarTFull + (acc))), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
@@ -406,6 +411,49 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
                        "r"(w[4 * k + 1]), "r"(w[4 * k + 2]), "r"(w[4 * k + 3])
                        : "memory");
         fence_proxy_async_smem();
+        if (!kOutF32 && !kGeglu) {
+          if (p.gn_stats != nullptr) {
+            // Fused GroupNorm statistics of this 128 x 64 output group, read back TRANSPOSED from the staging tile:
+            // lane = one column pair, walking the 32 rows my own warp has just written (one image, see b200sd.h) -
+            // conflict-free 4-byte loads, a rolled loop.  Lanes of the same channel group are then combined by a
+            // segmented shuffle reduction and the segment heads issue the two atomics.
+            __syncwarp();
+            const uint32_t rows_ok = __ballot_sync(0xffffffffu, gn_row_ok);
+            const uint32_t wofs = (static_cast<uint32_t>(lane) & 3u) * 4u, chunk = static_cast<uint32_t>(lane) >> 2;
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+            for (int rr = 0; rr < 32; ++rr) {
+              const uint32_t row = static_cast<uint32_t>(q * 32 + rr);
+              uint32_t wv;
+              asm volatile("ld.shared.b32 %0, [%1];" : "=r"(wv) : "r"(stg + row * 128 + ((chunk ^ (row & 7u)) << 4) + wofs));
+              const float2 v = unpack_act2(wv);
+              if ((rows_ok >> rr) & 1u) {
+                s0 += v.x;
+                q0 = fmaf(v.x, v.x, q0);
+                s1 += v.y;
+                q1 = fmaf(v.y, v.y, q1);
+              }
+            }
+            const int col = ocol0 + 2 * lane;
+            const int g = col / p.gn_cpg;  // channels per group are even: both columns of the pair share a group
+            float gs = s0 + s1, gq = q0 + q1;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+              const float so = __shfl_down_sync(0xffffffffu, gs, o), qo = __shfl_down_sync(0xffffffffu, gq, o);
+              const int go = __shfl_down_sync(0xffffffffu, g, o);
+              if (lane + o < 32 && go == g) {
+                gs += so;
+                gq += qo;
+              }
+            }
+            const int gprev = __shfl_up_sync(0xffffffffu, g, 1);
+            if ((lane == 0 || gprev != g) && col < p.N) {
+              float* gst = p.gn_stats + (static_cast<size_t>(gn_img) * p.gn_groups + g) * 2;
+              atomicAdd(gst, gs);
+              atomicAdd(gst + 1, gq);
+            }
+          }
+        }
         named_bar_sync(bar_id, 128);
         if (issuer) {
           tma_store_4d(&p.tmO, stg, ocol0, w0, h0, n0);
@@ -595,6 +643,21 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   B200SD_REQUIRE(d.num_stages >= 2, B200SD_ERR_CUDA, "gemm: not enough shared memory (%d B opt-in)", di.max_smem_optin);
   d.bias = h.bias;
   d.rowbias = h.rowbias;
+  d.gn_stats = h.gn_stats;
+  if (h.gn_stats != nullptr) {
+    B200SD_REQUIRE(!geglu && !f32, B200SD_ERR_BAD_ARGUMENT, "gemm: fused GroupNorm statistics need a 16-bit, non-GEGLU output");
+    B200SD_REQUIRE(h.gn_groups > 0 && (h.n % h.gn_groups) == 0 && ((h.n / h.gn_groups) % 2) == 0, B200SD_ERR_BAD_SHAPE,
+                   "gemm: %d output channels / %d groups must be a whole, even number of channels", h.n, h.gn_groups);
+    if (h.gn_rows_per_img > 0)
+      B200SD_REQUIRE(h.nimg == 1 && h.h == 1 && (h.gn_rows_per_img % 32) == 0, B200SD_ERR_BAD_SHAPE,
+                     "gemm: gn_rows_per_img needs the flattened geometry and a multiple of 32 rows per image");
+    else
+      B200SD_REQUIRE(d.bw * d.bh >= 32, B200SD_ERR_BAD_SHAPE,
+                     "gemm: fused GroupNorm statistics need at least 32 pixels of an image per tile (%d x %d)", d.bw, d.bh);
+    d.gn_groups = h.gn_groups;
+    d.gn_cpg = h.n / h.gn_groups;
+    d.gn_rows_per_img = h.gn_rows_per_img;
+  }
   d.ld_rowbias = h.ld_rowbias;
   d.act = h.act;
   d.alpha = h.alpha;

@@ -14,11 +14,12 @@ from . import ops
 
 
 class Act:
-    """NHWC bf16 activation: tensor [nimg, h, w, c] (contiguous)."""
-    __slots__ = ("t", "nimg", "h", "w", "c")
+    """NHWC 16-bit activation: tensor [nimg, h, w, c] (contiguous).  `stats` = (f32 [nimg, groups, 2], groups) when
+    the kernel that produced it also accumulated its GroupNorm statistics (fused into the GEMM epilogue)."""
+    __slots__ = ("t", "nimg", "h", "w", "c", "stats")
 
-    def __init__(self, t, nimg, h, w, c):
-        self.t, self.nimg, self.h, self.w, self.c = t, nimg, h, w, c
+    def __init__(self, t, nimg, h, w, c, stats=None):
+        self.t, self.nimg, self.h, self.w, self.c, self.stats = t, nimg, h, w, c, stats
 
     @property
     def hw(self):
@@ -164,6 +165,17 @@ class Builder:
     def add(self, call):
         self.plan.calls.append(call)
 
+    def stats_slice(self, nimg, groups):
+        nst = nimg * groups * 2
+        assert self.stats_off + nst <= self.stats.numel(), "GroupNorm statistics scratch exhausted"
+        st = self.stats[self.stats_off:self.stats_off + nst]
+        self.stats_off += nst
+        return st
+
+    @staticmethod
+    def _pow2_ceil(v):
+        return 1 << max(0, (v - 1).bit_length())
+
     def finish(self) -> Plan:
         if self.stats_off:
             self.plan.calls.insert(0, ops.memset_zero(self.stats, self.stats_off * 4))
@@ -171,10 +183,17 @@ class Builder:
 
     # ------------------------------------------------------------------ layers
     def conv(self, W: DeviceWeights, name, x, cout, ksize, *, bias=True, rowbias=None, ld_rowbias=0, residual=None,
-             act=L.ACT_NONE, out_dtype=None, out=None, ldc=None, wsplit=None):
-        """x: Act or (Act, Act) virtual concat.  Returns Act [nimg, h, w, cout]."""
+             act=L.ACT_NONE, out_dtype=None, out=None, ldc=None, wsplit=None, gn_groups=None):
+        """x: Act or (Act, Act) virtual concat.  Returns Act [nimg, h, w, cout].  gn_groups: also accumulate the
+        GroupNorm statistics of the output in the epilogue (long reductions only - a 3x3 conv hides it completely;
+        tiles must hold >= 32 pixels of an image, see b200sd.h)."""
         xs = x if isinstance(x, tuple) else (x,)
         a0 = xs[0]
+        st = None
+        if (gn_groups and ksize == 3 and out is None and ldc is None and out_dtype in (None, ops.act_dtype())
+                and cout % (2 * gn_groups) == 0 and 9 * sum(a.c for a in xs) >= 24 * 64  # long reductions only
+                and min(128, self._pow2_ceil(a0.w)) * self._pow2_ceil(a0.h) >= 32):
+            st = self.stats_slice(a0.nimg, gn_groups)
         split = wsplit or tuple(a.c for a in xs)  # wsplit: real weight channels when the activation is zero padded
         w = W.conv(name, split)
         b = W.vec(name + ".bias") if bias else None
@@ -184,8 +203,10 @@ class Builder:
         self.add(ops.gemm(a0.t, w, out, nimg=a0.nimg, h=a0.h, w_=a0.w, c0=a0.c, n=cout, ksize=ksize,
                           a1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c, bias=b, rowbias=rowbias,
                           ld_rowbias=ld_rowbias, residual=None if residual is None else residual.t,
-                          ldr=0 if residual is None else residual.c, ldc=ldc, act=act))
-        return Act(out, a0.nimg, a0.h, a0.w, cout if ldc is None else ldc)
+                          ldr=0 if residual is None else residual.c, ldc=ldc, act=act, gn_stats=st,
+                          gn_groups=gn_groups if st is not None else 0))
+        return Act(out, a0.nimg, a0.h, a0.w, cout if ldc is None else ldc,
+                   stats=None if st is None else (st, gn_groups))
 
     def linear_w(self, x: Act, w, b, n, *, residual=None, act=L.ACT_NONE, out_dtype=None, rowbias=None,
                  ld_rowbias=0, per_image_rows=False):
@@ -210,14 +231,13 @@ class Builder:
         a1 = xs[1] if len(xs) > 1 else None
         C = sum(a.c for a in xs)
         out = self.alloc((a0.nimg, a0.h, a0.w, C))
-        nst = a0.nimg * groups * 2
-        assert self.stats_off + nst <= self.stats.numel(), "GroupNorm statistics scratch exhausted"
-        st = self.stats[self.stats_off:self.stats_off + nst]
-        self.stats_off += nst
+        fused = a1 is None and a0.stats is not None and a0.stats[1] == groups
+        st = a0.stats[0] if fused else self.stats_slice(a0.nimg, groups)
         s_call, a_call = ops.groupnorm(a0.t, out, st, W.vec(name + ".weight"), W.vec(name + ".bias"), nimg=a0.nimg,
                                        hw=a0.hw, c0=a0.c, groups=groups, eps=eps, silu=silu,
                                        x1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c)
-        self.add(s_call)
+        if not fused:  # otherwise the producing GEMM's epilogue has already accumulated the statistics
+            self.add(s_call)
         self.add(a_call)
         return Act(out, a0.nimg, a0.h, a0.w, C)
 
@@ -238,25 +258,30 @@ class Builder:
         self.add(ops.upsample2x(x.t, out, nimg=x.nimg, h=x.h, w_=x.w, c=x.c))
         return Act(out, x.nimg, 2 * x.h, 2 * x.w, x.c)
 
-    def conv_s2(self, W: DeviceWeights, name, x: Act, cout):
+    def conv_s2(self, W: DeviceWeights, name, x: Act, cout, gn_groups=None):
         """3x3 stride-2 pad-1 conv = patch gather into scratch + linear GEMM."""
         cp = ops.ceil_to(x.c, 64)
         ho, wo = x.h // 2, x.w // 2
         col = self.alloc((x.nimg, ho, wo, 9 * cp))
         self.add(ops.im2col_s2(x.t, col, nimg=x.nimg, h=x.h, w_=x.w, c=x.c))
         out = self.alloc((x.nimg, ho, wo, cout))
+        st = None
+        if gn_groups and cout % (2 * gn_groups) == 0 and (ho * wo) % 32 == 0 and 9 * cp >= 24 * 64:
+            st = self.stats_slice(x.nimg, gn_groups)
         self.add(ops.gemm(col, W.conv(name), out, nimg=1, h=1, w_=x.nimg * ho * wo, c0=9 * cp, n=cout, ksize=1,
-                          bias=W.vec(name + ".bias")))
+                          bias=W.vec(name + ".bias"), gn_stats=st, gn_groups=gn_groups if st is not None else 0,
+                          gn_rows_per_img=ho * wo if st is not None else 0))
         self.free(col)
-        return Act(out, x.nimg, ho, wo, cout)
+        return Act(out, x.nimg, ho, wo, cout, stats=None if st is None else (st, gn_groups))
 
     # ------------------------------------------------------------------ composite blocks (UNet + VAE)
     def resnet(self, W, p, x, cout, groups, eps, temb=None, ld_temb=0):
-        """ResnetBlock2D: x Act or (Act, Act).  temb: fp32 tensor view [nimg, cout] (row stride ld_temb) or None."""
+        """ResnetBlock2D: x Act or (Act, Act).  temb: fp32 tensor view [nimg, cout] (row stride ld_temb) or None.
+        Both 3x3 convs also accumulate the GroupNorm statistics of their output (norm2 / the next block's norm)."""
         xs = x if isinstance(x, tuple) else (x,)
         cin = sum(a.c for a in xs)
         h = self.groupnorm(W, p + ".norm1", x, groups, eps, silu=True)
-        h1 = self.conv(W, p + ".conv1", h, cout, 3, rowbias=temb, ld_rowbias=ld_temb)
+        h1 = self.conv(W, p + ".conv1", h, cout, 3, rowbias=temb, ld_rowbias=ld_temb, gn_groups=groups)
         self.free(h)
         h2 = self.groupnorm(W, p + ".norm2", h1, groups, eps, silu=True)
         self.free(h1)
@@ -265,7 +290,7 @@ class Builder:
         else:
             assert len(xs) == 1
             sc = xs[0]
-        out = self.conv(W, p + ".conv2", h2, cout, 3, residual=sc)
+        out = self.conv(W, p + ".conv2", h2, cout, 3, residual=sc, gn_groups=groups)
         self.free(h2)
         if cin != cout:
             self.free(sc)

@@ -25,7 +25,8 @@ class GemmParams(C.Structure):
     _fields_ = [("a0", vp), ("a1", vp), ("w", vp), ("out", vp), ("bias", vp), ("rowbias", vp), ("residual", vp),
                 ("nimg", i32), ("h", i32), ("w_", i32), ("c0", i32), ("c1", i32), ("ld0", i32), ("ld1", i32),
                 ("n", i32), ("ksize", i32), ("ldc", i32), ("ldr", i32), ("ld_rowbias", i32), ("act", i32),
-                ("out_dtype", i32), ("bn_hint", i32), ("alpha", f32)]
+                ("out_dtype", i32), ("bn_hint", i32), ("alpha", f32), ("gn_stats", vp), ("gn_groups", i32),
+                ("gn_rows_per_img", i32)]
 
 
 class AttnParams(C.Structure):

@@ -61,7 +61,8 @@ def geglu_perm(n2: int) -> torch.Tensor:
 
 # ------------------------------------------------------------------------------------------------ call builders
 def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld1=None, bias=None, rowbias=None,
-         ld_rowbias=0, residual=None, ldr=0, ldc=None, act=L.ACT_NONE, out_dtype=None, alpha=1.0, bn_hint=0):
+         ld_rowbias=0, residual=None, ldr=0, ldc=None, act=L.ACT_NONE, out_dtype=None, alpha=1.0, bn_hint=0,
+         gn_stats=None, gn_groups=0, gn_rows_per_img=0):
     p = L.GemmParams()
     p.a0, p.a1, p.w, p.out = _ptr(a0), _ptr(a1), _ptr(w), _ptr(out)
     p.bias, p.rowbias, p.residual = _ptr(bias), _ptr(rowbias), _ptr(residual)
@@ -79,7 +80,8 @@ def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld
     p.out_dtype = out_dtype
     p.bn_hint = bn_hint
     p.alpha = alpha
-    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual))
+    p.gn_stats, p.gn_groups, p.gn_rows_per_img = _ptr(gn_stats), gn_groups, gn_rows_per_img
+    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual, gn_stats))
 
 
 def attention(q, k, v, out, *, batch, heads, nq, nk, d, ldq, ldk, ldv, ldo, scale, causal=False):

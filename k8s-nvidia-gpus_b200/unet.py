@@ -181,7 +181,7 @@ class UNetEngine:
             return out
 
         # --- down path
-        x = bld.conv(W, "conv_in", Act(xin, n, h, w, 8), ch[0], 3, wsplit=(cfg["in_channels"],))
+        x = bld.conv(W, "conv_in", Act(xin, n, h, w, 8), ch[0], 3, wsplit=(cfg["in_channels"],), gn_groups=g)
         skips = [x]
         for i, btype in enumerate(cfg["down_block_types"]):
             for j in range(layers):
@@ -193,7 +193,7 @@ class UNetEngine:
                 x = y
                 skips.append(x)
             if i < len(ch) - 1:
-                x = bld.conv_s2(W, f"down_blocks.{i}.downsamplers.0.conv", x, ch[i])
+                x = bld.conv_s2(W, f"down_blocks.{i}.downsamplers.0.conv", x, ch[i], gn_groups=g)
                 skips.append(x)
         # --- mid
         y = resnet("mid_block.resnets.0", x, ch[-1])

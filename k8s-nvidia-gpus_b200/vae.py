@@ -69,7 +69,7 @@ class VAEDecoderEngine:
         # post_quant_conv 1x1 (4 -> 4) written into a zero-padded 8-channel buffer (TMA wants 16-byte pixels)
         z2 = bld.persistent((batch, h, w, 8))
         bld.conv(W, "post_quant_conv", Act(z, batch, h, w, 8), lc, 1, out=z2, ldc=8, wsplit=(lc,))
-        x = bld.conv(W, "decoder.conv_in", Act(z2, batch, h, w, 8), ch[-1], 3, wsplit=(lc,))
+        x = bld.conv(W, "decoder.conv_in", Act(z2, batch, h, w, 8), ch[-1], 3, wsplit=(lc,), gn_groups=g)
         y = bld.resnet(W, "decoder.mid_block.resnets.0", x, ch[-1], g, 1e-6)
         bld.free(x)
         y2 = self._mid_attention(bld, "decoder.mid_block.attentions.0", y, g)
@@ -85,7 +85,7 @@ class VAEDecoderEngine:
             if i < len(ch) - 1:
                 up = bld.upsample2x(x)
                 bld.free(x)
-                x = bld.conv(W, f"decoder.up_blocks.{i}.upsamplers.0.conv", up, rch[i], 3)
+                x = bld.conv(W, f"decoder.up_blocks.{i}.upsamplers.0.conv", up, rch[i], 3, gn_groups=g)
                 bld.free(up)
         gn = bld.groupnorm(W, "decoder.conv_norm_out", x, g, 1e-6, silu=True)
         bld.free(x)

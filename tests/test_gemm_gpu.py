@@ -163,6 +163,44 @@ def test_conv3x3_concat_temb_residual(cuda_lib, b200sd):
     _report("conv3x3 concat+temb+residual", out, ref, 1e-2)
 
 
+@pytest.mark.parametrize("nimg,H,W,cin,cout,groups,flat", [
+    (2, 16, 16, 64, 128, 32, False), (3, 8, 8, 128, 320, 32, False), (1, 24, 20, 32, 96, 8, False),
+    (4, 64, 64, 64, 320, 32, False), (5, 8, 8, 64, 640, 32, True), (2, 32, 32, 64, 64, 8, True)])
+def test_fused_groupnorm_statistics(cuda_lib, b200sd, nimg, H, W, cin, cout, groups, flat):
+    """The epilogue's (image, group) sums and sums of squares of the conv output (bias + time-embedding row bias +
+    residual included) against torch on the fp32 result; `flat` = the im2col / linear geometry with rows per image."""
+    torch.manual_seed(6)
+    ops = b200sd.ops
+    ks = 1 if flat else 3
+    x = _rand(nimg, H, W, cin)
+    w = _rand(cout, cin, ks, ks, scale=(ks * ks * cin) ** -0.5)
+    bias = torch.randn(cout, device="cuda")
+    res = _rand(nimg, H, W, cout)
+    temb = torch.randn(nimg, cout, device="cuda")
+    out = torch.empty(nimg, H, W, cout, device="cuda", dtype=ACT())
+    stats = torch.zeros(nimg, groups, 2, device="cuda")
+    wp = ops.pack_conv_weight(w.float().cpu()).cuda()
+    if flat:
+        geo = dict(nimg=1, h=1, w_=nimg * H * W, gn_rows_per_img=H * W)
+        kw = {}
+    else:
+        geo = dict(nimg=nimg, h=H, w_=W)
+        kw = dict(rowbias=temb, ld_rowbias=cout)
+    ops.gemm(x, wp, out, c0=cin, n=cout, ksize=ks, bias=bias, residual=res, gn_stats=stats, gn_groups=groups,
+             **geo, **kw)(ops.current_stream())
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=ks // 2).permute(0, 2, 3, 1) + res.float()
+    if not flat:
+        ref = ref + temb[:, None, None, :]
+    _report("conv with fused stats", out, ref, 1e-2)
+    g = ref.reshape(nimg, H * W, groups, cout // groups)
+    want = torch.stack([g.sum(dim=(1, 3)), (g * g).sum(dim=(1, 3))], dim=-1)
+    err = (stats - want).abs().max().item()
+    scale = want.abs().max().item()
+    print("fused GN stats max err", err, "scale", scale)
+    assert err <= 2e-4 * scale + 1e-2
+
+
 def test_gemm_rejects_bad_arguments(cuda_lib, b200sd):
     ops = b200sd.ops
     x = _rand(64, 60)
