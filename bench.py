@@ -160,7 +160,7 @@ def run_reference(args):
         "e2e": {"value": r["ips"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "detail": {k: round(v, 4) for k, v in r.items()},
     }
-    print(json.dumps(line))
+    emit(json.dumps(line))
     return 0
 
 
@@ -392,13 +392,36 @@ def run_cuda(args):
         "breakdown_note": f"CUDA-event intervals of an eager pass minus the empty-interval gap ({event_gap_ms * 1e3:.1f} us)",
         "device": {"sm_count": info["sm_count"], "cc": list(info["cc"])},
     }
-    print(json.dumps(line))
+    emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: keep a private duplicate of fd 1 for it and point fd 1 at stderr, so that
+    nothing printed by libraries underneath (NCCL's version banner, C-level printf, warnings) can land there."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(text: str):
+    data = (text + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(text + "\n")
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main(argv=None):
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
