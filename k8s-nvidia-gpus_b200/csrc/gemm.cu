@@ -524,7 +524,6 @@ static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_k
   return best;
 }
 
-static bool g_gemm_attr_set = false;
 
 template <bool F, bool G, bool R, bool P>
 static int launch_one(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
