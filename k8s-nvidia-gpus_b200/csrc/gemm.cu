@@ -692,7 +692,6 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   const int smem_bytes = d.num_stages * stage_bytes + d.res_bufs * kEpiStageBytes + 1024;
   const int num_tiles = (d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m) * d.tiles_ncol;
   const int grid = d.pair ? 2 * min(num_tiles, di.sm_count / 2) : min(num_tiles, di.sm_count);
-  (void)g_gemm_attr_set;
   if (geglu) return launch_variant<false, true, false>(d, grid, smem_bytes, di.max_smem_optin, stream);
   if (f32) return launch_variant<true, false, false>(d, grid, smem_bytes, di.max_smem_optin, stream);
   if (res) return launch_variant<false, false, true>(d, grid, smem_bytes, di.max_smem_optin, stream);
