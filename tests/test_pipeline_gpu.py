@@ -155,3 +155,32 @@ def test_from_pretrained_checkpoint_directory(tiny, b200sd, tmp_path):
     psnr = [_psnr(out.images[i], ref["images"][i]) for i in range(len(PROMPTS))]
     print("checkpoint-dir PNDM PSNR", psnr)
     assert min(psnr) >= 30.0
+
+
+def test_call_variants_match_oracle(tiny):
+    """The remaining `pipe(...)` argument forms of the upstream signature, each against the oracle: non-square size,
+    per-prompt negative prompts, one shared generator for the whole batch, caller-supplied latents, an empty prompt
+    and a prompt longer than 77 tokens (truncated)."""
+    cfg, oracle, pipe = tiny
+    long_prompt = "a very long prompt about pandas and motorbikes " * 20
+    prompts = ["a green motorbike", "", long_prompt]
+    neg = ["blurry", "", "low quality, jpeg artifacts"]
+    kw = dict(num_inference_steps=3, guidance_scale=6.0, width=96, height=64, negative_prompt=neg, scheduler="euler")
+    ref = oracle(prompts, generator=torch.Generator().manual_seed(11), **kw)
+    out = pipe(prompts, generator=torch.Generator().manual_seed(11), output_type="u8", **kw)
+    assert out.images.shape == (3, 64, 96, 3)
+    psnr = [_psnr(out.images[i], ref["images"][i]) for i in range(3)]
+    print("variants PSNR", psnr)
+    assert min(psnr) >= 30.0
+    # caller-supplied latents (scaled by init_noise_sigma inside, like upstream prepare_latents)
+    lat0 = torch.randn(2, 4, 32, 32, generator=torch.Generator().manual_seed(5))
+    kw2 = dict(num_inference_steps=2, guidance_scale=7.5, width=64, height=64, scheduler="pndm")
+    ref2 = oracle(PROMPTS, latents=lat0.clone(), **kw2)
+    got2 = pipe(PROMPTS, latents=lat0.clone(), output_type="latent", **kw2).images
+    r = _rel(got2, ref2["latents"])
+    print("explicit latents rel err", r)
+    assert r <= 1e-2
+    with pytest.raises(ValueError, match="generators"):
+        pipe(PROMPTS, num_inference_steps=1, width=64, height=64, generator=[torch.Generator().manual_seed(0)])
+    with pytest.raises(ValueError, match="negative_prompt"):
+        pipe(PROMPTS, num_inference_steps=1, width=64, height=64, negative_prompt=["a", "b", "c"])
