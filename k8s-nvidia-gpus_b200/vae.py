@@ -63,7 +63,7 @@ class VAEDecoderEngine:
         layers = cfg["layers_per_block"] + 1
         lc = cfg["latent_channels"]
         assert lc == 4
-        bld = Builder(self.device)
+        bld = Builder(self.device, fuse_gn_stats=True)
         z = bld.persistent((batch, h, w, 8))
         bld.add(ops.latent_to_act(latents, z, b=batch, hw=h * w, scale=1.0 / cfg["scaling_factor"]))
         # post_quant_conv 1x1 (4 -> 4) written into a zero-padded 8-channel buffer (TMA wants 16-byte pixels)
