@@ -33,6 +33,32 @@ static constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
 static constexpr uint32_t kEpiTileBytes = 128 * 128;        // 128 rows x 128 B
 static constexpr int kEpiStageBytes = 2 * kEpiTileBytes;    // one staging tile per epilogue warpgroup
 
+// Division by a launch-time constant as multiply-high + shift (exact for dividends < 2^31): the tile decode runs once
+// per tile in the epilogue's critical path, where four or five 32-bit integer divisions cost several hundred cycles.
+// mul = ceil(2^(31 + s) / d), s = ceil(log2 d); d == 1 is flagged by shift < 0.
+struct FastDiv {
+  uint32_t mul;
+  int32_t shift;
+  uint32_t d;
+};
+static inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f;
+  f.d = d;
+  if (d <= 1) {
+    f.mul = 0;
+    f.shift = -1;
+    return f;
+  }
+  int s = 0;
+  while ((1u << s) < d) ++s;
+  f.mul = static_cast<uint32_t>(((1ull << (31 + s)) + d - 1) / d);
+  f.shift = s - 1;
+  return f;
+}
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv& f) {
+  return f.shift < 0 ? n : (__umulhi(n, f.mul) >> f.shift);
+}
+
 struct alignas(64) GemmDev {
   CUtensorMap tmA0;
   CUtensorMap tmA1;
@@ -47,6 +73,7 @@ struct alignas(64) GemmDev {
   int nimg, H, W;
   int bw, bh, bn;
   int tiles_w, tiles_h, tiles_n, tiles_m, tiles_ncol;
+  FastDiv div_munits, div_tw, div_twth;  // tile -> column tile; M tile -> (tw, th, tn)
   int ksize, pad, taps;
   int cblk0, cblk1;
   int num_stages;
@@ -61,13 +88,14 @@ struct alignas(64) GemmDev {
 // full-width and (narrower) last-column tiles instead of always the same column.  In pair mode `tile` counts PAIR
 // tiles (two consecutive M tiles, one per CTA).
 __device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int rank, int& n0, int& h0, int& w0, int& col0) {
-  const int m_units = p.pair ? (p.tiles_m + 1) / 2 : p.tiles_m;
-  const int nt = tile / m_units;
+  const int m_units = static_cast<int>(p.div_munits.d);
+  const int nt = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits));
   int mt = tile - nt * m_units;
   if (p.pair) mt = 2 * mt + rank;  // an M tile past the end is all out of bounds: TMA zero-fills / clips it
-  const int tw = mt % p.tiles_w;
-  const int th = (mt / p.tiles_w) % p.tiles_h;
-  const int tn = mt / (p.tiles_w * p.tiles_h);
+  const int tn = static_cast<int>(fdiv(static_cast<uint32_t>(mt), p.div_twth));
+  const int rem = mt - tn * static_cast<int>(p.div_twth.d);
+  const int th = static_cast<int>(fdiv(static_cast<uint32_t>(rem), p.div_tw));
+  const int tw = rem - th * p.tiles_w;
   n0 = tn * p.bn;
   h0 = th * p.bh;
   w0 = tw * p.bw;
@@ -192,9 +220,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const int m_units = kPair ? (p.tiles_m + 1) / 2 : p.tiles_m;
       for (int tile = tile0; tile < num_tiles; tile += tile_step) {
-        const int col0 = (tile / m_units) * p.BN;
+        const int col0 = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits)) * p.BN;
         const int ncols = min(p.BN, p.N - col0);
         // no MMA work on padding columns; pair mode: one M = 256 instruction spans both CTAs
         const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBlockM : kBlockM, (ncols + 15) & ~15, 0, 0);
@@ -257,7 +284,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       g += 2;
       for (;;) {
         if (tile >= num_tiles) return;
-        const int c0 = (tile / (kPair ? (p.tiles_m + 1) / 2 : p.tiles_m)) * p.BN;
+        const int c0 = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits)) * p.BN;
         const int ng = (min(p.BN, p.N - c0) + acols - 1) / acols;
         if (g < ng) return;
         tile += tile_step;
@@ -618,6 +645,9 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
                  B200SD_ERR_BAD_ARGUMENT, "gemm: bad bn_hint %d (must be a multiple of %d, <= 256)", bn_tile, gran);
   d.BN = bn_tile;
   d.tiles_ncol = ceil_div(h.n, d.BN);
+  d.div_munits = make_fastdiv(static_cast<uint32_t>(d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m));
+  d.div_tw = make_fastdiv(static_cast<uint32_t>(d.tiles_w));
+  d.div_twth = make_fastdiv(static_cast<uint32_t>(d.tiles_w * d.tiles_h));
   d.N = h.n;
   d.nimg = h.nimg;
   d.H = h.h;

@@ -86,6 +86,33 @@ def test_bn_independent_flop_model(b200sd):
     assert kind == "gemm" and fl == 2.0 * 16 * 4096 * 320 * 9 * 320
 
 
+def test_fastdiv_constants_are_exact():
+    """The multiply-high + shift division the GEMM's tile decode uses (csrc/gemm.cu make_fastdiv / fdiv), replayed in
+    Python: exact for every dividend < 2^31 - checked on edge dividends for a spread of divisors."""
+    def make(d):
+        if d <= 1:
+            return 0, -1
+        s = 0
+        while (1 << s) < d:
+            s += 1
+        return ((1 << (31 + s)) + d - 1) // d, s - 1
+
+    def fdiv(n, mul, shift):
+        return n if shift < 0 else ((n * mul) >> 32) >> shift
+
+    rng = np.random.default_rng(0)
+    divisors = list(range(1, 70)) + [100, 127, 128, 129, 148, 255, 256, 257, 511, 512, 1000, 4096, 65535, 65536, 99991,
+                                     2 ** 20 + 7, 2 ** 30 - 1, 2 ** 30, 2 ** 31 - 1]
+    for d in divisors:
+        mul, shift = make(d)
+        assert mul < 2 ** 32
+        ns = [0, 1, d - 1, d, d + 1, 2 * d - 1, 2 * d, 2 ** 31 - 1, 2 ** 31 - 2, (2 ** 31 - 1) // d * d,
+              max(0, (2 ** 31 - 1) // d * d - 1)] + [int(x) for x in rng.integers(0, 2 ** 31, size=200)]
+        for n in ns:
+            if 0 <= n < 2 ** 31:
+                assert fdiv(n, mul, shift) == n // d, (n, d)
+
+
 # ------------------------------------------------------------------------------------------------ fake pipeline
 class FakePipe:
     """Stands in for the GPU pipeline in boundary tests: deterministic image from (prompt, seed)."""
