@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
 // several rows' loads are in flight per warp and the two reductions take log2(kLPR) shuffles.  Two-pass mean /
 // variance like the fp32 reference.
 template <int kLPR, int kVecs>
-__global__ void __launch_bounds__(kNormThreads) layernorm_kernel(const act_t* __restrict__ x,
+__global__ void __launch_bounds__(kNormThreads, (kVecs <= 5 ? 4 : 1)) layernorm_kernel(const act_t* __restrict__ x,
                                                                  const float* __restrict__ gamma,
                                                                  const float* __restrict__ beta, act_t* __restrict__ out,
                                                                  int rows, int c, float eps) {

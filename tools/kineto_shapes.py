@@ -11,8 +11,12 @@ from torch.profiler import ProfilerActivity, profile  # noqa: E402
 
 import b200sd  # noqa: E402
 
-pipe = b200sd.StableDiffusionPipeline.from_pretrained("sd15", scheduler="ddim")
-job = pipe.job(8, 64, 64, 7.5, True)
+# usage: kineto_shapes.py [model=sd15] [batch=8] [latent_side=64]   (e.g. sdxl 2 128)
+model = sys.argv[1] if len(sys.argv) > 1 else "sd15"
+batch = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+side = int(sys.argv[3]) if len(sys.argv) > 3 else 64
+pipe = b200sd.StableDiffusionPipeline.from_pretrained(model, scheduler="euler" if "xl" in model else "ddim")
+job = pipe.job(batch, side, side, 7.5, True, zero_negative=pipe.is_xl)
 sched = pipe.make_schedule(25)
 job.step_table[: sched.num_evals].copy_(sched.table)
 job.init_latents.normal_()
@@ -44,5 +48,5 @@ for e, c in zip(evs, calls):
     a[2] += fl
 tot = sum(a[1] for a in agg.values())
 print(f"one denoise step: {tot / 1e3:.3f} ms kernel time")
-for k, (n, t, fl) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:int(sys.argv[1]) if len(sys.argv) > 1 else 40]:
+for k, (n, t, fl) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:int(sys.argv[4]) if len(sys.argv) > 4 else 40]:
     print(f"{k:52s} x{n:3d} {t / 1e3:7.3f} ms {100 * t / tot:5.1f}%  {fl / t / 1e6 if fl else 0:7.0f} TF/s")
