@@ -86,7 +86,9 @@ typedef struct {
   int32_t ldc, ldr, ld_rowbias;
   int32_t act;       /* b200sd_act */
   int32_t out_dtype; /* b200sd_dtype */
-  int32_t bn_hint;   /* 0 = auto; else tile N (multiple of 32, <= 256) */
+  int32_t bn_hint;   /* 0 = auto.  Else the tile width in columns: a multiple of 64 (32 for f32 out, 128 for GEGLU), <= 256,
+                        or <= 512 in multiples of 64 (wide single-accumulator tiles); + 1000 forces single-CTA tiles,
+                        + 2000 forces CTA pairs.  For tests and tuning sweeps. */
   float alpha;       /* accumulator scale (1.0 for plain layers) */
   /* Optional fused GroupNorm statistics of the OUTPUT (the next layer's GroupNorm, torch.nn.GroupNorm inside
    * ResnetBlock2D / Transformer2DModel): the epilogue adds sum and sum of squares of out[., g * n/gn_groups ...] per

@@ -78,6 +78,11 @@ struct alignas(64) GemmDev {
   int cblk0, cblk1;
   int num_stages;
   int res_bufs;  // staging tiles per epilogue warpgroup: 2 = the residual of the NEXT group is prefetched
+  // wide tiles (256 < BN <= 512, single-CTA only): ONE accumulator of BN TMEM columns instead of two of 256, two MMAs
+  // and two B loads per step.  For problems of about one wave (M = 4096 x N = 1280 makes 160 tiles of 128 x 256 for
+  // 148 SMs: two rounds) a 128 x 320 tile brings the count under the SM count; nothing is lost by not double-buffering
+  // an accumulator that is used once.
+  int wide;
   int pair;  // 1: CTA pairs (cta_group::2): M tile 256 across two CTAs, each CTA loads half of B
   int ld_rowbias;
   int act;
@@ -126,6 +131,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   const uint32_t rank = kPair ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs, owns the full barriers)
   const uint32_t b_bytes = static_cast<uint32_t>(kPair ? p.BN / 2 : p.BN) * kBlockK * 2;  // this CTA's share of B
   const uint32_t stage_bytes = kABytes + b_bytes;
+  const int nacc = (!kPair && p.wide) ? 1 : 2;  // TMEM accumulators in rotation
   const int num_tiles = (kPair ? (p.tiles_m + 1) / 2 : p.tiles_m) * p.tiles_ncol;
   const int tile0 = kPair ? blockIdx.x / 2 : blockIdx.x;
   const int tile_step = kPair ? gridDim.x / 2 : gridDim.x;
@@ -193,7 +199,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         } else {
           mbar_arrive_expect_tx_w(leader, bar, stage_bytes);
           tma_load_4d_w(leader, sa, tmA, bar, ch, w0 + kw - p.pad, h0 + kh - p.pad, n0);
-          tma_load_2d_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+          if (p.wide) {  // box = BN / 2 rows
+            tma_load_2d_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+            tma_load_2d_w(leader, sa + kABytes + b_bytes / 2, &p.tmB, bar, kb * kBlockK, bcol + p.BN / 2);
+          } else {
+            tma_load_2d_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+          }
         }
         if (++cb == cblk) {
           cb = 0;
@@ -224,7 +235,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         const int col0 = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits)) * p.BN;
         const int ncols = min(p.BN, p.N - col0);
         // no MMA work on padding columns; pair mode: one M = 256 instruction spans both CTAs
-        const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBlockM : kBlockM, (ncols + 15) & ~15, 0, 0);
+        const int ncols16 = (ncols + 15) & ~15;
+        const uint32_t idesc = make_idesc_f16(kPair ? 2 * kBlockM : kBlockM, min(ncols16, 256), 0, 0);
+        // wide tiles: columns 256.. take a second MMA per step (B rows 256.. sit 32 KB further in the stage)
+        const int ncols_hi = ncols16 - 256;
+        const uint32_t idesc_hi = make_idesc_f16(kBlockM, max(ncols_hi, 16), 0, 0);
         mbar_wait(bar0 + 8 * (kBarTEmpty + acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -239,6 +254,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
               umma_f16_ss_pair_w(leader, d_tmem, a_lo + 2 * k, d_hi, a_lo + b_off + 2 * k, d_hi, idesc, (kb | k) != 0);
             else
               umma_f16_ss_w(leader, d_tmem, a_lo + 2 * k, d_hi, a_lo + b_off + 2 * k, d_hi, idesc, (kb | k) != 0);
+            if (!kPair && ncols_hi > 0)
+              umma_f16_ss_w(leader, d_tmem + 256, a_lo + 2 * k, d_hi, a_lo + b_off + (256 * 128 >> 4) + 2 * k, d_hi,
+                            idesc_hi, (kb | k) != 0);
           }
           if (kPair)
             umma_commit_pair_w(leader, bar0 + 8 * (kBarEmpty + stage));  // frees the stage in both CTAs
@@ -253,7 +271,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           umma_commit_pair_w(leader, bar0 + 8 * (kBarTFull + acc));
         else
           umma_commit_w(leader, bar0 + 8 * (kBarTFull + acc));
-        if (++acc == 2) {
+        if (++acc == nacc) {
           acc = 0;
           acc_phase ^= 1u;
         }
@@ -496,7 +514,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         else
           mbar_arrive((bar0 + 8 * (kBarTEmpty + (acc))));
       }
-      if (++acc == 2) {
+      if (++acc == nacc) {
         acc = 0;
         acc_phase ^= 1u;
       }
@@ -534,9 +552,11 @@ static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_k
   TilePlan best{gran, 0, 1e30};
   for (int pair = 0; pair < 2; ++pair) {
     if (pair && M_tiles < 2) continue;
-    for (int bn = 256; bn >= gran; bn -= gran) {
+    // single-CTA tiles may be wide (up to 512 columns, one TMEM accumulator): worth it when it saves a whole round
+    for (int bn = pair ? 256 : 512; bn >= gran; bn -= gran) {
       if (bn - gran >= N && bn > gran) continue;  // wider than needed
       if (pair && (bn % 32) != 0) continue;       // each CTA's half of B must be whole 8-row swizzle groups (and /16)
+      if (bn > 256 && (bn % 64) != 0) continue;   // wide: two B boxes of bn / 2 rows, whole swizzle groups each
       const int tn = (N + bn - 1) / bn;
       const long long units = static_cast<long long>(pair ? (M_tiles + 1) / 2 : M_tiles) * tn;
       const int slots = pair ? sm_count / 2 : sm_count;
@@ -544,13 +564,16 @@ static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_k
       const double w = static_cast<double>(bn < N ? bn : N);
       const double fetch = 2.84 * (128.0 + (pair ? bn / 2 : bn));
       const double per_kb = (2.0 * w > fetch ? 2.0 * w : fetch) + (pair ? 4000.0 : 600.0) / num_kb;  // pairs pay extra per-tile hand-offs
-      const double cost = static_cast<double>(waves) * per_kb;
+      // the drain of a tile (~2600 cycles per pair of 64-column groups) hides behind the next tile's mainloop except
+      // for the last tile of a CTA - and for EVERY tile of a wide plan, whose single accumulator cannot be
+      // double-buffered
+      const double epi = 2600.0 * ((w / gran + 1.0) / 2.0);
+      const double cost = static_cast<double>(waves) * per_kb + (bn > 256 ? static_cast<double>(waves) : 1.0) * epi / num_kb;
       if (cost < best.cost - 1e-9) best = TilePlan{bn, pair, cost};
     }
   }
   return best;
 }
-
 
 template <bool F, bool G, bool R, bool P>
 static int launch_one(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
@@ -641,9 +664,13 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   if (bn_tile == 0) bn_tile = plan.bn;
   if (force == 1) d.pair = 0;
   if (force == 2) d.pair = 1;
-  B200SD_REQUIRE(bn_tile >= gran && bn_tile <= 256 && (bn_tile % gran) == 0 && (!d.pair || (bn_tile % 32) == 0),
-                 B200SD_ERR_BAD_ARGUMENT, "gemm: bad bn_hint %d (must be a multiple of %d, <= 256)", bn_tile, gran);
+  if (bn_tile > 256 && force != 2) d.pair = 0;  // wide tiles are single-CTA
+  B200SD_REQUIRE(bn_tile >= gran && bn_tile <= (d.pair ? 256 : 512) && (bn_tile % gran) == 0 &&
+                     (!d.pair || (bn_tile % 32) == 0) && (bn_tile <= 256 || (bn_tile % 64) == 0),
+                 B200SD_ERR_BAD_ARGUMENT, "gemm: bad bn_hint %d (multiple of %d, <= 256, or <= 512 in multiples of 64 "
+                 "for single-CTA tiles)", bn_tile, gran);
   d.BN = bn_tile;
+  d.wide = bn_tile > 256 ? 1 : 0;
   d.tiles_ncol = ceil_div(h.n, d.BN);
   d.div_munits = make_fastdiv(static_cast<uint32_t>(d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m));
   d.div_tw = make_fastdiv(static_cast<uint32_t>(d.tiles_w));
@@ -708,7 +735,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
     const uint64_t ktot = static_cast<uint64_t>(d.taps) * (d.cblk0 + d.cblk1) * kBlockK;
     const uint64_t dims[2] = {ktot, static_cast<uint64_t>(h.n)};
     const uint64_t st[1] = {ktot * 2};
-    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(d.pair ? d.BN / 2 : d.BN)};
+    const uint32_t box[2] = {kBlockK, static_cast<uint32_t>((d.pair || d.wide) ? d.BN / 2 : d.BN)};
     if (int e = encode_tmap_act(&d.tmB, h.w, 2, dims, st, box)) return e;
   }
   {

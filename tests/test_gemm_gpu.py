@@ -42,7 +42,10 @@ def _rand(*shape, scale=1.0):
                                       (700, 320, 320, 0), (2048, 640, 200, 128),
                                       # forced tile modes: 1000 + bn = single-CTA tiles, 2000 + bn = CTA pairs
                                       (300, 320, 200, 2128), (700, 320, 320, 2192), (4096, 1280, 320, 2256),
-                                      (65536, 320, 960, 2256), (65536, 320, 960, 1256), (1000, 64, 64, 2064)])
+                                      (65536, 320, 960, 2256), (65536, 320, 960, 1256), (1000, 64, 64, 2064),
+                                      # wide tiles (256 < bn <= 512): one TMEM accumulator, two MMAs / B loads a step
+                                      (4096, 1280, 1280, 1320), (4096, 320, 1000, 512), (700, 192, 328, 384),
+                                      (40000, 320, 960, 1320)])
 def test_linear(cuda_lib, b200sd, M, K, N, bn):
     torch.manual_seed(0)
     ops = b200sd.ops
@@ -116,6 +119,42 @@ def test_conv3x3(cuda_lib, b200sd, nimg, H, W, cin, cout):
     torch.cuda.synchronize()
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=1).permute(0, 2, 3, 1)
     _report(f"conv3x3 {nimg}x{H}x{W} {cin}->{cout}", out, ref, 2e-3)
+
+
+def test_wide_tiles_conv_residual_geglu_f32(cuda_lib, b200sd):
+    """Wide-tile plan through the other epilogues: 3x3 conv + residual + fused GroupNorm statistics, GEGLU, fp32 out."""
+    torch.manual_seed(8)
+    ops, L = b200sd.ops, b200sd.lib
+    s = ops.current_stream()
+    nimg, H, W, cin, cout = 16, 16, 16, 128, 640
+    x, w = _rand(nimg, H, W, cin), _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+    bias, res = torch.randn(cout, device="cuda"), _rand(nimg, H, W, cout)
+    out = torch.full((nimg, H, W, cout), float("nan"), device="cuda", dtype=ACT())
+    stats = torch.zeros(nimg, 32, 2, device="cuda")
+    ops.gemm(x, ops.pack_conv_weight(w.float().cpu()).cuda(), out, nimg=nimg, h=H, w_=W, c0=cin, n=cout, ksize=3,
+             bias=bias, residual=res, gn_stats=stats, gn_groups=32, bn_hint=320)(s)
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=1).permute(0, 2, 3, 1) + res.float()
+    _report("wide conv3x3 + residual", out, ref, 1e-2)
+    g = out.float().reshape(nimg, H * W, 32, cout // 32)
+    want = torch.stack([g.sum(dim=(1, 3)), (g * g).sum(dim=(1, 3))], dim=-1)
+    assert (stats - want).abs().max().item() <= 2e-4 * want.abs().max().item() + 1e-2
+    M, K, Fh = 4096, 320, 512
+    xl = _rand(M, K)
+    w2, b2 = _rand(2 * Fh, K, scale=K ** -0.5), torch.randn(2 * Fh, device="cuda")
+    perm = ops.geglu_perm(2 * Fh)
+    outg = torch.empty(M, Fh, device="cuda", dtype=ACT())
+    ops.gemm(xl, ops.pack_linear_weight(w2.float().cpu()[perm]).cuda(), outg, nimg=1, h=1, w_=M, c0=K, n=2 * Fh,
+             bias=b2[perm.cuda()].contiguous(), act=L.ACT_GEGLU, bn_hint=512)(s)
+    torch.cuda.synchronize()
+    z = xl.float() @ w2.float().t() + b2
+    _report("wide geglu", outg, z[:, :Fh] * F.gelu(z[:, Fh:]), 1e-2)
+    wl = _rand(352, K, scale=K ** -0.5)
+    out32 = torch.empty(M, 352, device="cuda", dtype=torch.float32)
+    ops.gemm(xl, ops.pack_linear_weight(wl.float().cpu()).cuda(), out32, nimg=1, h=1, w_=M, c0=K, n=352,
+             bn_hint=352)(s)
+    torch.cuda.synchronize()
+    _report("wide fp32 out", out32, xl.float() @ wl.float().t(), 2e-5 * 50)
 
 
 @pytest.mark.parametrize("mode", [1000, 2000])
