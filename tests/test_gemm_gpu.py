@@ -152,7 +152,7 @@ def test_wide_tiles_conv_residual_geglu_f32(cuda_lib, b200sd):
     wl = _rand(352, K, scale=K ** -0.5)
     out32 = torch.empty(M, 352, device="cuda", dtype=torch.float32)
     ops.gemm(xl, ops.pack_linear_weight(wl.float().cpu()).cuda(), out32, nimg=1, h=1, w_=M, c0=K, n=352,
-             bn_hint=352)(s)
+             bn_hint=384)(s)
     torch.cuda.synchronize()
     _report("wide fp32 out", out32, xl.float() @ wl.float().t(), 2e-5 * 50)
 
