@@ -552,11 +552,12 @@ static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_k
   TilePlan best{gran, 0, 1e30};
   for (int pair = 0; pair < 2; ++pair) {
     if (pair && M_tiles < 2) continue;
-    // single-CTA tiles may be wide (up to 512 columns, one TMEM accumulator): worth it when it saves a whole round
-    for (int bn = pair ? 256 : 512; bn >= gran; bn -= gran) {
+    // (wide tiles - 256 < bn <= 512, bn_hint only - are not considered: measured on the one-wave shapes they were
+    // meant for, M = 4096 x N = 1280, a 128 x 320 tile is within 6 % of two rounds of 128 x 256 either way, because
+    // the single round then runs into the L2 -> SM operand bandwidth)
+    for (int bn = 256; bn >= gran; bn -= gran) {
       if (bn - gran >= N && bn > gran) continue;  // wider than needed
       if (pair && (bn % 32) != 0) continue;       // each CTA's half of B must be whole 8-row swizzle groups (and /16)
-      if (bn > 256 && (bn % 64) != 0) continue;   // wide: two B boxes of bn / 2 rows, whole swizzle groups each
       const int tn = (N + bn - 1) / bn;
       const long long units = static_cast<long long>(pair ? (M_tiles + 1) / 2 : M_tiles) * tn;
       const int slots = pair ? sm_count / 2 : sm_count;
@@ -564,11 +565,7 @@ static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_k
       const double w = static_cast<double>(bn < N ? bn : N);
       const double fetch = 2.84 * (128.0 + (pair ? bn / 2 : bn));
       const double per_kb = (2.0 * w > fetch ? 2.0 * w : fetch) + (pair ? 4000.0 : 600.0) / num_kb;  // pairs pay extra per-tile hand-offs
-      // the drain of a tile (~2600 cycles per pair of 64-column groups) hides behind the next tile's mainloop except
-      // for the last tile of a CTA - and for EVERY tile of a wide plan, whose single accumulator cannot be
-      // double-buffered
-      const double epi = 2600.0 * ((w / gran + 1.0) / 2.0);
-      const double cost = static_cast<double>(waves) * per_kb + (bn > 256 ? static_cast<double>(waves) : 1.0) * epi / num_kb;
+      const double cost = static_cast<double>(waves) * per_kb;
       if (cost < best.cost - 1e-9) best = TilePlan{bn, pair, cost};
     }
   }

@@ -267,7 +267,7 @@ def mode_sweep():
         res = torch.randn(m, nout, device="cuda").to(dt) if has_res else None
         bias = torch.zeros(nn, device="cuda")
         results = {}
-        for hint in [0] + [md + bn for md in (1000, 2000) for bn in (64, 96, 128, 160, 192, 224, 256)]:
+        for hint in [0] + [md + bn for md in (1000, 2000) for bn in (64, 128, 192, 256)] + [320, 384, 448, 512]:
             try:
                 call = ops.gemm(x, w, out, c0=cin, n=nn, ksize=ks, bias=bias, bn_hint=hint, residual=res,
                                 act=L.ACT_GEGLU if geglu else L.ACT_NONE, **geo)
