@@ -225,3 +225,48 @@ def test_oracle_pipeline_tiny_runs_and_is_deterministic(b200sd):
     # batch invariance: image 1 of the batch == the same prompt/seed generated alone (sharding invariance on CPU)
     assert (a["latents"][1] - b["latents"][0]).abs().max().item() < 1e-4
     assert math.isfinite(float(a["latents"].abs().max()))
+
+
+# ------------------------------------------------------------------------------------------------ attention anchors
+def test_oracle_attention_matches_torch_sdpa():
+    """oracle.unet.Attention (self- and cross-attention of BasicTransformerBlock) against an independent statement of
+    the same layer built from torch's own F.scaled_dot_product_attention + F.linear (torch is the reference's runtime,
+    configmap.yaml:10): same weights, fp32, 1e-5."""
+    import torch.nn.functional as F
+    from oracle.unet import Attention
+    torch.manual_seed(0)
+    for dim, heads, ctx_dim, n, m in ((320, 8, None, 96, 96), (640, 8, 768, 50, 77), (64, 2, 32, 33, 7)):
+        att = Attention(dim, heads, ctx_dim).eval()
+        x = torch.randn(2, n, dim)
+        ctx = None if ctx_dim is None else torch.randn(2, m, ctx_dim)
+        src = x if ctx is None else ctx
+        with torch.no_grad():
+            got = att(x, ctx)
+            d = dim // heads
+            q = F.linear(x, att.to_q.weight).view(2, n, heads, d).transpose(1, 2)
+            k = F.linear(src, att.to_k.weight).view(2, src.shape[1], heads, d).transpose(1, 2)
+            v = F.linear(src, att.to_v.weight).view(2, src.shape[1], heads, d).transpose(1, 2)
+            o = F.scaled_dot_product_attention(q, k, v)  # default scale = d ** -0.5, no mask
+            ref = F.linear(o.transpose(1, 2).reshape(2, n, dim), att.to_out[0].weight, att.to_out[0].bias)
+        assert (got - ref).abs().max().item() < 1e-5 * max(1.0, ref.abs().max().item())
+
+
+def test_oracle_vae_attention_matches_torch_sdpa():
+    """oracle.vae.VaeAttention (single head, d = C, GroupNorm in front, residual behind) against
+    F.group_norm + F.scaled_dot_product_attention + F.linear."""
+    import torch.nn.functional as F
+    from oracle.vae import VaeAttention
+    torch.manual_seed(1)
+    for c, groups, h, w in ((64, 8, 6, 5), (512, 32, 8, 8)):
+        att = VaeAttention(c, groups).eval()
+        x = torch.randn(2, c, h, w)
+        with torch.no_grad():
+            got = att(x)
+            t = F.group_norm(x, groups, att.group_norm.weight, att.group_norm.bias, 1e-6).flatten(2).transpose(1, 2)
+            q = F.linear(t, att.to_q.weight, att.to_q.bias)[:, None]
+            k = F.linear(t, att.to_k.weight, att.to_k.bias)[:, None]
+            v = F.linear(t, att.to_v.weight, att.to_v.bias)[:, None]
+            o = F.scaled_dot_product_attention(q, k, v)[:, 0]
+            o = F.linear(o, att.to_out[0].weight, att.to_out[0].bias)
+            ref = o.transpose(1, 2).reshape(2, c, h, w) + x
+        assert (got - ref).abs().max().item() < 1e-5 * max(1.0, ref.abs().max().item())
