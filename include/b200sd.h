@@ -92,12 +92,13 @@ typedef struct {
   float alpha;       /* accumulator scale (1.0 for plain layers) */
   /* Optional fused GroupNorm statistics of the OUTPUT (the next layer's GroupNorm, torch.nn.GroupNorm inside
    * ResnetBlock2D / Transformer2DModel): the epilogue adds sum and sum of squares of out[., g * n/gn_groups ...] per
-   * (image, group) to gn_stats [images, gn_groups, 2] with atomics - the caller zeroes it; b200sd_groupnorm_apply then
-   * needs no b200sd_groupnorm_stats pass.  16-bit, non-GEGLU outputs only; n / gn_groups whole and even.  The sums are
+   * (image, group) to gn_stats - the same scratch b200sd_groupnorm_stats fills (b200sd_groupnorm_workspace_bytes;
+   * order-independent integer accumulation) - the caller zeroes it; b200sd_groupnorm_apply then needs no
+   * b200sd_groupnorm_stats pass.  16-bit, non-GEGLU outputs only; n / gn_groups whole and even.  The sums are
    * taken over the ROUNDED 16-bit outputs (what the apply pass reads).  Every 32-row slab of
    * a tile must lie in one image: gn_rows_per_img = 0 takes images from the NHWC geometry (needs
    * pow2ceil(w) * pow2ceil(h) >= 32); for a flattened geometry (nimg = 1, h = 1) pass the rows per image (% 32 == 0). */
-  float* gn_stats;
+  void* gn_stats;
   int32_t gn_groups;
   int32_t gn_rows_per_img;
 } b200sd_gemm_params;
@@ -126,12 +127,16 @@ int b200sd_attention(const b200sd_attn_params* p, b200sd_stream stream);
  * GroupNorm (+ optional SiLU) over the virtual concat of two NHWC sources; two passes.
  * Replaces: torch group_norm + silu in ResnetBlock2D.norm1/norm2, Transformer2DModel.norm, conv_norm_out, VAE
  * norms — SURVEY §8(a) a10.2/a10.3/a13 (K7/K8/K14).
- * stats: f32 [nimg, groups, 2] scratch; b200sd_groupnorm_stats ACCUMULATES into it (caller zeroes it first).
+ * stats: caller-owned scratch of b200sd_groupnorm_workspace_bytes(p) bytes (B200SD_GN_STATS_WORDS 4-byte words per
+ * (image, group), 16-byte aligned); b200sd_groupnorm_stats ACCUMULATES into it (the caller zeroes it first).
+ * The sums are kept as 64-bit fixed-point integers, so the totals - and therefore the images - are bit-identical from
+ * run to run and do not depend on the order in which thread blocks finish (fp32 atomics would).
  */
+#define B200SD_GN_STATS_WORDS 8
 typedef struct {
   const void* x0;
   const void* x1; /* or NULL */
-  float* stats;
+  void* stats;
   const float* gamma; /* f32 [c0+c1] */
   const float* beta;  /* f32 [c0+c1] */
   void* out;          /* act16 [nimg, hw, c0+c1] */
@@ -141,6 +146,8 @@ typedef struct {
 } b200sd_groupnorm_params;
 int b200sd_groupnorm_stats(const b200sd_groupnorm_params* p, b200sd_stream stream);
 int b200sd_groupnorm_apply(const b200sd_groupnorm_params* p, b200sd_stream stream);
+/* bytes of `stats` scratch for p->nimg images and p->groups groups (0 for bad arguments) */
+size_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p);
 
 /* GroupNorm (+ optional SiLU) in ONE call that needs no scratch from the caller and allocates nothing.
  * (No counterpart in the reference: it has no C ABI at all; this exists for hosts of this library.)
@@ -152,8 +159,9 @@ int b200sd_groupnorm_apply(const b200sd_groupnorm_params* p, b200sd_stream strea
  *
  * Same parameters and same result as b200sd_groupnorm_stats followed by b200sd_groupnorm_apply, except that
  * p->stats is IGNORED: the per-(image, group) sums are kept in a fixed array inside the library,
- * B200SD_GN_NOALLOC_MAX_STATS floats (64 KiB) that every GPU which loads the library holds until the process exits.
- *   - limit: nimg * groups * 2 <= B200SD_GN_NOALLOC_MAX_STATS, otherwise B200SD_ERR_TOO_LARGE is returned and nothing
+ * B200SD_GN_NOALLOC_MAX_STATS 4-byte words (64 KiB) that every GPU which loads the library holds until the process
+ * exits.
+ *   - limit: nimg * groups * B200SD_GN_STATS_WORDS <= B200SD_GN_NOALLOC_MAX_STATS (nimg * groups <= 2048), otherwise B200SD_ERR_TOO_LARGE is returned and nothing
  *     is launched (use the two-call form with your own scratch);
  *   - the array is shared by all calls on a device and still holds the previous call's sums, so each call first
  *     clears the part it uses (a cudaMemsetAsync on `stream`); two calls whose GPU work overlaps (different streams,

@@ -15,6 +15,7 @@ from . import clip  # noqa: F401
 from . import unet  # noqa: F401
 from . import vae  # noqa: F401
 from . import pipeline  # noqa: F401
+from . import dist  # noqa: F401
 from .pipeline import StableDiffusionPipeline, StableDiffusionXLPipeline  # noqa: F401
 
 __version__ = "0.1.0"

@@ -500,6 +500,34 @@ __device__ __forceinline__ float gelu_erf_f(float x) {
   return x * phi;
 }
 
+// ------------------------------------------------------------------ order-independent statistics accumulation
+// GroupNorm sums are gathered from many CTAs / warps.  fp32 atomics make the result depend on arrival order (images
+// differed by a few LSB between identical runs), so the partial sums are accumulated as 64-bit INTEGERS instead:
+// integer addition is associative, the total is the same whichever producer arrives first.  A fp32 partial p becomes
+// fixed point with LSB 2^-24, split so that no carry ever crosses words:
+//     p * 2^24 = H * 2^31 + L,  0 <= L < 2^31      acc[0] += H,  acc[1] += L     (two independent 64-bit sums)
+// Both conversions are exact up to the 2^-24 LSB (power-of-two scalings, floor, and a remainder that only drops high
+// bits).  Range: |total| < 2^63 * 128 for H and 2^32 partials for L - far beyond any tensor here.
+// One (image, group) statistics slot = 4 such words {sum H, sum L, sum-of-squares H, sum-of-squares L} = 32 bytes
+// (B200SD_GN_STATS_WORDS 4-byte words in b200sd.h).
+static constexpr int kGnSlotWords64 = 4;
+__device__ __forceinline__ void fixed_split(float p, long long& H, long long& L) {
+  const float h = floorf(p * 0.0078125f);  // p / 128, exact
+  H = __float2ll_rn(h);
+  const float r = fmaf(-128.f, h, p);      // 0 <= r < 128, exact (only high bits are removed)
+  L = __float2ll_rn(r * 16777216.f);
+}
+__device__ __forceinline__ void fixed_add_global(unsigned long long* slot2, float p) {
+  long long H, L;
+  fixed_split(p, H, L);
+  atomicAdd(slot2, static_cast<unsigned long long>(H));  // result unused: compiles to fire-and-forget RED.64
+  atomicAdd(slot2 + 1, static_cast<unsigned long long>(L));
+}
+__device__ __forceinline__ double fixed_value(const unsigned long long* slot2) {
+  return static_cast<double>(static_cast<long long>(slot2[0])) * 128.0 +
+         static_cast<double>(static_cast<long long>(slot2[1])) * 5.9604644775390625e-08;  // 2^-24
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

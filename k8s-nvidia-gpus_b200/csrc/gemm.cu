@@ -67,7 +67,7 @@ struct alignas(64) GemmDev {
   CUtensorMap tmR;  // residual (16-bit), same box
   const float* bias;
   const float* rowbias;
-  float* gn_stats;  // fused GroupNorm statistics of the output, or nullptr
+  unsigned long long* gn_stats;  // fused GroupNorm statistics of the output (32-byte fixed-point slots), or nullptr
   int gn_groups, gn_cpg, gn_rows_per_img;
   int N, BN;
   int nimg, H, W;
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             // Fused GroupNorm statistics of this 128 x 64 output group, read back TRANSPOSED from the staging tile:
             // lane = one column pair, walking the 32 rows my own warp has just written (one image, see b200sd.h) -
             // conflict-free 4-byte loads, a rolled loop.  Lanes of the same channel group are then combined by a
-            // segmented shuffle reduction and the segment heads issue the two atomics.
+            // segmented shuffle reduction and the segment heads add their sums to the (image, group) slot.
             __syncwarp();
             const uint32_t rows_ok = __ballot_sync(0xffffffffu, gn_row_ok);
             const uint32_t wofs = (static_cast<uint32_t>(lane) & 3u) * 4u, chunk = static_cast<uint32_t>(lane) >> 2;
@@ -493,9 +493,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             }
             const int gprev = __shfl_up_sync(0xffffffffu, g, 1);
             if ((lane == 0 || gprev != g) && col < p.N) {
-              float* gst = p.gn_stats + (static_cast<size_t>(gn_img) * p.gn_groups + g) * 2;
-              atomicAdd(gst, gs);
-              atomicAdd(gst + 1, gq);
+              // integer (fixed-point) accumulation: the total does not depend on which warp / CTA arrives first
+              unsigned long long* gst = p.gn_stats + (static_cast<size_t>(gn_img) * p.gn_groups + g) * kGnSlotWords64;
+              fixed_add_global(gst, gs);
+              fixed_add_global(gst + 2, gq);
             }
           }
         }
@@ -696,7 +697,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   B200SD_REQUIRE(d.num_stages >= 2, B200SD_ERR_CUDA, "gemm: not enough shared memory (%d B opt-in)", di.max_smem_optin);
   d.bias = h.bias;
   d.rowbias = h.rowbias;
-  d.gn_stats = h.gn_stats;
+  d.gn_stats = static_cast<unsigned long long*>(h.gn_stats);
   if (h.gn_stats != nullptr) {
     B200SD_REQUIRE(!geglu && !f32, B200SD_ERR_BAD_ARGUMENT, "gemm: fused GroupNorm statistics need a 16-bit, non-GEGLU output");
     B200SD_REQUIRE(h.gn_groups > 0 && (h.n % h.gn_groups) == 0 && ((h.n / h.gn_groups) % 2) == 0, B200SD_ERR_BAD_SHAPE,

@@ -30,19 +30,31 @@ __device__ __forceinline__ void store8(act_t* p, const float (&f)[8]) {
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: stats
 // grid (chunks, nimg).  Each thread owns one 8-channel vector column ("octet") and walks pixels, keeping 8 sums and
-// 8 sums of squares in registers; one shared-memory atomic pass per CTA, then one global atomic per (group, CTA).
+// 8 sums of squares in registers (fixed order: deterministic); the per-thread results are then added as 64-bit
+// fixed-point integers (common.cuh, fixed_split) - first into shared memory, then one global add per (group, CTA)
+// word - so the totals are bit-identical from run to run whatever the CTA / warp arrival order.
 __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __restrict__ x0,
-                                                                const act_t* __restrict__ x1, float* __restrict__ stats,
-                                                                int hw, int c0, int c1, int groups, int pix_per_cta) {
-  extern __shared__ float gacc[];  // [groups][2]
+                                                                const act_t* __restrict__ x1,
+                                                                unsigned long long* __restrict__ stats, int hw, int c0,
+                                                                int c1, int groups, int pix_per_cta) {
+  extern __shared__ unsigned long long gacc[];  // [groups][4]: {sum H, sum L, sumsq H, sumsq L}
   const int n = blockIdx.y;
   const int C = c0 + c1;
   const int octs = C >> 3;
   const int cpg = C / groups;
   const int p_begin = blockIdx.x * pix_per_cta;
   const int p_end = min(hw, p_begin + pix_per_cta);
-  for (int i = threadIdx.x; i < groups * 2; i += blockDim.x) gacc[i] = 0.f;
+  for (int i = threadIdx.x; i < groups * kGnSlotWords64; i += blockDim.x) gacc[i] = 0ull;
   __syncthreads();
+  auto add_run = [&](int g, float rs, float rq) {
+    long long H, L;
+    fixed_split(rs, H, L);
+    atomicAdd(&gacc[4 * g], static_cast<unsigned long long>(H));
+    atomicAdd(&gacc[4 * g + 1], static_cast<unsigned long long>(L));
+    fixed_split(rq, H, L);
+    atomicAdd(&gacc[4 * g + 2], static_cast<unsigned long long>(H));
+    atomicAdd(&gacc[4 * g + 3], static_cast<unsigned long long>(L));
+  };
   const int Wd = min(octs, kNormThreads);
   const int S = kNormThreads / Wd;
   const int stream = threadIdx.x / Wd;
@@ -93,21 +105,19 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
       for (int e = 0; e < 8; ++e) {
         const int g = (ch0 + e) / cpg;
         if (g != g_cur) {
-          atomicAdd(&gacc[2 * g_cur], rs);
-          atomicAdd(&gacc[2 * g_cur + 1], rq);
+          add_run(g_cur, rs, rq);
           rs = rq = 0.f;
           g_cur = g;
         }
         rs += s[e];
         rq += q[e];
       }
-      atomicAdd(&gacc[2 * g_cur], rs);
-      atomicAdd(&gacc[2 * g_cur + 1], rq);
+      add_run(g_cur, rs, rq);
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < groups * 2; i += blockDim.x)
-    atomicAdd(&stats[static_cast<size_t>(n) * groups * 2 + i], gacc[i]);
+  for (int i = threadIdx.x; i < groups * kGnSlotWords64; i += blockDim.x)
+    if (gacc[i] != 0ull) atomicAdd(&stats[static_cast<size_t>(n) * groups * kGnSlotWords64 + i], gacc[i]);
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: apply
@@ -116,7 +126,7 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
 // loop is load16 -> 8 fma (+SiLU) -> store16 with four pixels in flight.
 __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* __restrict__ x0,
                                                                 const act_t* __restrict__ x1,
-                                                                const float* __restrict__ stats,
+                                                                const unsigned long long* __restrict__ stats,
                                                                 const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, act_t* __restrict__ out,
                                                                 int hw, int c0, int c1, int groups, int pix_per_cta,
@@ -125,7 +135,7 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
   const int C = c0 + c1;
   const int octs = C >> 3;
   const int cpg = C / groups;
-  const float inv_cnt = 1.f / (static_cast<float>(hw) * static_cast<float>(cpg));
+  const double inv_cnt = 1.0 / (static_cast<double>(hw) * static_cast<double>(cpg));
   const int p_begin = blockIdx.x * pix_per_cta;
   const int p_end = min(hw, p_begin + pix_per_cta);
   const int Wd = min(octs, kNormThreads);
@@ -135,14 +145,24 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
   for (int oct = threadIdx.x % Wd; oct < octs; oct += Wd) {
     const int ch0 = oct * 8;
     float sc[8], sh[8];
+    int g_have = -1;
+    float mean = 0.f, rstd = 0.f;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int c = ch0 + e;
       const int g = c / cpg;
-      const float2 st = *reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * groups + g) * 2);
-      const float mean = st.x * inv_cnt;
-      const float var = fmaxf(st.y * inv_cnt - mean * mean, 0.f);
-      const float rstd = rsqrtf(var + eps);
+      if (g != g_have) {
+        // exact integer totals -> mean / variance in double (no E[x^2] - mean^2 cancellation in fp32)
+        const unsigned long long* sl = stats + (static_cast<size_t>(n) * groups + g) * kGnSlotWords64;
+        const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(sl);
+        const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(sl + 2);
+        const unsigned long long sw[2] = {a.x, a.y}, qw[2] = {b.x, b.y};
+        const double m = fixed_value(sw) * inv_cnt;
+        const double var = fmax(fixed_value(qw) * inv_cnt - m * m, 0.0);
+        mean = static_cast<float>(m);
+        rstd = rsqrtf(static_cast<float>(var) + eps);
+        g_have = g;
+      }
       sc[e] = __ldg(gamma + c) * rstd;
       sh[e] = __ldg(beta + c) - mean * sc[e];
     }
@@ -326,14 +346,10 @@ static int gn_check(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chu
   B200SD_REQUIRE((h.c1 == 0) == (h.x1 == nullptr), B200SD_ERR_BAD_ARGUMENT, "groupnorm: x1 and c1 must agree");
   B200SD_REQUIRE(aligned16(h.x0) && aligned16(h.x1) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
                  "groupnorm: pointers must be 16-byte aligned");
-  // CTA count: ~128 KB of input per CTA, between 4 and 16 CTAs per SM over the whole launch.  Small tensors (UNet)
-  // want few CTAs (per-thread set-up and the per-CTA atomics dominate), large ones (VAE at 512x512) want many waves.
-  const long long bytes = 2ll * h.nimg * h.hw * C;
-  long long ctas = bytes / (128 << 10);
-  if (ctas < 4 * 148) ctas = 4 * 148;
-  if (ctas > 16 * 148) ctas = 16 * 148;
-  int want = static_cast<int>((ctas + h.nimg - 1) / h.nimg);
-  int ppc = (h.hw + want - 1) / want;
+  // Pixels per CTA: ~64 KB of input, a function of the per-image shape ONLY - never of the batch size - so that an
+  // image's partial sums (and with them its pixels) are bit-identical whatever batch it rides in (batch / sharding
+  // invariance).
+  int ppc = (64 << 10) / (2 * C);
   if (ppc < 8) ppc = 8;
   if (ppc > h.hw) ppc = h.hw;
   *pix_per_cta = ppc;
@@ -351,8 +367,10 @@ extern "C" int b200sd_groupnorm_stats(const b200sd_groupnorm_params* hp, b200sd_
   if (int e = gn_check(*hp, &ppc, &chunks)) return e;
   const b200sd_groupnorm_params& h = *hp;
   dim3 grid(chunks, h.nimg);
-  gn_stats_kernel<<<grid, kNormThreads, h.groups * 2 * sizeof(float), static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
+  gn_stats_kernel<<<grid, kNormThreads, h.groups * kGnSlotWords64 * sizeof(unsigned long long),
+                    static_cast<cudaStream_t>(stream_)>>>(static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1),
+                                                          static_cast<unsigned long long*>(h.stats), h.hw, h.c0, h.c1,
+                                                          h.groups, ppc);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
@@ -367,10 +385,15 @@ extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_
   (void)C;
   dim3 grid(chunks, h.nimg);
   gn_apply_kernel<<<grid, kNormThreads, 0, static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
-      static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<const unsigned long long*>(h.stats),
+      h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
+}
+
+extern "C" size_t b200sd_groupnorm_workspace_bytes(const b200sd_groupnorm_params* p) {
+  if (!p || p->nimg <= 0 || p->groups <= 0) return 0;
+  return static_cast<size_t>(p->nimg) * p->groups * B200SD_GN_STATS_WORDS * 4;
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm, no allocation
@@ -403,13 +426,15 @@ static int gn_noalloc_scratch(float** out) {
 extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200sd_stream stream_) {
   B200SD_REQUIRE(hp != nullptr, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: params is NULL");
   B200SD_REQUIRE(hp->nimg > 0 && hp->groups > 0, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: bad arguments");
-  const long long need = 2ll * hp->nimg * hp->groups;
+  const long long need = static_cast<long long>(B200SD_GN_STATS_WORDS) * hp->nimg * hp->groups;  // 4-byte words
   B200SD_REQUIRE(need <= B200SD_GN_NOALLOC_MAX_STATS, B200SD_ERR_TOO_LARGE,
-                 "groupnorm_noalloc: nimg * groups * 2 = %lld statistics exceed the built-in scratch of %d floats "
+                 "groupnorm_noalloc: nimg * groups * 8 = %lld statistics words exceed the built-in scratch of %d words "
                  "(use b200sd_groupnorm_stats/_apply with caller-provided scratch for larger problems)",
                  need, B200SD_GN_NOALLOC_MAX_STATS);
   b200sd_groupnorm_params h = *hp;  // same kernels as the two-call path; only the scratch pointer differs
-  if (int e = gn_noalloc_scratch(&h.stats)) return e;
+  float* scratch = nullptr;
+  if (int e = gn_noalloc_scratch(&scratch)) return e;
+  h.stats = scratch;
   int ppc, chunks;
   if (int e = gn_check(h, &ppc, &chunks)) return e;
   B200SD_REQUIRE(h.out && h.gamma && h.beta, B200SD_ERR_BAD_ARGUMENT, "groupnorm_noalloc: out/gamma/beta required");
@@ -419,12 +444,13 @@ extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200s
   // the scratch still holds the previous call's sums: the accumulators of this call must start from zero
   B200SD_CUDA_CHECK(cudaMemsetAsync(h.stats, 0, static_cast<size_t>(need) * sizeof(float), s));
   dim3 grid(chunks, h.nimg);
-  gn_stats_kernel<<<grid, kNormThreads, h.groups * 2 * sizeof(float), s>>>(
-      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.hw, h.c0, h.c1, h.groups, ppc);
+  gn_stats_kernel<<<grid, kNormThreads, h.groups * kGnSlotWords64 * sizeof(unsigned long long), s>>>(
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<unsigned long long*>(h.stats), h.hw,
+      h.c0, h.c1, h.groups, ppc);
   B200SD_CUDA_CHECK(cudaGetLastError());
   gn_apply_kernel<<<grid, kNormThreads, 0, s>>>(
-      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), h.stats, h.gamma, h.beta,
-      static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
+      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<const unsigned long long*>(h.stats),
+      h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }

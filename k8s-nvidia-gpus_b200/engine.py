@@ -14,7 +14,7 @@ from . import ops
 
 
 class Act:
-    """NHWC 16-bit activation: tensor [nimg, h, w, c] (contiguous).  `stats` = (f32 [nimg, groups, 2], groups) when
+    """NHWC 16-bit activation: tensor [nimg, h, w, c] (contiguous).  `stats` = (statistics scratch slice, groups) when
     the kernel that produced it also accumulated its GroupNorm statistics (fused into the GEMM epilogue)."""
     __slots__ = ("t", "nimg", "h", "w", "c", "stats")
 
@@ -126,7 +126,7 @@ class DeviceWeights:
 
 
 class Builder:
-    def __init__(self, device, stats_floats: int = 1 << 20, fuse_gn_stats: bool = False):
+    def __init__(self, device, stats_words: int = 1 << 21, fuse_gn_stats: bool = False):
         """fuse_gn_stats: let long-reduction 3x3 convs accumulate the GroupNorm statistics of their output in the
         epilogue.  Measured: the VAE decoder gains 9 % (its statistics passes stream 0.5 GB tensors), the UNet step
         about 1 % (43 of 61 passes go, the conv epilogues get longer)."""
@@ -134,7 +134,8 @@ class Builder:
         self.fuse_gn_stats = fuse_gn_stats
         self.plan = Plan()
         self.pool = {}
-        self.stats = torch.zeros(stats_floats, dtype=torch.float32, device=device)
+        # GroupNorm statistics scratch of the whole plan (4-byte words; one memset per run)
+        self.stats = torch.zeros(stats_words, dtype=torch.int32, device=device)
         self.stats_off = 0
         self.plan.keep.append(self.stats)
 
@@ -170,7 +171,7 @@ class Builder:
         self.plan.calls.append(call)
 
     def stats_slice(self, nimg, groups):
-        nst = nimg * groups * 2
+        nst = nimg * groups * L.GN_STATS_WORDS
         assert self.stats_off + nst <= self.stats.numel(), "GroupNorm statistics scratch exhausted"
         st = self.stats[self.stats_off:self.stats_off + nst]
         self.stats_off += nst

@@ -14,7 +14,8 @@ _lib = None
 ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU, ACT_GELU = 0, 1, 2, 3, 4
 ACT16, F32 = 0, 1
 BF16 = ACT16  # historical alias
-GN_NOALLOC_MAX_STATS = 16384  # B200SD_GN_NOALLOC_MAX_STATS
+GN_NOALLOC_MAX_STATS = 16384  # B200SD_GN_NOALLOC_MAX_STATS (4-byte words)
+GN_STATS_WORDS = 8  # B200SD_GN_STATS_WORDS: 4-byte words of statistics scratch per (image, group)
 ST_TIMESTEP, ST_IN_SCALE, ST_KIND, ST_C0, ST_C1, ST_C2, ST_C3, ST_W0, ST_PNDM_MODE, ST_PUSH, ST_WIDTH = (
     0, 1, 2, 3, 4, 5, 6, 7, 11, 12, 16)
 
@@ -104,6 +105,7 @@ ENTRY_POINTS = {
     "b200sd_groupnorm_stats": GroupNormParams,
     "b200sd_groupnorm_apply": GroupNormParams,
     "b200sd_groupnorm_noalloc": GroupNormParams,
+    "b200sd_groupnorm_workspace_bytes": None,
     "b200sd_layernorm": LayerNormParams,
     "b200sd_prep_unet_input": PrepParams,
     "b200sd_timestep_embedding": TembParams,
@@ -150,6 +152,8 @@ def load():
         fn.restype = C.c_int
     lib.b200sd_im2col_s2_bytes.argtypes = [C.POINTER(Im2colS2Params)]
     lib.b200sd_im2col_s2_bytes.restype = C.c_size_t
+    lib.b200sd_groupnorm_workspace_bytes.argtypes = [C.POINTER(GroupNormParams)]
+    lib.b200sd_groupnorm_workspace_bytes.restype = C.c_size_t
     _lib = lib
     return lib
 

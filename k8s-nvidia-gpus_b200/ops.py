@@ -102,6 +102,25 @@ def groupnorm(x0, out, stats, gamma, beta, *, nimg, hw, c0, groups, eps, silu, x
     return (L.Call("b200sd_groupnorm_stats", p, keep=keep), L.Call("b200sd_groupnorm_apply", p, keep=keep))
 
 
+def groupnorm_stats_buffer(nimg: int, groups: int, device="cuda") -> torch.Tensor:
+    """Zeroed statistics scratch for `groupnorm` / fused GEMM statistics: int32 [nimg, groups, GN_STATS_WORDS]
+    (64-bit fixed-point sums; size = b200sd_groupnorm_workspace_bytes)."""
+    return torch.zeros(nimg, groups, L.GN_STATS_WORDS, dtype=torch.int32, device=device)
+
+
+def groupnorm_stats_values(buf: torch.Tensor) -> torch.Tensor:
+    """Decode a statistics scratch (see groupnorm_stats_buffer) to float64 [nimg, groups, 2] = (sum, sum of squares):
+    each is two int64 words (H, L) with value H * 128 + L * 2^-24.  For tests and tools."""
+    w = buf.contiguous().view(torch.int64).reshape(buf.shape[0], buf.shape[1], 2, 2).to(torch.float64)
+    return w[..., 0] * 128.0 + w[..., 1] * 2.0 ** -24
+
+
+def groupnorm_workspace_bytes(*, nimg, groups) -> int:
+    p = L.GroupNormParams()
+    p.nimg, p.groups = nimg, groups
+    return int(L.load().b200sd_groupnorm_workspace_bytes(C.byref(p)))
+
+
 def layernorm(x, out, gamma, beta, *, rows, c, eps):
     p = L.LayerNormParams()
     p.x, p.gamma, p.beta, p.out, p.rows, p.c, p.eps = _ptr(x), _ptr(gamma), _ptr(beta), _ptr(out), rows, c, eps

@@ -13,7 +13,9 @@ request there dies with NameError instead of continuing, :30-35); the `--steps` 
 Additions (supersets, all optional): `--local` generates in-process on the local B200(s) through
 b200sd.StableDiffusionPipeline instead of HTTP — batched (`--batch-size`), seeded per image (`--seed` + index),
 with `--guidance-scale/--width/--height/--scheduler/--model`, `--prompts-file` (one prompt per line, cycled) and PNG
-encoding on `--png-threads` threads overlapped with the next batch; `--concurrency N` keeps N HTTP requests in flight
+encoding on `--png-threads` threads overlapped with the next batch, and sharded over all GPUs of the node when started
+under `torchrun --nproc-per-node N -- batch_generate.py ...` (one process per GPU, same files for any N; the `--` keeps
+torchrun's own parser away from `--local`); `--concurrency N` keeps N HTTP requests in flight
 so that b200sd's batching server can coalesce them (default 1: the reference's sequential loop).
 """
 import argparse
@@ -77,6 +79,11 @@ def generate_local(prompts, steps, out_dir: Path, prefix: str, count: int, *, ba
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     if root not in sys.path:
         sys.path.insert(0, root)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        return generate_local_sharded(prompts, steps, out_dir, prefix, count, batch_size=batch_size, seed=seed,
+                                      guidance_scale=guidance_scale, width=width, height=height, scheduler=scheduler,
+                                      model=model, pipe=pipe, png_threads=png_threads)
     if pipe is None:
         import b200sd
         pipe = b200sd.StableDiffusionPipeline.from_pretrained(model, scheduler=scheduler)
@@ -116,6 +123,50 @@ def generate_local(prompts, steps, out_dir: Path, prefix: str, count: int, *, ba
     print("[*] Generation loop finished (with possible errors).")
 
 
+def generate_local_sharded(prompts, steps, out_dir: Path, prefix: str, count: int, *, batch_size: int, seed: int,
+                           guidance_scale: float, width: int, height: int, scheduler, model: str, pipe=None,
+                           png_threads: int = 4, backend: str | None = None) -> None:
+    """Local mode under `torchrun --nproc-per-node N`: one process per GPU, the `count` images sharded over the ranks
+    by b200sd.dist.generate_sharded (contiguous slices, image i always seeded with seed + i - 1, so the files are
+    byte-identical for any N), one gather of the uint8 images, rank 0 writes the same files as the single-GPU mode."""
+    import torch
+    import torch.distributed as dist
+    import b200sd
+    rank, local = int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    own_group = not dist.is_initialized()
+    if pipe is None:
+        torch.cuda.set_device(local)
+        if own_group:
+            dist.init_process_group(backend or "nccl", device_id=torch.device("cuda", local))
+        pipe = b200sd.StableDiffusionPipeline.from_pretrained(model, device=f"cuda:{local}", scheduler=scheduler)
+    elif own_group:
+        dist.init_process_group(backend or "gloo")
+    all_prompts = [prompts[i % len(prompts)] for i in range(count)]
+    t0 = time.time()
+    images = b200sd.dist.generate_sharded(pipe, all_prompts, base_seed=seed, max_batch=batch_size,
+                                          num_inference_steps=steps, guidance_scale=guidance_scale, width=width,
+                                          height=height)
+    dt = time.time() - t0
+    if rank == 0:
+        from concurrent.futures import ThreadPoolExecutor
+        from PIL import Image
+        out_dir.mkdir(parents=True, exist_ok=True)
+        arr = images.cpu().numpy()
+        with ThreadPoolExecutor(max_workers=png_threads) as pool:
+            futs = []
+            for i in range(count):
+                target = _target(out_dir, prefix, i + 1)
+                print(f"[*] Generating {target.name} -> {target}")
+                futs.append(pool.submit(lambda a, t: Image.fromarray(a).save(t, format="PNG"), arr[i], target))
+                print(f"    ✔ done in {dt / max(1, count):.2f}s")
+            for f in futs:
+                f.result()
+        print("[*] Generation loop finished (with possible errors).")
+    if own_group:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def build_parser() -> argparse.ArgumentParser:
     ap = argparse.ArgumentParser(description="Batch-generate images via the SD15 API")
     ap.add_argument("prompt", help="prompt to send to the API")
@@ -153,7 +204,8 @@ def main(argv: list) -> int:
                        scheduler=args.scheduler, model=args.model, png_threads=args.png_threads)
     else:
         generate(args.prompt, args.steps, args.url, out_dir, args.prefix, args.count, args.delay, args.concurrency)
-    print(f"All done. Images saved under {out_dir.resolve()}")
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(f"All done. Images saved under {out_dir.resolve()}")
     return 0
 
 

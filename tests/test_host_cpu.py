@@ -366,6 +366,42 @@ def _gloo_worker(rank, world, port, n_prompts, out_dir):
     dist.destroy_process_group()
 
 
+def _gloo_cli_worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), LOCAL_RANK=str(rank),
+                      WORLD_SIZE=str(world))
+    sys.path.insert(0, str(ROOT))
+    sys.path.insert(0, str(ROOT / "scripts"))
+    import importlib
+    cli = importlib.import_module("batch_generate")
+    from pathlib import Path
+    cli.generate_local(["a panda", "a cabin in the woods"], 3, Path(out_dir), "img", 5, batch_size=2, seed=40,
+                       guidance_scale=7.5, width=16, height=16, scheduler=None, model="tiny", pipe=FakePipe())
+
+
+def test_cli_local_mode_shards_under_torchrun_env(tmp_path):
+    """`batch_generate.py --local` with WORLD_SIZE=2 (what torchrun sets): prompts sharded over the ranks through
+    dist.generate_sharded, rank 0 writes the same files a single process writes."""
+    import torch.multiprocessing as mp
+    from PIL import Image
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    two, one = tmp_path / "w2", tmp_path / "w1"
+    mp.spawn(_gloo_cli_worker, args=(2, port, str(two)), nprocs=2, join=True)
+    sys.path.insert(0, str(ROOT / "scripts"))
+    import importlib
+    cli = importlib.import_module("batch_generate")
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE"):
+        os.environ.pop(k, None)
+    cli.generate_local(["a panda", "a cabin in the woods"], 3, one, "img", 5, batch_size=2, seed=40,
+                       guidance_scale=7.5, width=16, height=16, scheduler=None, model="tiny", pipe=FakePipe())
+    names = sorted(p_.name for p_ in two.iterdir())
+    assert names == [f"img_{i:02d}.png" for i in range(1, 6)] == sorted(p_.name for p_ in one.iterdir())
+    for n in names:
+        assert np.array_equal(np.asarray(Image.open(two / n)), np.asarray(Image.open(one / n)))
+
+
 @pytest.mark.parametrize("n_prompts", [5, 1])
 def test_sharded_generation_is_world_size_invariant(tmp_path, n_prompts):
     import torch.multiprocessing as mp

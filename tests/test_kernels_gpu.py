@@ -21,7 +21,7 @@ def test_groupnorm(cuda_lib, b200sd, nimg, hw, c0, c1, groups, silu):
     x1 = (_rand(nimg, hw, c1).float() * 0.5 - 1.1).to(ACT()) if c1 else None
     gamma = torch.randn(C, device="cuda")
     beta = torch.randn(C, device="cuda")
-    stats = torch.zeros(nimg, groups, 2, device="cuda")
+    stats = ops.groupnorm_stats_buffer(nimg, groups)
     out = torch.empty(nimg, hw, C, device="cuda", dtype=ACT())
     st, ap = ops.groupnorm(x0, out, stats, gamma, beta, nimg=nimg, hw=hw, c0=c0, groups=groups, eps=1e-5, silu=silu,
                            x1=x1, c1=c1)
@@ -34,6 +34,36 @@ def test_groupnorm(cuda_lib, b200sd, nimg, hw, c0, c1, groups, silu):
     if silu:
         ref = F.silu(ref)
     _report(f"groupnorm {nimg}x{hw}x{C}", out, ref, 1e-2)
+
+
+def test_groupnorm_is_deterministic_and_handles_large_means(cuda_lib, b200sd):
+    """(1) The statistics are accumulated as integers: two runs on the same input give bit-identical scratch and output
+    (fp32 atomics did not).  (2) mean >> std (the E[x^2] - mean^2 regime): exact totals + double finalisation keep
+    the result on torch.group_norm."""
+    torch.manual_seed(3)
+    ops = b200sd.ops
+    nimg, hw, C, groups = 4, 4096, 320, 32
+    x = (20.0 + 0.25 * torch.randn(nimg, hw, C, device="cuda")).to(ACT())
+    gamma, beta = torch.randn(C, device="cuda"), torch.randn(C, device="cuda")
+    outs, sts = [], []
+    for _ in range(3):
+        stats = ops.groupnorm_stats_buffer(nimg, groups)
+        out = torch.empty(nimg, hw, C, device="cuda", dtype=ACT())
+        st, ap = ops.groupnorm(x, out, stats, gamma, beta, nimg=nimg, hw=hw, c0=C, groups=groups, eps=1e-5, silu=False)
+        st(ops.current_stream())
+        ap(ops.current_stream())
+        torch.cuda.synchronize()
+        outs.append(out)
+        sts.append(stats)
+    assert torch.equal(sts[0], sts[1]) and torch.equal(sts[0], sts[2])
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    g = x.double().reshape(nimg, hw, groups, C // groups)
+    want = torch.stack([g.sum(dim=(1, 3)), (g * g).sum(dim=(1, 3))], dim=-1)
+    got = ops.groupnorm_stats_values(sts[0])
+    assert ((got - want).abs() <= 1e-6 * want.abs() + 1e-3).all()
+    ref = F.group_norm(x.float().permute(0, 2, 1), groups, gamma, beta, 1e-5).permute(0, 2, 1)
+    _report("groupnorm mean >> std", outs[0], ref, 1e-2)
+    assert ops.groupnorm_workspace_bytes(nimg=nimg, groups=groups) == stats.numel() * 4
 
 
 @pytest.mark.parametrize("rows,c", [(77, 768), (4096, 320), (1000, 640), (300, 1280), (64, 32), (10, 2048)])
@@ -224,3 +254,37 @@ def test_layout_kernels(cuda_lib, b200sd):
     ops.latent_to_act(lat, o, b=2, hw=64, scale=1 / 0.18215)(s)
     torch.cuda.synchronize()
     _report("latent_to_bf16", o, torch.cat([lat / 0.18215, torch.zeros_like(lat)], -1), 1e-2)
+
+
+@pytest.mark.parametrize("n", [2, 4, 25])
+def test_cfg_sched_kernel_pndm_follows_oracle_scheduler(cuda_lib, b200sd, n):
+    """cfg_sched_kernel's PNDM / PLMS path driven by the product's own step table - first step (mode 1: keep the
+    sample), repeated second step (mode 2: average with the stored eps, restore the sample, no history push), then the
+    2-, 3- and 4-term linear multistep combines over the device history ring - against oracle.schedulers.PNDMScheduler
+    fed the same guided eps (fp32, 2e-5)."""
+    from oracle.schedulers import PNDMScheduler
+    ops, S = b200sd.ops, b200sd.schedulers
+    torch.manual_seed(n)
+    b, hw, gs = 2, 96, 7.5
+    sched = S.make_schedule("pndm", n, steps_offset=1)
+    o = PNDMScheduler(steps_offset=1)
+    o.set_timesteps(n)
+    assert sched.num_evals == len(o.timesteps) == n + 1
+    table = torch.zeros(sched.num_evals, 16)
+    table.copy_(sched.table)
+    table = table.cuda()
+    counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+    lat = torch.randn(b, hw, 4, device="cuda")
+    hist = torch.zeros(4, b, hw, 4, device="cuda")
+    cur = torch.zeros(b, hw, 4, device="cuda")
+    x_o = lat.cpu().clone()
+    s = ops.current_stream()
+    for i, t in enumerate(o.timesteps):
+        eps = torch.randn(2 * b, hw, 4, device="cuda") * 0.7
+        ops.cfg_scheduler_step(eps, lat, hist, cur, table, counter, b=b, hw=hw, ld_eps=4, cfg=True,
+                               guidance_scale=gs)(s)
+        torch.cuda.synchronize()
+        e = eps.cpu()
+        x_o = o.step(e[:b] + gs * (e[b:] - e[:b]), t, x_o)
+        _report(f"pndm n={n} eval {i}", lat, x_o.cuda(), 2e-5)
+        assert counter.tolist() == [i + 1, 0]

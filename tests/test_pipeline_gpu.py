@@ -125,8 +125,7 @@ def test_dynamic_batching_is_transparent(tiny, b200sd):
     bt.shutdown()
     assert bt.stats["largest"] >= 2
     for a, b in zip(got, solo):
-        d = np.abs(a.astype(np.int32) - b.astype(np.int32))
-        assert d.max() <= 2, d.max()  # GroupNorm atomics order only
+        assert np.array_equal(a, b)  # byte-identical: nothing in the path depends on the batch an image rides in
 
 
 def test_from_pretrained_checkpoint_directory(tiny, b200sd, tmp_path):

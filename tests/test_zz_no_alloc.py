@@ -8,7 +8,7 @@ offered as a single call whose statistics scratch is a fixed 64 KiB array inside
 This test calls the new entry point through the C ABI (ctypes, raw pointers) and compares it with the existing
 two-call path (b200sd_groupnorm_stats + b200sd_groupnorm_apply on caller-provided, caller-zeroed scratch).  Both run
 the same kernels, so the outputs must agree within the 1e-2 * max|ref| bound used by the other GroupNorm tests (in
-practice they differ only by fp32 atomic-add ordering).  It is done twice in a row with different data and a different
+practice they are bit-identical: the statistics are accumulated as integers).  It is done twice in a row with different data and a different
 shape, because the built-in scratch is shared between calls and still holds the previous call's sums.
 The file name sorts last so that a `-x` run has already executed every other test before this one.
 """
@@ -41,7 +41,7 @@ def _both_paths(b200sd, seed, nimg, hw, c0, c1, groups, silu):
     stream = torch.cuda.current_stream().cuda_stream
 
     # existing path: caller owns (and zeroes) the statistics scratch
-    stats = torch.zeros(nimg, groups, 2, device="cuda")
+    stats = torch.zeros(nimg, groups, lib.GN_STATS_WORDS, dtype=torch.int32, device="cuda")
     ref = torch.empty(nimg, hw, C_, device="cuda", dtype=dt)
     p = _params(lib, x0, x1, stats, gamma, beta, ref, nimg, hw, c0, c1, groups, silu, 1e-5)
     assert so.b200sd_groupnorm_stats(C.byref(p), stream) == 0, so.b200sd_last_error()
@@ -70,7 +70,7 @@ def test_noalloc_rejects_oversize_and_touches_no_allocator(cuda_lib, b200sd):
     so = lib.load()
     dt = lib.act_dtype()
     groups = 32
-    nimg = lib.GN_NOALLOC_MAX_STATS // (2 * groups) + 1   # one image too many for the built-in scratch
+    nimg = lib.GN_NOALLOC_MAX_STATS // (lib.GN_STATS_WORDS * groups) + 1   # one image too many for the built-in scratch
     x = torch.zeros(nimg, 8, 64, device="cuda", dtype=dt)
     gamma = torch.ones(64, device="cuda")
     beta = torch.zeros(64, device="cuda")
@@ -83,7 +83,7 @@ def test_noalloc_rejects_oversize_and_touches_no_allocator(cuda_lib, b200sd):
     assert "exceed the built-in scratch" in msg and str(lib.GN_NOALLOC_MAX_STATS) in msg
 
     # the largest admissible problem still runs, and device memory in use does not grow across calls
-    nimg = lib.GN_NOALLOC_MAX_STATS // (2 * groups)
+    nimg = lib.GN_NOALLOC_MAX_STATS // (lib.GN_STATS_WORDS * groups)
     x = torch.randn(nimg, 8, 64, device="cuda").to(dt)
     out = torch.empty_like(x)
     p = _params(lib, x, None, None, gamma, beta, out, nimg, 8, 64, 0, groups, False, 1e-5)
