@@ -147,14 +147,17 @@ def run_reference(args):
     f = 2 ** (len(cfg["vae"]["block_out_channels"]) - 1)
     h, w = args.height // f, args.width // f
     r = cpu_sample(cfg, unet, vae, clip, args.steps, args.warmup, args.inference_steps, h, w)
+    pb, mode = resolve_batch(args, args.gpus)
     sample = (f"1 image: {args.steps} timed + {args.warmup} warm-up CFG-paired UNet evaluations (2 samples, "
               f"{h}x{w} latent), 1 VAE decode, 1 CLIP pass of 2 sequences; images/sec = 1/({args.inference_steps}"
               f"*t_unet + t_vae + t_clip)")
     line = {
         "impl": "reference", "metric": "images/sec", "value": r["ips"], "unit": "images/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["t_unet_pair_s"] * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, cfg, 1),
+        # same unit as the CUDA arm: ms for one bench step = one whole batch of images (extrapolated from the sample)
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * pb * args.gpus / r["ips"],
+        "sample_ms_per_unet_pair": r["t_unet_pair_s"] * 1e3,
+        "higher_is_better": True, "scaling": mode, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, cfg, args.gpus),
         "cpu_baseline": {"value": r["ips"], "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
                          "sample": sample},
         "e2e": {"value": r["ips"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -164,10 +167,24 @@ def run_reference(args):
     return 0
 
 
+def resolve_batch(args, n_gpus):
+    """Per-GPU batch and scaling mode.  One GPU: BASELINE.json configs[1] (batch 8).  Several GPUs: configs[2] as
+    written - a FIXED 64-prompt batch sharded over the ranks (32 / 16 / 8 per GPU at N = 2 / 4 / 8; strong scaling) -
+    unless --weak keeps --batch prompts per GPU.  --global-batch overrides the total."""
+    if args.global_batch is None and (n_gpus == 1 or args.weak):
+        return args.batch, "weak"
+    g = args.global_batch if args.global_batch is not None else 64
+    if g % n_gpus != 0:
+        raise SystemExit(f"bench.py: global batch {g} is not divisible by {n_gpus} GPUs")
+    return g // n_gpus, "strong"
+
+
 def workload_config(args, cfg, n_gpus):
+    pb, mode = resolve_batch(args, n_gpus)
     return {"workload": f"{cfg['name']} architecture (random-init), {args.width}x{args.height}, "
-                        f"{args.inference_steps} {args.scheduler.upper()} steps, CFG {args.guidance_scale}, batch {args.batch} per GPU",
-            "global_batch": args.batch * n_gpus, "per_gpu_batch": args.batch, "scheduler": args.scheduler,
+                        f"{args.inference_steps} {args.scheduler.upper()} steps, CFG {args.guidance_scale}, "
+                        + (f"batch {pb} per GPU" if mode == "weak" else f"{pb * n_gpus}-prompt batch sharded over {n_gpus} GPU(s)"),
+            "global_batch": pb * n_gpus, "per_gpu_batch": pb, "scheduler": args.scheduler,
             "inference_steps": args.inference_steps, "guidance_scale": args.guidance_scale,
             "resolution": [args.width, args.height], "parallelism": f"dp{n_gpus} (prompt sharding, image gather)",
             "l2": "inputs larger than L2: each step streams ~2 GB of weights plus activations through a 126 MB L2; "
@@ -209,12 +226,61 @@ def profile_plan(plan, blocker=None):
     agg = {}
     for i, c in enumerate(plan.calls):
         fl, kind = flops_of_call(c)
-        a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0})
+        a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
         a["launches"] += 1
         a["ms"] += max(0.0, ev[i].elapsed_time(ev[i + 1]) - gap)
         a["flops"] += fl
+        a["bytes"] += algorithmic_bytes(c)
     agg["_event_gap_ms"] = gap
     return agg
+
+
+def algorithmic_bytes(call):
+    """Algorithmic HBM bytes of the bandwidth-bound kernels (16-bit, each element read / written once
+    per pass)."""
+    p = call.params
+    if call.name == "b200sd_groupnorm_stats":
+        return 2.0 * p.nimg * p.hw * (p.c0 + p.c1)
+    if call.name == "b200sd_groupnorm_apply":
+        return 4.0 * p.nimg * p.hw * (p.c0 + p.c1)
+    if call.name == "b200sd_layernorm":
+        return 4.0 * p.rows * p.c
+    return 0.0
+
+
+def cupti_profile(plan, replays=3):
+    """Per-kernel device durations of `replays` graph replays of `plan` from CUPTI activity records (torch.profiler:
+    hardware start / end timestamps of every kernel, no serialisation between launches, no replay - unlike ncu), matched
+    to the plan's call list by launch order.  Returns {kind: {launches, ms, flops, bytes}} averaged per replay, plus
+    the busy / span totals, or None when the profiler is unavailable."""
+    try:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(replays):
+                plan.launch()
+            torch.cuda.synchronize()
+        evs = sorted([e for e in prof.events() if e.device_type.name == "CUDA" and "emset" not in e.name.lower()
+                      and "emcpy" not in e.name.lower()], key=lambda e: e.time_range.start)
+    except Exception as exc:  # noqa: BLE001
+        return {"error": repr(exc)[:200]}
+    calls = [c for c in plan.calls if c.name != "b200sd_memset_zero"]
+    if len(evs) != replays * len(calls):
+        return {"error": f"{len(evs)} kernel records for {replays} x {len(calls)} calls"}
+    agg = {}
+    for i, e in enumerate(evs):
+        c = calls[i % len(calls)]
+        fl, kind = flops_of_call(c)
+        a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+        a["launches"] += 1
+        a["ms"] += e.device_time_total * 1e-3
+        a["flops"] += fl
+        a["bytes"] += algorithmic_bytes(c)
+    for a in agg.values():
+        for k in a:
+            a[k] /= replays
+    busy = sum(a["ms"] for a in agg.values())
+    span = (evs[-1].time_range.end - evs[0].time_range.start) * 1e-3 / replays
+    return {"kinds": agg, "busy_ms": busy, "span_ms": span}
 
 
 def run_cuda(args):
@@ -227,9 +293,7 @@ def run_cuda(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        # NCCL prints its version banner on stdout at VERSION/INFO level; stdout carries exactly one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL_DEBUG is left as the caller set it: claim_stdout() already keeps NCCL's banner off the JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     b200sd.lib.load()
     info = b200sd.lib.device_info()
@@ -237,7 +301,7 @@ def run_cuda(args):
     cfg = pipe.cfg
     f = pipe.vae_scale_factor
     h, w = args.height // f, args.width // f
-    B = args.batch
+    B, scaling = resolve_batch(args, world)
     sched = pipe.make_schedule(args.inference_steps)
     evals = sched.num_evals
     job = pipe.job(B, h, w, args.guidance_scale, True, zero_negative=pipe.is_xl)
@@ -294,6 +358,11 @@ def run_cuda(args):
     u1.record()
     torch.cuda.synchronize()
     unet_ms = u0.elapsed_time(u1) / evals
+    # per-kernel CUPTI durations of the same graph-replayed loop (rank 0), while the clock sampler still runs
+    cupti = None
+    if rank == 0 and not args.no_cupti:
+        job.reset()
+        cupti = cupti_profile(job.step_plan, replays=evals)
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end through the public call: host prompts / CPU-generator latents in, host uint8 images out
@@ -332,37 +401,62 @@ def run_cuda(args):
     vprof.pop("_event_gap_ms")
     peaks = measured_peaks()
     gm = prof["gemm"]
-    # Events between every launch serialise the step more than the graph replay does (sum of intervals > the timed
-    # step), so the kernel's time inside the TIMED region is its measured share x the event-timed graph step.
+    # Dominant kernel: gemm_conv_kernel.  Its time comes from CUPTI activity records of the graph-replayed denoise loop
+    # (hardware timestamps of every kernel of `evals` back-to-back replays, taken right after the timed region on the
+    # same warm, power-capped GPU; `cupti` below).  The CUDA-event figures are kept beside it: events between launches
+    # serialise the step more than the graph replay does, so there the kernel's time is its SHARE of the intervals x
+    # the event-timed graph step.
     raw_sum_ms = sum(a["ms"] for a in prof.values())
     gemm_share = gm["ms"] / raw_sum_ms
-    gemm_ms_in_step = gemm_share * unet_ms
+    gemm_ms_event_share = gemm_share * unet_ms
+    cupti_ok = isinstance(cupti, dict) and "kinds" in cupti and "gemm" in cupti["kinds"]
+    if cupti_ok:
+        gemm_ms_in_step = cupti["kinds"]["gemm"]["ms"]
+        method = (f"CUPTI activity records (torch.profiler) of {evals} graph replays of the denoise step, kernel "
+                  "durations matched to the plan's calls by launch order; achieved = sum 2MNK / sum of durations")
+    else:
+        gemm_ms_in_step = gemm_ms_event_share
+        method = ("share of the step from per-launch CUDA-event intervals (eager pass) x the CUDA-event-timed graph "
+                  "step of the timed region (CUPTI unavailable: %s)" % (cupti or {}).get("error"))
     achieved_tf = gm["flops"] / (gemm_ms_in_step * 1e-3) / 1e12
-    traffic = None
+    traffic, traffic_source = None, None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("gemm_conv_kernel_dram_bytes_per_launch")
+            tj = json.load(open(tpath))
+            traffic = tj.get("gemm_conv_kernel_dram_bytes_per_launch")
+            traffic_source = ("not measured by this run: ncu dram__bytes_read.sum + dram__bytes_write.sum per launch, "
+                              f"mean over one denoise step, from profiles/roofline_traffic.json ({tj.get('source', 'earlier ncu session')})")
         except Exception:
             traffic = None
     roofline = {"bound": "tensor", "kernel": "gemm_conv_kernel (tcgen05 implicit-GEMM conv/linear)",
                 "achieved": achieved_tf, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                "frac": achieved_tf / peaks["tf_sustained"], "traffic": traffic,
+                "frac": achieved_tf / peaks["tf_sustained"], "traffic": traffic, "traffic_source": traffic_source,
                 "peak_source": f"{peaks['source']} (sustained cuBLAS bf16; burst {peaks['tf_burst']})",
                 "launches_per_unet_step": gm["launches"], "flops_per_launch": gm["flops"] / gm["launches"],
                 "avg_launch_ms": gemm_ms_in_step / gm["launches"],
-                "share_of_unet_step": gemm_share,
-                "method": "share of the step from per-launch CUDA-event intervals (eager pass) x the CUDA-event-timed "
-                          "graph step of the timed region",
+                "method": method,
+                "share_of_unet_step": (gemm_ms_in_step / cupti["busy_ms"]) if cupti_ok else gemm_share,
+                "event_share_of_unet_step": gemm_share,
+                "event_share_tflops": gm["flops"] / (gemm_ms_event_share * 1e-3) / 1e12,
                 "eager_interval_avg_launch_ms": gm["ms"] / gm["launches"],
                 "eager_interval_tflops": gm["flops"] / (gm["ms"] * 1e-3) / 1e12}
+    cupti_breakdown = None
+    if cupti_ok:
+        cupti_breakdown = {"busy_ms_per_step": round(cupti["busy_ms"], 4), "span_ms_per_step": round(cupti["span_ms"], 4)}
+        for k, a in sorted(cupti["kinds"].items(), key=lambda kv: -kv[1]["ms"]):
+            cupti_breakdown[k] = {"launches": int(round(a["launches"])), "ms": round(a["ms"], 4),
+                                  "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None,
+                                  "gbs": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9, 1) if a["bytes"] else None,
+                                  "frac_of_hbm_peak": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], 3)
+                                  if a["bytes"] else None}
     step_flops = sum(a["flops"] for a in prof.values())
-    breakdown = {k: {"launches": a["launches"], "ms": round(a["ms"], 4),
-                     "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None}
-                 for k, a in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
-    vae_breakdown = {k: {"launches": a["launches"], "ms": round(a["ms"], 4),
-                         "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None}
-                     for k, a in sorted(vprof.items(), key=lambda kv: -kv[1]["ms"])}
+    def table(pr):
+        return {k: {"launches": a["launches"], "ms": round(a["ms"], 4),
+                    "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None,
+                    "gbs": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9, 1) if a["bytes"] and a["ms"] > 0 else None}
+                for k, a in sorted(pr.items(), key=lambda kv: -kv[1]["ms"])}
+    breakdown, vae_breakdown = table(prof), table(vprof)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -378,7 +472,7 @@ def run_cuda(args):
     img_tf = (evals * 2 * UNET_GF_PER_SAMPLE + VAE_GF_PER_IMAGE + 2 * CLIP_GF_PER_SEQ) / 1e3
     line = {
         "metric": "images/sec", "value": ips, "unit": "images/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": scaling,
         "vs_baseline": None, "dtype": "fp16" if b200sd.lib.act_dtype() == torch.float16 else "bf16",
         "data": "synthetic", "config": workload_config(args, cfg, world),
         "unet_ms_per_step": unet_ms,
@@ -388,7 +482,7 @@ def run_cuda(args):
         "e2e": {"value": e2e_ips, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": args.steps * job.launches(evals),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "unet_step_breakdown": breakdown, "vae_breakdown": vae_breakdown,
+        "unet_step_cupti": cupti_breakdown, "unet_step_breakdown": breakdown, "vae_breakdown": vae_breakdown,
         "breakdown_note": f"CUDA-event intervals of an eager pass minus the empty-interval gap ({event_gap_ms * 1e3:.1f} us)",
         "device": {"sm_count": info["sm_count"], "cc": list(info["cc"])},
     }
@@ -428,13 +522,18 @@ def main(argv=None):
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="sd15")
-    ap.add_argument("--batch", type=int, default=8, help="images per GPU per bench step")
+    ap.add_argument("--batch", type=int, default=8, help="images per GPU per bench step (one GPU, or with --weak)")
+    ap.add_argument("--global-batch", type=int, default=None,
+                    help="total images per bench step, sharded over the GPUs (default with --gpus N > 1: 64 = configs[2])")
+    ap.add_argument("--weak", action="store_true", help="several GPUs: keep --batch images per GPU (weak scaling)")
     ap.add_argument("--inference-steps", type=int, default=25)
     ap.add_argument("--guidance-scale", type=float, default=7.5)
     ap.add_argument("--width", type=int, default=512)
     ap.add_argument("--height", type=int, default=512)
     ap.add_argument("--scheduler", default="ddim")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cupti", action="store_true", help="skip the CUPTI per-kernel pass (roofline falls back to "
+                                                            "the CUDA-event share method)")
     args = ap.parse_args(argv)
     if args.impl == "reference":
         return run_reference(args)
