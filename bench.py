@@ -196,7 +196,8 @@ def flops_of_call(call):
     p = call.params
     if call.name == "b200sd_gemm":
         m = p.nimg * p.h * p.w_
-        return 2.0 * m * p.n * (p.ksize * p.ksize) * (p.c0 + p.c1), "gemm"
+        taps = p.kh * p.kw if p.kh else p.ksize * p.ksize  # MACs actually executed (folded up-convs: 4 x 2x2 taps)
+        return 2.0 * m * p.n * taps * (p.c0 + p.c1), "gemm"
     if call.name == "b200sd_attention":
         return 4.0 * p.batch * p.heads * p.nq * p.nk * p.d, "attention"
     return 0.0, call.name.replace("b200sd_", "")
@@ -359,10 +360,11 @@ def run_cuda(args):
     torch.cuda.synchronize()
     unet_ms = u0.elapsed_time(u1) / evals
     # per-kernel CUPTI durations of the same graph-replayed loop (rank 0), while the clock sampler still runs
-    cupti = None
+    cupti = cupti_vae = None
     if rank == 0 and not args.no_cupti:
         job.reset()
         cupti = cupti_profile(job.step_plan, replays=evals)
+        cupti_vae = cupti_profile(job.vae_plan, replays=2)
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end through the public call: host prompts / CPU-generator latents in, host uint8 images out
@@ -441,15 +443,18 @@ def run_cuda(args):
                 "event_share_tflops": gm["flops"] / (gemm_ms_event_share * 1e-3) / 1e12,
                 "eager_interval_avg_launch_ms": gm["ms"] / gm["launches"],
                 "eager_interval_tflops": gm["flops"] / (gm["ms"] * 1e-3) / 1e12}
-    cupti_breakdown = None
-    if cupti_ok:
-        cupti_breakdown = {"busy_ms_per_step": round(cupti["busy_ms"], 4), "span_ms_per_step": round(cupti["span_ms"], 4)}
-        for k, a in sorted(cupti["kinds"].items(), key=lambda kv: -kv[1]["ms"]):
-            cupti_breakdown[k] = {"launches": int(round(a["launches"])), "ms": round(a["ms"], 4),
-                                  "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None,
-                                  "gbs": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9, 1) if a["bytes"] else None,
-                                  "frac_of_hbm_peak": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], 3)
-                                  if a["bytes"] else None}
+    def cupti_table(cp):
+        if not (isinstance(cp, dict) and "kinds" in cp):
+            return cp
+        t = {"busy_ms": round(cp["busy_ms"], 4), "span_ms": round(cp["span_ms"], 4)}
+        for k, a in sorted(cp["kinds"].items(), key=lambda kv: -kv[1]["ms"]):
+            t[k] = {"launches": int(round(a["launches"])), "ms": round(a["ms"], 4),
+                    "tflops": round(a["flops"] / (a["ms"] * 1e-3) / 1e12, 1) if a["flops"] else None,
+                    "gbs": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9, 1) if a["bytes"] else None,
+                    "frac_of_hbm_peak": round(a["bytes"] / (a["ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], 3)
+                    if a["bytes"] else None}
+        return t
+    cupti_breakdown, cupti_vae_breakdown = cupti_table(cupti), cupti_table(cupti_vae)
     step_flops = sum(a["flops"] for a in prof.values())
     def table(pr):
         return {k: {"launches": a["launches"], "ms": round(a["ms"], 4),
@@ -482,7 +487,7 @@ def run_cuda(args):
         "e2e": {"value": e2e_ips, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": args.steps * job.launches(evals),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "unet_step_cupti": cupti_breakdown, "unet_step_breakdown": breakdown, "vae_breakdown": vae_breakdown,
+        "unet_step_cupti": cupti_breakdown, "vae_decode_cupti": cupti_vae_breakdown, "unet_step_breakdown": breakdown, "vae_breakdown": vae_breakdown,
         "breakdown_note": f"CUDA-event intervals of an eager pass minus the empty-interval gap ({event_gap_ms * 1e3:.1f} us)",
         "device": {"sm_count": info["sm_count"], "cc": list(info["cc"])},
     }

@@ -101,6 +101,18 @@ typedef struct {
   void* gn_stats;
   int32_t gn_groups;
   int32_t gn_rows_per_img;
+  /* Optional filter / output geometry (all 0 = the plain ksize x ksize, stride-1, dense-output layer above).
+   *   kh, kw (1..3), off_h, off_w: explicit filter window; tap (i, j) reads input pixel
+   *       (y * stride + i + off_h, x * stride + j + off_w).  W is then [n, kh*kw, c0p + c1p].
+   *   stride = 2: Downsample2D (conv 3x3, stride 2, padding 1: off = -1).  h, w_ are the OUTPUT size; the sources are
+   *       [nimg, 2h, 2w_, c] and the TMA unit reads every other pixel - no patch matrix is materialised.
+   *   out_pix_stride / out_row_stride / out_img_stride (elements, multiples of 16 bytes): the output pixels are
+   *       scattered into a larger tensor.  Upsample2D (nearest 2x + conv 3x3) runs as four 2x2 convolutions on the
+   *       LOW-resolution input (weights pre-summed per output phase (py, px); taps at off = py - 1, px - 1), each
+   *       writing its quarter of the pixels: out + ((py * 2w_) + px) * C, pixel stride 2C, row stride 4 w_ C.
+   *       No upsampled tensor exists and 16 instead of 36 MACs are spent per input pixel and channel pair. */
+  int32_t kh, kw, off_h, off_w, stride;
+  int32_t out_pix_stride, out_row_stride, out_img_stride;
 } b200sd_gemm_params;
 int b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream stream);
 
@@ -243,24 +255,6 @@ int b200sd_cfg_scheduler_step(const b200sd_sched_params* p, b200sd_stream stream
 /* ---------------------------------------------------------------------------------------------------------
  * Layout / gather helpers (bandwidth-bound).
  */
-/* nearest-neighbour 2x upsample, NHWC act16 (Upsample2D; K13). */
-typedef struct {
-  const void* x;
-  void* out;
-  int32_t nimg, h, w_, c;
-} b200sd_upsample_params;
-int b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream stream);
-
-/* 3x3 stride-2 pad-1 patch gather: out act16 [nimg, h/2, w/2, 9*cp] (cp = c rounded up to 64, pad zeroed), feeding
- * b200sd_gemm as a linear layer (Downsample2D; K2).  `out` is caller-provided scratch. */
-typedef struct {
-  const void* x;
-  void* out;
-  int32_t nimg, h, w_, c;
-} b200sd_im2col_s2_params;
-int b200sd_im2col_s2(const b200sd_im2col_s2_params* p, b200sd_stream stream);
-size_t b200sd_im2col_s2_bytes(const b200sd_im2col_s2_params* p);
-
 /* CLIP token + position embedding: out act16 [rows, c] = tok[ids[r]] + pos[r % seq]. (CLIPTextEmbeddings; a7) */
 typedef struct {
   const int32_t* ids;

@@ -55,7 +55,7 @@ static const int kActCode = 1;
 #endif
 
 static int encode_tmap_any(CUtensorMap* tm, CUtensorMapDataType dtype, const void* base, int rank, const uint64_t* dims,
-                           const uint64_t* strides_bytes, const uint32_t* box) {
+                           const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides) {
   if (g_encode == nullptr) {
     std::lock_guard<std::mutex> lk(g_mu);
     if (g_encode == nullptr) {
@@ -74,7 +74,7 @@ static int encode_tmap_any(CUtensorMap* tm, CUtensorMapDataType dtype, const voi
   for (int i = 0; i < rank; ++i) {
     gdims[i] = dims[i];
     gbox[i] = box[i];
-    estr[i] = 1;
+    estr[i] = elem_strides ? elem_strides[i] : 1;
     if (i + 1 < rank) gstr[i] = strides_bytes[i];
   }
   for (int i = 0; i + 1 < rank; ++i)
@@ -92,12 +92,12 @@ static int encode_tmap_any(CUtensorMap* tm, CUtensorMapDataType dtype, const voi
 }
 
 int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                    const uint32_t* box) {
-  return encode_tmap_any(tm, kTmaDtype, base, rank, dims, strides_bytes, box);
+                    const uint32_t* box, const uint32_t* elem_strides) {
+  return encode_tmap_any(tm, kTmaDtype, base, rank, dims, strides_bytes, box, elem_strides);
 }
 int encode_tmap_f32(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box) {
-  return encode_tmap_any(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_bytes, box);
+  return encode_tmap_any(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_bytes, box, nullptr);
 }
 
 }  // namespace b200sd
@@ -126,8 +126,7 @@ extern "C" int b200sd_struct_sizes(int32_t* out, int32_t max_entries) {
       (int32_t)sizeof(b200sd_gemm_params),       (int32_t)sizeof(b200sd_attn_params),
       (int32_t)sizeof(b200sd_groupnorm_params),  (int32_t)sizeof(b200sd_layernorm_params),
       (int32_t)sizeof(b200sd_prep_params),       (int32_t)sizeof(b200sd_temb_params),
-      (int32_t)sizeof(b200sd_sched_params),      (int32_t)sizeof(b200sd_upsample_params),
-      (int32_t)sizeof(b200sd_im2col_s2_params),  (int32_t)sizeof(b200sd_embed_params),
+      (int32_t)sizeof(b200sd_sched_params),      (int32_t)sizeof(b200sd_embed_params),
       (int32_t)sizeof(b200sd_denorm_params),     (int32_t)sizeof(b200sd_latent_cast_params),
       (int32_t)sizeof(b200sd_softmax_params),     (int32_t)sizeof(b200sd_memset_params),
   };

@@ -1,6 +1,7 @@
 // Small fused, bandwidth-bound kernels around the denoise loop: UNet-input preparation, sinusoidal timestep
-// embedding, classifier-free-guidance + scheduler step (DDIM / Euler / PNDM-PLMS), nearest-2x upsample, stride-2
-// patch gather, CLIP embedding lookup, image denormalisation.  SURVEY §2.1 K2, K10-K13, K17.
+// embedding, classifier-free-guidance + scheduler step (DDIM / Euler / PNDM-PLMS), CLIP embedding lookup, image
+// denormalisation.  SURVEY §2.1 K10-K12, K17.  (K13 nearest-2x upsample and K2 stride-2 conv live inside the GEMM
+// kernel's addressing - gemm.cu - and have no kernels of their own.)
 //
 // The timestep-dependent kernels read a device-resident step table indexed by a device step counter, so a single
 // captured CUDA graph of "one denoise step" is replayed for every step with no host round trip.
@@ -135,43 +136,6 @@ __global__ void cfg_sched_kernel(const float* __restrict__ eps, float4* __restri
   }
 }
 
-__global__ void upsample2x_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int nimg, int h, int w,
-                                  int octs) {
-  const size_t total = static_cast<size_t>(nimg) * (2 * h) * (2 * w) * octs;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int oct = static_cast<int>(i % octs);
-    size_t r = i / octs;
-    const int ox = static_cast<int>(r % (2 * w));
-    r /= (2 * w);
-    const int oy = static_cast<int>(r % (2 * h));
-    const int n = static_cast<int>(r / (2 * h));
-    out[i] = __ldg(x + ((static_cast<size_t>(n) * h + (oy >> 1)) * w + (ox >> 1)) * octs + oct);
-  }
-}
-
-__global__ void im2col_s2_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int nimg, int h, int w, int octs,
-                                 int octs_p) {
-  const int ho = h >> 1, wo = w >> 1;
-  const size_t total = static_cast<size_t>(nimg) * ho * wo * 9 * octs_p;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int oct = static_cast<int>(i % octs_p);
-    size_t r = i / octs_p;
-    const int tap = static_cast<int>(r % 9);
-    r /= 9;
-    const int ox = static_cast<int>(r % wo);
-    r /= wo;
-    const int oy = static_cast<int>(r % ho);
-    const int n = static_cast<int>(r / ho);
-    const int iy = 2 * oy + tap / 3 - 1, ix = 2 * ox + tap % 3 - 1;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (oct < octs && iy >= 0 && iy < h && ix >= 0 && ix < w)
-      v = __ldg(x + ((static_cast<size_t>(n) * h + iy) * w + ix) * octs + oct);
-    out[i] = v;
-  }
-}
-
 __global__ void clip_embed_kernel(const int* __restrict__ ids, const act_t* __restrict__ tok,
                                   const act_t* __restrict__ pos, act_t* __restrict__ out, int rows, int seq, int c,
                                   int vocab) {
@@ -253,38 +217,6 @@ extern "C" int b200sd_cfg_scheduler_step(const b200sd_sched_params* p, b200sd_st
       p->eps, reinterpret_cast<float4*>(p->latents), reinterpret_cast<float4*>(p->history),
       reinterpret_cast<float4*>(p->cur_sample), p->step_table, p->step_counter, npix, p->ld_eps, p->cfg,
       p->guidance_scale);
-  B200SD_CUDA_CHECK(cudaGetLastError());
-  return B200SD_OK;
-}
-
-extern "C" int b200sd_upsample2x(const b200sd_upsample_params* p, b200sd_stream stream_) {
-  B200SD_REQUIRE(p && p->x && p->out && p->nimg > 0 && p->h > 0 && p->w_ > 0 && p->c > 0 && (p->c % 8) == 0,
-                 B200SD_ERR_BAD_ARGUMENT, "upsample2x: bad arguments (c must be a multiple of 8)");
-  const size_t total = static_cast<size_t>(p->nimg) * p->h * p->w_ * 4 * (p->c / 8);
-  const int grid = static_cast<int>(std::min<size_t>((total + kEwThreads - 1) / kEwThreads, 148 * 16));
-  upsample2x_kernel<<<grid, kEwThreads, 0, EW_STREAM>>>(reinterpret_cast<const uint4*>(p->x),
-                                                         reinterpret_cast<uint4*>(p->out), p->nimg, p->h, p->w_,
-                                                         p->c / 8);
-  B200SD_CUDA_CHECK(cudaGetLastError());
-  return B200SD_OK;
-}
-
-extern "C" size_t b200sd_im2col_s2_bytes(const b200sd_im2col_s2_params* p) {
-  if (!p || p->nimg <= 0 || p->h <= 0 || p->w_ <= 0 || p->c <= 0) return 0;
-  const size_t cp = static_cast<size_t>((p->c + 63) / 64) * 64;
-  return static_cast<size_t>(p->nimg) * (p->h / 2) * (p->w_ / 2) * 9 * cp * 2;
-}
-
-extern "C" int b200sd_im2col_s2(const b200sd_im2col_s2_params* p, b200sd_stream stream_) {
-  B200SD_REQUIRE(p && p->x && p->out && p->nimg > 0 && p->h > 1 && p->w_ > 1 && p->c > 0 && (p->c % 8) == 0 &&
-                     (p->h % 2) == 0 && (p->w_ % 2) == 0,
-                 B200SD_ERR_BAD_ARGUMENT, "im2col_s2: bad arguments (even h/w, c multiple of 8)");
-  const int octs = p->c / 8, octs_p = ((p->c + 63) / 64) * 8;
-  const size_t total = static_cast<size_t>(p->nimg) * (p->h / 2) * (p->w_ / 2) * 9 * octs_p;
-  const int grid = static_cast<int>(std::min<size_t>((total + kEwThreads - 1) / kEwThreads, 148 * 16));
-  im2col_s2_kernel<<<grid, kEwThreads, 0, EW_STREAM>>>(reinterpret_cast<const uint4*>(p->x),
-                                                        reinterpret_cast<uint4*>(p->out), p->nimg, p->h, p->w_, octs,
-                                                        octs_p);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }

@@ -74,7 +74,9 @@ struct alignas(64) GemmDev {
   int bw, bh, bn;
   int tiles_w, tiles_h, tiles_n, tiles_m, tiles_ncol;
   FastDiv div_munits, div_tw, div_twth;  // tile -> column tile; M tile -> (tw, th, tn)
-  int ksize, pad, taps;
+  int kw_taps, taps;     // filter taps along w; total taps (kh * kw)
+  int off_h, off_w;      // input pixel of tap (0, 0) relative to output pixel * stride (-pad for a centred filter)
+  int stride;            // 1, or 2: the A tensor map then walks every other input pixel (element strides)
   int cblk0, cblk1;
   int num_stages;
   int res_bufs;  // staging tiles per epilogue warpgroup: 2 = the residual of the NEXT group is prefetched
@@ -194,11 +196,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         const int ch = (first ? cb : cb - p.cblk0) * kBlockK;
         if (kPair) {
           if (rank == 0) mbar_arrive_expect_tx_w(leader, bar, 2 * stage_bytes);  // both CTAs' loads land on the leader's barrier
-          tma_load_4d_pair_w(leader, sa, tmA, bar, ch, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+          tma_load_4d_pair_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
           tma_load_2d_pair_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
         } else {
           mbar_arrive_expect_tx_w(leader, bar, stage_bytes);
-          tma_load_4d_w(leader, sa, tmA, bar, ch, w0 + kw - p.pad, h0 + kh - p.pad, n0);
+          tma_load_4d_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
           if (p.wide) {  // box = BN / 2 rows
             tma_load_2d_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
             tma_load_2d_w(leader, sa + kABytes + b_bytes / 2, &p.tmB, bar, kb * kBlockK, bcol + p.BN / 2);
@@ -208,7 +210,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         }
         if (++cb == cblk) {
           cb = 0;
-          if (++kw == p.ksize) {
+          if (++kw == p.kw_taps) {
             kw = 0;
             ++kh;
           }
@@ -616,6 +618,16 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   const b200sd_gemm_params& h = *hp;
   B200SD_REQUIRE(h.a0 && h.w && h.out, B200SD_ERR_BAD_ARGUMENT, "gemm: a0/w/out must be non-NULL");
   B200SD_REQUIRE(h.ksize == 1 || h.ksize == 3, B200SD_ERR_BAD_SHAPE, "gemm: ksize must be 1 or 3 (got %d)", h.ksize);
+  // filter geometry: ksize x ksize centred (default) or an explicit kh x kw window whose tap (0, 0) sits at input
+  // pixel (out * stride + off_h, out * stride + off_w)
+  const bool custom = (h.kh != 0 || h.kw != 0);
+  const int f_kh = custom ? h.kh : h.ksize, f_kw = custom ? h.kw : h.ksize;
+  const int f_offh = custom ? h.off_h : -(h.ksize / 2), f_offw = custom ? h.off_w : -(h.ksize / 2);
+  const int f_stride = h.stride == 0 ? 1 : h.stride;
+  B200SD_REQUIRE(f_kh >= 1 && f_kh <= 3 && f_kw >= 1 && f_kw <= 3, B200SD_ERR_BAD_SHAPE,
+                 "gemm: filter window %d x %d unsupported (1..3)", f_kh, f_kw);
+  B200SD_REQUIRE(f_stride == 1 || f_stride == 2, B200SD_ERR_BAD_SHAPE, "gemm: stride must be 1 or 2 (got %d)", h.stride);
+  B200SD_REQUIRE(f_offh >= -3 && f_offh <= 3 && f_offw >= -3 && f_offw <= 3, B200SD_ERR_BAD_SHAPE, "gemm: bad tap origin");
   B200SD_REQUIRE(h.nimg > 0 && h.h > 0 && h.w_ > 0 && h.c0 > 0 && h.n > 0 && h.c1 >= 0, B200SD_ERR_BAD_SHAPE,
                  "gemm: non-positive dimension");
   B200SD_REQUIRE((h.c0 % 8) == 0 && (h.c1 % 8) == 0 && (h.ld0 % 8) == 0 && (h.c1 == 0 || (h.ld1 % 8) == 0),
@@ -657,7 +669,7 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   int bn_tile = h.bn_hint % 1000;
   const int force = h.bn_hint / 1000;
   const TilePlan plan = pick_tiles(d.tiles_m, h.n, di.sm_count, gran,
-                                   h.ksize * h.ksize * (ceil_div(h.c0, kBlockK) + ceil_div(h.c1, kBlockK)));
+                                   f_kh * f_kw * (ceil_div(h.c0, kBlockK) + ceil_div(h.c1, kBlockK)));
   d.pair = plan.pair;
   if (bn_tile == 0) bn_tile = plan.bn;
   if (force == 1) d.pair = 0;
@@ -677,9 +689,11 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.nimg = h.nimg;
   d.H = h.h;
   d.W = h.w_;
-  d.ksize = h.ksize;
-  d.pad = h.ksize / 2;
-  d.taps = h.ksize * h.ksize;
+  d.kw_taps = f_kw;
+  d.taps = f_kh * f_kw;
+  d.off_h = f_offh;
+  d.off_w = f_offw;
+  d.stride = f_stride;
   d.cblk0 = ceil_div(h.c0, kBlockK);
   d.cblk1 = ceil_div(h.c1, kBlockK);
   const uint32_t stage_bytes = kABytes + (d.pair ? d.BN / 2 : d.BN) * kBlockK * 2;
@@ -716,19 +730,40 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   d.act = h.act;
   d.alpha = h.alpha;
 
-  const uint32_t boxA[4] = {kBlockK, static_cast<uint32_t>(d.bw), static_cast<uint32_t>(d.bh),
+  // A: the input feature map [nimg, h * stride, w * stride, c]; a stride-2 box spans 2 bw x 2 bh input pixels and the
+  // TMA unit picks every other one (element strides), so the tile in shared memory is the same 128 x 64 as for stride 1
+  const uint32_t sA = static_cast<uint32_t>(f_stride);
+  const uint32_t boxA[4] = {kBlockK, static_cast<uint32_t>(d.bw) * sA, static_cast<uint32_t>(d.bh) * sA,
                             static_cast<uint32_t>(d.bn)};
-  auto nhwc_map = [&](CUtensorMap* tm, const void* ptr, int c, int ld, int elem_bytes, const uint32_t* box,
-                      bool as_f32) -> int {
+  const uint32_t estrA[4] = {1, sA, sA, 1};
+  auto in_map = [&](CUtensorMap* tm, const void* ptr, int c, int ld) -> int {
+    const uint64_t dims[4] = {static_cast<uint64_t>(c), static_cast<uint64_t>(h.w_) * sA, static_cast<uint64_t>(h.h) * sA,
+                              static_cast<uint64_t>(h.nimg)};
+    const uint64_t pix = static_cast<uint64_t>(ld) * 2;
+    const uint64_t st[3] = {pix, pix * dims[1], pix * dims[1] * dims[2]};
+    return encode_tmap_act(tm, ptr, 4, dims, st, boxA, f_stride > 1 ? estrA : nullptr);
+  };
+  // O / residual: [nimg, h, w, n_out] with pixel stride ld - or explicit pixel / row / image strides (elements) when the
+  // output pixels are interleaved into a larger tensor (the four phases of a folded 2x upsample + conv)
+  auto out_map = [&](CUtensorMap* tm, const void* ptr, int c, int ld, int elem_bytes, const uint32_t* box,
+                     bool as_f32, bool strided) -> int {
     const uint64_t dims[4] = {static_cast<uint64_t>(c), static_cast<uint64_t>(h.w_), static_cast<uint64_t>(h.h),
                               static_cast<uint64_t>(h.nimg)};
-    const uint64_t pix = static_cast<uint64_t>(ld) * elem_bytes;
-    const uint64_t st[3] = {pix, pix * h.w_, pix * h.w_ * h.h};
+    const uint64_t pix = static_cast<uint64_t>(strided ? h.out_pix_stride : ld) * elem_bytes;
+    const uint64_t row = strided ? static_cast<uint64_t>(h.out_row_stride) * elem_bytes : pix * h.w_;
+    const uint64_t img = strided ? static_cast<uint64_t>(h.out_img_stride) * elem_bytes : row * h.h;
+    const uint64_t st[3] = {pix, row, img};
     return as_f32 ? encode_tmap_f32(tm, ptr, 4, dims, st, box) : encode_tmap_act(tm, ptr, 4, dims, st, box);
   };
-  if (int e = nhwc_map(&d.tmA0, h.a0, h.c0, h.ld0, 2, boxA, false)) return e;
+  const bool out_strided = h.out_pix_stride != 0;
+  if (out_strided)
+    B200SD_REQUIRE(h.out_pix_stride >= h.ldc && h.out_row_stride >= h.out_pix_stride && h.out_img_stride >= h.out_row_stride &&
+                       (h.out_pix_stride * esz) % 16 == 0 && (h.out_row_stride * esz) % 16 == 0 &&
+                       (h.out_img_stride * esz) % 16 == 0 && !res,
+                   B200SD_ERR_BAD_ARGUMENT, "gemm: bad output strides (16-byte multiples, pix <= row <= img, no residual)");
+  if (int e = in_map(&d.tmA0, h.a0, h.c0, h.ld0)) return e;
   if (h.c1 > 0)
-    if (int e = nhwc_map(&d.tmA1, h.a1, h.c1, h.ld1, 2, boxA, false)) return e;
+    if (int e = in_map(&d.tmA1, h.a1, h.c1, h.ld1)) return e;
   {
     const uint64_t ktot = static_cast<uint64_t>(d.taps) * (d.cblk0 + d.cblk1) * kBlockK;
     const uint64_t dims[2] = {ktot, static_cast<uint64_t>(h.n)};
@@ -739,9 +774,9 @@ extern "C" int b200sd_gemm(const b200sd_gemm_params* hp, b200sd_stream stream_) 
   {
     const uint32_t boxO[4] = {static_cast<uint32_t>(f32 ? 32 : 64), static_cast<uint32_t>(d.bw),
                               static_cast<uint32_t>(d.bh), static_cast<uint32_t>(d.bn)};
-    if (int e = nhwc_map(&d.tmO, h.out, n_out, h.ldc, esz, boxO, f32)) return e;
+    if (int e = out_map(&d.tmO, h.out, n_out, h.ldc, esz, boxO, f32, out_strided)) return e;
     if (res)
-      if (int e = nhwc_map(&d.tmR, h.residual, n_out, h.ldr, 2, boxO, false)) return e;
+      if (int e = out_map(&d.tmR, h.residual, n_out, h.ldr, 2, boxO, false, false)) return e;
   }
 
   const int smem_bytes = d.num_stages * stage_bytes + d.res_bufs * kEpiStageBytes + 1024;

@@ -37,8 +37,10 @@ int get_device_info(DeviceInfo* out);
 
 // cuTensorMapEncodeTiled via the runtime's driver entry point (no -lcuda link dependency).
 // dims/strides innermost first; strides[i] = byte stride of dim i+1 (rank-1 entries); act_t elements; 128B swizzle.
+// elem_strides (optional, per dim): traversal step inside the box - the TMA unit then loads every elem_strides[i]-th
+// element, ceil(box[i] / elem_strides[i]) of them (the stride-2 convolutions read every other pixel this way).
 int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                     const uint32_t* box);
+                     const uint32_t* box, const uint32_t* elem_strides = nullptr);
 // same, fp32 elements (epilogue output maps)
 int encode_tmap_f32(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box);

@@ -27,7 +27,8 @@ class GemmParams(C.Structure):
                 ("nimg", i32), ("h", i32), ("w_", i32), ("c0", i32), ("c1", i32), ("ld0", i32), ("ld1", i32),
                 ("n", i32), ("ksize", i32), ("ldc", i32), ("ldr", i32), ("ld_rowbias", i32), ("act", i32),
                 ("out_dtype", i32), ("bn_hint", i32), ("alpha", f32), ("gn_stats", vp), ("gn_groups", i32),
-                ("gn_rows_per_img", i32)]
+                ("gn_rows_per_img", i32), ("kh", i32), ("kw", i32), ("off_h", i32), ("off_w", i32), ("stride", i32),
+                ("out_pix_stride", i32), ("out_row_stride", i32), ("out_img_stride", i32)]
 
 
 class AttnParams(C.Structure):
@@ -60,14 +61,6 @@ class SchedParams(C.Structure):
                 ("guidance_scale", f32)]
 
 
-class UpsampleParams(C.Structure):
-    _fields_ = [("x", vp), ("out", vp), ("nimg", i32), ("h", i32), ("w_", i32), ("c", i32)]
-
-
-class Im2colS2Params(C.Structure):
-    _fields_ = [("x", vp), ("out", vp), ("nimg", i32), ("h", i32), ("w_", i32), ("c", i32)]
-
-
 class EmbedParams(C.Structure):
     _fields_ = [("ids", vp), ("tok", vp), ("pos", vp), ("out", vp),
                 ("rows", i32), ("seq", i32), ("c", i32), ("vocab", i32)]
@@ -91,7 +84,7 @@ class MemsetParams(C.Structure):
 
 # declaration order of include/b200sd.h (b200sd_struct_sizes reports sizeof() in this order)
 STRUCTS = [GemmParams, AttnParams, GroupNormParams, LayerNormParams, PrepParams, TembParams, SchedParams,
-           UpsampleParams, Im2colS2Params, EmbedParams, DenormParams, LatentCastParams, SoftmaxParams, MemsetParams]
+           EmbedParams, DenormParams, LatentCastParams, SoftmaxParams, MemsetParams]
 
 # entry point -> params struct (None = special signature); must list every symbol include/b200sd.h declares
 ENTRY_POINTS = {
@@ -110,9 +103,6 @@ ENTRY_POINTS = {
     "b200sd_prep_unet_input": PrepParams,
     "b200sd_timestep_embedding": TembParams,
     "b200sd_cfg_scheduler_step": SchedParams,
-    "b200sd_upsample2x": UpsampleParams,
-    "b200sd_im2col_s2": Im2colS2Params,
-    "b200sd_im2col_s2_bytes": None,
     "b200sd_clip_embed": EmbedParams,
     "b200sd_denorm_u8": DenormParams,
     "b200sd_latent_to_act": LatentCastParams,
@@ -150,8 +140,6 @@ def load():
         fn = getattr(lib, name)
         fn.argtypes = [C.POINTER(st), vp]
         fn.restype = C.c_int
-    lib.b200sd_im2col_s2_bytes.argtypes = [C.POINTER(Im2colS2Params)]
-    lib.b200sd_im2col_s2_bytes.restype = C.c_size_t
     lib.b200sd_groupnorm_workspace_bytes.argtypes = [C.POINTER(GroupNormParams)]
     lib.b200sd_groupnorm_workspace_bytes.restype = C.c_size_t
     _lib = lib

@@ -218,10 +218,9 @@ class UNetEngine:
                     y = y2
                 x = y
             if i < len(ch) - 1:
-                up = bld.upsample2x(x)
+                up = bld.upsample_conv(W, f"up_blocks.{i}.upsamplers.0.conv", x, rch[i])
                 bld.free(x)
-                x = bld.conv(W, f"up_blocks.{i}.upsamplers.0.conv", up, rch[i], 3)
-                bld.free(up)
+                x = up
         # --- head
         gn = bld.groupnorm(W, "conv_norm_out", x, g, eps, silu=True)
         bld.free(x)

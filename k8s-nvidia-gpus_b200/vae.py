@@ -83,10 +83,9 @@ class VAEDecoderEngine:
                 bld.free(x)
                 x = y
             if i < len(ch) - 1:
-                up = bld.upsample2x(x)
+                up = bld.upsample_conv(W, f"decoder.up_blocks.{i}.upsamplers.0.conv", x, rch[i], gn_groups=g)
                 bld.free(x)
-                x = bld.conv(W, f"decoder.up_blocks.{i}.upsamplers.0.conv", up, rch[i], 3, gn_groups=g)
-                bld.free(up)
+                x = up
         gn = bld.groupnorm(W, "decoder.conv_norm_out", x, g, 1e-6, silu=True)
         bld.free(x)
         H, Wd = gn.h, gn.w

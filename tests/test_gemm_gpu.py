@@ -240,6 +240,56 @@ def test_fused_groupnorm_statistics(cuda_lib, b200sd, nimg, H, W, cin, cout, gro
     assert err <= 2e-4 * scale + 1e-2
 
 
+@pytest.mark.parametrize("nimg,H,W,cin,cout", [(2, 16, 16, 32, 64), (3, 64, 64, 320, 320), (2, 8, 8, 1280, 1280),
+                                               (1, 24, 40, 64, 96)])
+def test_conv3x3_stride2_tma_element_strides(cuda_lib, b200sd, nimg, H, W, cin, cout):
+    """Downsample2D (conv 3x3, stride 2, padding 1) as an implicit GEMM: the A tiles are fetched with TMA element
+    strides (every other input pixel), no patch matrix - against F.conv2d(stride=2, padding=1)."""
+    torch.manual_seed(21)
+    ops = b200sd.ops
+    x = _rand(nimg, H, W, cin)
+    w = _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+    bias = torch.randn(cout, device="cuda")
+    out = torch.full((nimg, H // 2, W // 2, cout), float("nan"), device="cuda", dtype=ACT())
+    ops.gemm(x, ops.pack_conv_weight(w.float().cpu()).cuda(), out, nimg=nimg, h=H // 2, w_=W // 2, c0=cin, n=cout,
+             ksize=3, kh=3, kw=3, off_h=-1, off_w=-1, stride=2, bias=bias)(ops.current_stream())
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, stride=2, padding=1).permute(0, 2, 3, 1)
+    _report("conv3x3 stride 2", out, ref, 1e-2)
+
+
+@pytest.mark.parametrize("nimg,H,W,cin,cout,groups", [(2, 8, 8, 64, 64, 0), (2, 32, 32, 320, 640, 32),
+                                                      (1, 12, 20, 128, 128, 0), (3, 16, 16, 512, 256, 32)])
+def test_upsample_conv_folded_into_four_phase_convs(cuda_lib, b200sd, nimg, H, W, cin, cout, groups):
+    """Upsample2D (nearest 2x, then conv 3x3 pad 1) as four 2x2 convolutions on the low-resolution input with
+    pre-summed weights, each writing one output phase through a strided output tensor map - against
+    F.conv2d(F.interpolate(x, scale_factor=2, mode='nearest')).  With fused GroupNorm statistics of the full output."""
+    torch.manual_seed(22)
+    ops = b200sd.ops
+    x = _rand(nimg, H, W, cin)
+    w = _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+    bias = torch.randn(cout, device="cuda")
+    out = torch.full((nimg, 2 * H, 2 * W, cout), float("nan"), device="cuda", dtype=ACT())
+    w4 = [t.cuda() for t in ops.pack_upconv_weights(w.float().cpu())]
+    stats = ops.groupnorm_stats_buffer(nimg, groups) if groups else None
+    strides = (2 * cout, 4 * W * cout, 4 * H * W * cout)
+    s = ops.current_stream()
+    for py in (0, 1):
+        for px in (0, 1):
+            ops.gemm(x, w4[py * 2 + px], out[:, py::2, px::2, :], nimg=nimg, h=H, w_=W, c0=cin, n=cout, ksize=1, kh=2,
+                     kw=2, off_h=py - 1, off_w=px - 1, bias=bias, ldc=cout, out_strides=strides, gn_stats=stats,
+                     gn_groups=groups)(s)
+    torch.cuda.synchronize()
+    up = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest")
+    ref = F.conv2d(up, w.float(), bias, padding=1).permute(0, 2, 3, 1)
+    _report("upsample + conv3x3 (folded)", out, ref, 1e-2)
+    if groups:
+        g = out.float().reshape(nimg, 4 * H * W, groups, cout // groups)
+        want = torch.stack([g.sum(dim=(1, 3)), (g * g).sum(dim=(1, 3))], dim=-1).double()
+        got = ops.groupnorm_stats_values(stats)
+        assert (got - want).abs().max().item() <= 2e-4 * want.abs().max().item() + 1e-2
+
+
 def test_gemm_rejects_bad_arguments(cuda_lib, b200sd):
     ops = b200sd.ops
     x = _rand(64, 60)

@@ -212,28 +212,6 @@ def test_layout_kernels(cuda_lib, b200sd):
     torch.manual_seed(0)
     ops = b200sd.ops
     s = ops.current_stream()
-    x = _rand(2, 6, 10, 64)
-    up = torch.empty(2, 12, 20, 64, device="cuda", dtype=ACT())
-    ops.upsample2x(x, up, nimg=2, h=6, w_=10, c=64)(s)
-    ref = F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest").permute(0, 2, 3, 1)
-    torch.cuda.synchronize()
-    assert torch.equal(up.float(), ref)
-
-    # stride-2 3x3 conv through im2col + linear gemm
-    nimg, H, W, c, cout = 2, 16, 16, 32, 64
-    x = _rand(nimg, H, W, c)
-    w = _rand(cout, c, 3, 3, scale=(9 * c) ** -0.5)
-    nbytes = ops.im2col_s2_bytes(nimg=nimg, h=H, w_=W, c=c)
-    assert nbytes == nimg * 8 * 8 * 9 * 64 * 2
-    col = torch.empty(nbytes // 2, device="cuda", dtype=ACT())
-    ops.im2col_s2(x, col, nimg=nimg, h=H, w_=W, c=c)(s)
-    out = torch.empty(nimg, 8, 8, cout, device="cuda", dtype=torch.float32)
-    ops.gemm(col, ops.pack_conv_weight(w.float().cpu()).cuda().view(cout, 1, -1), out, nimg=1, h=1, w_=nimg * 64,
-             c0=9 * 64, n=cout)(s)
-    torch.cuda.synchronize()
-    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), stride=2, padding=1).permute(0, 2, 3, 1)
-    _report("conv s2 via im2col", out, ref, 2e-3)
-
     ids = torch.randint(0, 1000, (2 * 77,), device="cuda", dtype=torch.int32)
     tok, pos = _rand(1000, 64), _rand(77, 64)
     emb = torch.empty(2 * 77, 64, device="cuda", dtype=ACT())

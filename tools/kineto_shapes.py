@@ -35,8 +35,10 @@ agg = collections.OrderedDict()
 for e, c in zip(evs, calls):
     p = c.params
     if c.name == "b200sd_gemm":
-        key = f"gemm M={p.nimg * p.h * p.w_} K={p.ksize ** 2 * (p.c0 + p.c1)} N={p.n} k{p.ksize} act{p.act}{' res' if p.residual else ''}"
-        fl = 2.0 * p.nimg * p.h * p.w_ * p.n * p.ksize ** 2 * (p.c0 + p.c1)
+        taps = p.kh * p.kw if p.kh else p.ksize ** 2
+        key = (f"gemm M={p.nimg * p.h * p.w_} K={taps * (p.c0 + p.c1)} N={p.n} k{p.kh or p.ksize}x{p.kw or p.ksize}"
+               f"{'s2' if p.stride == 2 else ''} act{p.act}{' res' if p.residual else ''}{' gn' if p.gn_stats else ''}")
+        fl = 2.0 * p.nimg * p.h * p.w_ * p.n * taps * (p.c0 + p.c1)
     elif c.name == "b200sd_attention":
         key = f"attn nq={p.nq} nk={p.nk} d={p.d}"
         fl = 4.0 * p.batch * p.heads * p.nq * p.nk * p.d
