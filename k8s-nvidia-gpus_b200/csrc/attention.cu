@@ -23,9 +23,11 @@
 //                       partials: O = (f_e O_e + f_o O_o) / (f_e l_e + f_o l_o), f_x = 2^(ref_x - max ref).
 //   TMEM (512 columns): d <= 64: 2 query tiles x (2 S buffers x 64 + 2 accumulators x 64); larger head dims: 1 query
 //   tile x (2 x 64 + 2 x 192).
-//   Row sums: when the head dim leaves a spare UMMA column (d = 40 -> N = 48) column d of every V tile is set to
-//   1.0 after the TMA lands, so the tensor pipe accumulates sum_j P_ij in fp32 as column d of O for free (and it is
-//   rescaled together with O); otherwise the sum is accumulated in registers.
+//   Row sums are kept in registers (64 FADDs per tile and thread).  Both ways of getting them from the tensor pipe
+//   were measured slower on the 4096-token d = 40 call: a ones column written into every V tile (0.794 ms - the
+//   softmax warps then wait for V to land) and an extra P x ONES product with N = 16 (0.843 ms) against 0.735 ms -
+//   every tcgen05.mma re-reads its 128 x 16 A slice (4 KB) from shared memory whatever N is, and the shared-memory
+//   port (operand reads + P stores + TMA writes) is as loaded as the MUFU pipe in this kernel.
 #include "common.cuh"
 #include "host.cuh"
 
@@ -62,7 +64,6 @@ struct alignas(64) AttnDev {
   int qtiles;     // query tiles per CTA (1 or 2)
   int o_col;      // first TMEM column of the O accumulators
   int o_stride;   // TMEM column stride between accumulators (two per query tile: even / odd KV tiles)
-  int sum_col;    // >= 0: column of O that accumulates the row sums (ones column in V); -1: register sums
   int causal;
   float scale_log2;
 };
@@ -87,7 +88,6 @@ __device__ __forceinline__ void fma2(float a0, float a1, float s, float c, float
       : "f"(a0), "f"(a1), "f"(s), "f"(c));
 }
 
-template <bool kOnes>
 __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_constant__ AttnDev p) {
   extern __shared__ uint8_t smem_raw[];
   // all mbarriers in one block: one base address, every barrier a constant byte offset from it
@@ -256,11 +256,8 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       const uint32_t sPt = sP + (2 * t + wg) * kQAtom + r * 128;
       const uint32_t swz = static_cast<uint32_t>(r & 7) << 4;
       const int pair_bar = 1 + t * 4 + qd;  // named barrier shared by the two warps that own the same 32 rows
-      constexpr bool ones_col = kOnes;
       float mb = 0.f;     // my reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
       float l_run = 0.f;  // my row sum (register-sum variant)
-      int vst = wg;       // V ring position of my next tile (ones-column writer); p.stages >= 2
-      uint32_t vph = 0;
       for (int j = wg; j < T; j += 2) {
         const int col0 = j * kBKV;
         int limit = p.nk - col0;  // valid columns: [0, limit)
@@ -331,7 +328,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
             fma2(__uint_as_float(q < 4 ? sa[i] : sb[i]), __uint_as_float(q < 4 ? sa[i + 1] : sb[i + 1]), p.scale_log2,
                  -mb, x0, x1);
             const float p0 = ex2f(x0), p1 = ex2f(x1);
-            if (!ones_col) psum += p0 + p1;
+            psum += p0 + p1;
             w[q * 4 + e] = pack_act2(p0, p1);
           }
         }
@@ -343,22 +340,6 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
                        "r"(w[q * 4]), "r"(w[q * 4 + 1]), "r"(w[q * 4 + 2]), "r"(w[q * 4 + 3])
                        : "memory");
         l_run += psum;
-        if (ones_col) {
-          // V(j) has landed: set column `sum_col` of its 64 kv rows to 1.0 so O[:, sum_col] accumulates the row sums
-          mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
-          if (r < kBKV) {
-            const int scol = p.sum_col;
-            const uint32_t va = sV + vst * kv_bytes + (scol >> 6) * kKVAtom + r * 128 +
-                                (((((scol & 63) >> 3)) ^ (r & 7)) << 4) + (scol & 7) * 2;
-            const act_t one = to_act(1.f);
-            asm volatile("st.shared.b16 [%0], %1;" ::"r"(va), "h"(*reinterpret_cast<const uint16_t*>(&one)) : "memory");
-          }
-          vst += 2;
-          if (vst >= p.stages) {
-            vst -= p.stages;
-            vph ^= 1u;
-          }
-        }
         fence_proxy_async_smem();
         tc_fence_before();
         mbar_arrive((bar0 + 8 * (kBarPFull + 2 * (t) + (wg))));
@@ -382,22 +363,6 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       float l_e = wg ? l_o : l_run, l_d = wg ? l_run : l_o;
       const float mref = has_odd ? fmaxf(mb_e, mb_d) : mb_e;
       const float f_e = ex2f(mb_e - mref), f_d = has_odd ? ex2f(mb_d - mref) : 0.f;
-      if (ones_col) {
-        uint32_t o[16];
-        tmem_ld16(tO0 + (p.sum_col & ~15), o);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-          if (i == (p.sum_col & 15)) l_e = __uint_as_float(o[i]);
-        l_d = 0.f;
-        if (has_odd) {
-          tmem_ld16(tO0 + p.o_stride + (p.sum_col & ~15), o);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (i == (p.sum_col & 15)) l_d = __uint_as_float(o[i]);
-        }
-      }
       const float inv_l = 1.f / (f_e * l_e + f_d * l_d);
       const float g_e = f_e * inv_l, g_d = f_d * inv_l;
       act_t* orow = p.out + (static_cast<size_t>(b) * p.nq + qrow) * p.ldo + head * p.d;
@@ -477,7 +442,6 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   // TMEM: S double-buffered per query tile (64 columns each), then the O accumulators
   d.o_col = d.qtiles * 128;
   d.o_stride = d.qtiles == 2 ? 64 : 192;  // 2 x (128 + 2 * 64) or 128 + 2 * 192 = 512 columns
-  d.sum_col = (d.dN > h.d) ? h.d : -1;
   d.causal = h.causal;
   d.scale_log2 = h.scale * 1.4426950408889634f;
   // shared memory: Q + 2 P buffers per query tile are fixed; K/V rings take what is left (at most 4 stages)
@@ -500,17 +464,12 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
 
   const int smem_bytes = fixed + d.stages * per_stage;
   if (!g_attn_attr_set) {
-    B200SD_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           di.max_smem_optin - 512));
-    B200SD_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200SD_CUDA_CHECK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            di.max_smem_optin - 512));
     g_attn_attr_set = true;
   }
   dim3 grid(ceil_div(h.nq, kBQ * d.qtiles), h.heads, h.batch);
-  if (d.sum_col >= 0)
-    attention_kernel<true><<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
-  else
-    attention_kernel<false><<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
+  attention_kernel<<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
