@@ -497,6 +497,112 @@ def run_cuda(args):
     return 0
 
 
+def run_sweep(args):
+    """BASELINE.json configs[4]: total batch swept over --sweep (e.g. 1,2,4,...,128) on the GPUs of this launch.  The
+    prompts of each level are sharded over the ranks like the product does (contiguous slices, remainder to the low
+    ranks; levels smaller than the GPU count leave GPUs idle - reported as is).  One JSON line per level."""
+    import importlib
+    import torch.distributed as dist
+    import b200sd
+    P = importlib.import_module("k8s-nvidia-gpus_b200.pipeline")
+    D = b200sd.dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pipe = P.StableDiffusionPipeline.from_pretrained(args.model, device=f"cuda:{local}", scheduler=args.scheduler)
+    cfg = pipe.cfg
+    f = pipe.vae_scale_factor
+    h, w = args.height // f, args.width // f
+    sched = pipe.make_schedule(args.inference_steps)
+    evals = sched.num_evals
+    dev = torch.device("cuda", local)
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        unet, vae, clip = build_oracle(cfg)
+        r = cpu_sample(cfg, unet, vae, clip, 2, 1, args.inference_steps, h, w)
+        cpu = {"value": r["ips"], "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
+               "sample": "1 image: 2 timed + 1 warm-up CFG-paired UNet evaluations, 1 VAE decode, 1 CLIP pass"}
+        del unet, vae, clip
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    lines = []
+    for total in [int(x) for x in args.sweep.split(",")]:
+        b0, b1 = D.shard_range(total, world, rank)
+        B = b1 - b0
+        counts = D.shard_sizes(total, world)
+        job = None
+        if B > 0:
+            job = pipe.job(B, h, w, args.guidance_scale, True, zero_negative=pipe.is_xl)
+            prompts = synthetic_prompts(B, b0)
+            gens = [torch.Generator().manual_seed(1234 + b0 + i) for i in range(B)]
+            ids = pipe.tokenize(prompts, [""] * B, True)
+            lat = pipe.prepare_latents(B, h, w, gens, sched.init_noise_sigma)
+            job.ids_dev.copy_(ids)
+            job.eos_dev.copy_(pipe.eos_rows(ids, job.n_text))
+            job.init_latents.copy_(lat.permute(0, 2, 3, 1).reshape(B, h * w, 4))
+            job.step_table[:evals].copy_(sched.table)
+        empty = torch.zeros((0, h * f, w * f, 3), dtype=torch.uint8, device=dev)
+
+        def one_batch():
+            if job is not None:
+                job.reset()
+                job.run(evals)
+            if world > 1:
+                D.gather_images(job.images if job is not None else empty, counts)
+
+        for _ in range(max(1, args.warmup)):
+            one_batch()
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            one_batch()
+        e1.record()
+        sync_all()
+        t = torch.tensor([e0.elapsed_time(e1), 0.0], device=dev)
+        if job is not None:
+            job.reset()
+            u0, u1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            u0.record()
+            for _ in range(evals):
+                job.step_plan.launch()
+            u1.record()
+            torch.cuda.synchronize()
+            t[1] = u0.elapsed_time(u1) / evals
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            ips = args.steps * total / (t[0].item() * 1e-3)
+            line = {"metric": "images/sec", "sweep_total_batch": total, "value": ips, "unit": "images/s",
+                    "n_gpus": world, "gpus_busy": sum(1 for c in counts if c > 0), "per_gpu_batches": counts,
+                    "steps": args.steps, "warmup": max(1, args.warmup), "ms_per_step": t[0].item() / args.steps,
+                    "latency_ms_per_batch": t[0].item() / args.steps, "unet_ms_per_step_max": t[1].item(),
+                    "split_k_policy": os.environ.get("B200SD_SPLITK", "shape"),
+                    "vs_cpu_reference": (ips / cpu["value"]) if cpu else None, "cpu_baseline": cpu,
+                    "config": {"workload": f"{cfg['name']} architecture (random-init), {args.width}x{args.height}, "
+                                           f"{args.inference_steps} {args.scheduler.upper()} steps, CFG "
+                                           f"{args.guidance_scale}, total batch {total} sharded over {world} GPU(s)"}}
+            lines.append(line)
+            emit(json.dumps(line))
+        pipe._jobs.clear()   # the next level builds its own plans; give the activations back first
+        job = None
+        torch.cuda.empty_cache()
+    if rank == 0 and args.sweep_out:
+        with open(args.sweep_out, "w") as fo:
+            json.dump(lines, fo, indent=1)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 _RESULT_FD = None
 
 
@@ -536,12 +642,17 @@ def main(argv=None):
     ap.add_argument("--width", type=int, default=512)
     ap.add_argument("--height", type=int, default=512)
     ap.add_argument("--scheduler", default="ddim")
+    ap.add_argument("--sweep", default=None, help="batch-size sweep (configs[4]): comma-separated TOTAL batch sizes, one "
+                                                   "JSON line each (e.g. 1,2,4,8,16,32,64,128)")
+    ap.add_argument("--sweep-out", default=None, help="also write the sweep lines to this JSON file")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cupti", action="store_true", help="skip the CUPTI per-kernel pass (roofline falls back to "
                                                             "the CUDA-event share method)")
     args = ap.parse_args(argv)
     if args.impl == "reference":
         return run_reference(args)
+    if args.sweep:
+        return run_sweep(args)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if world != args.gpus and args.gpus > 1:
         print(f"bench.py: --gpus {args.gpus} needs torchrun with {args.gpus} ranks (WORLD_SIZE={world})", file=sys.stderr)

@@ -113,8 +113,19 @@ typedef struct {
    *       No upsampled tensor exists and 16 instead of 36 MACs are spent per input pixel and channel pair. */
   int32_t kh, kw, off_h, off_w, stride;
   int32_t out_pix_stride, out_row_stride, out_img_stride;
+  /* Split-K (0 or 1 = off): the reduction of every output tile is cut into split_k slices computed by different
+   * thread blocks - for layers with few output tiles and a long reduction (the 8x8-level convolutions: 40 tiles for
+   * 148 SMs at batch 8; everything at batch 1).  Each slice parks its fp32 accumulator tile in `workspace`; the block
+   * that arrives last adds the slices in INDEX order (bit-identical results whatever the arrival order) and runs the
+   * epilogue.  `workspace`: b200sd_gemm_workspace_bytes(p) bytes, 256-byte aligned, zero-filled once before its first
+   * use (calls leave its counters at zero, so consecutive calls on one stream may share it).  Single-CTA tiles only. */
+  int32_t split_k;
+  void* workspace;
+  int64_t workspace_bytes;
 } b200sd_gemm_params;
 int b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream stream);
+/* bytes of split-K workspace these parameters need (0 when split_k <= 1 or the parameters are rejected) */
+size_t b200sd_gemm_workspace_bytes(const b200sd_gemm_params* p);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Flash attention on tcgen05: out = softmax(Q K^T * scale [+ causal mask]) V, per (batch, head).
@@ -213,6 +224,8 @@ enum {
   B200SD_ST_W0 = 7,        /* PNDM: weights on eps history [newest .. oldest], 4 entries (7..10) */
   B200SD_ST_PNDM_MODE = 11,/* PNDM: 0 normal, 1 first step (store cur_sample), 2 second step (average, restore) */
   B200SD_ST_PUSH = 12,     /* PNDM: 1 = push eps into history ring */
+  B200SD_ST_GUIDANCE = 13, /* guidance scale of this call; 0 = use b200sd_sched_params.guidance_scale (so one captured
+                              graph serves every guidance value) */
   B200SD_ST_WIDTH = 16
 };
 

@@ -94,7 +94,9 @@ def unet_config(c: dict) -> dict:
 def vae_config(c: dict) -> dict:
     return {"latent_channels": c["latent_channels"], "out_channels": c["out_channels"],
             "block_out_channels": list(c["block_out_channels"]), "layers_per_block": c["layers_per_block"],
-            "norm_num_groups": c["norm_num_groups"], "scaling_factor": c.get("scaling_factor", 0.18215)}
+            "norm_num_groups": c["norm_num_groups"], "scaling_factor": c.get("scaling_factor", 0.18215),
+            # upstream runs a force_upcast VAE (SDXL) in fp32 because its activations overflow fp16: bf16 image here
+            "dtype": "bf16" if c.get("force_upcast", False) else "fp16"}
 
 
 def text_config(c: dict, penultimate: bool) -> dict:
@@ -118,6 +120,16 @@ def scheduler_config(c: dict) -> dict:
         raise NotImplementedError(f"beta_schedule {c['beta_schedule']!r}")
     if c.get("prediction_type", "epsilon") != "epsilon":
         raise NotImplementedError(f"prediction_type {c['prediction_type']!r}")
+    # what make_schedule() hard-codes; a checkpoint that asks for anything else must not load silently
+    want = {"timestep_spacing": "leading", "set_alpha_to_one": False, "clip_sample": False, "thresholding": False,
+            "use_karras_sigmas": False, "rescale_betas_zero_snr": False, "interpolation_type": "linear"}
+    if cls == "PNDMScheduler":
+        want["skip_prk_steps"] = True
+    if cls == "DDIMScheduler" and "clip_sample" not in c:
+        raise NotImplementedError("DDIMScheduler without clip_sample=false (upstream default is true: x0 clipping)")
+    for k, v in want.items():
+        if k in c and c[k] != v:
+            raise NotImplementedError(f"scheduler_config {k}={c[k]!r} is not implemented (only {v!r})")
     return {"type": _SCHED[cls], "steps_offset": c.get("steps_offset", 0), "beta_start": c["beta_start"],
             "beta_end": c["beta_end"], "num_train_timesteps": c.get("num_train_timesteps", 1000)}
 

@@ -1,5 +1,13 @@
 // C-ABI plumbing: version, thread-local error string, device query, TMA descriptor encoding.
+#include <map>
 #include <mutex>
+#include <set>
+#include <string>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+#include <string.h>
 
 #include "host.cuh"
 
@@ -40,6 +48,49 @@ int get_device_info(DeviceInfo* out) {
   }
   *out = g_info[dev];
   return B200SD_OK;
+}
+
+static std::set<std::pair<int, const void*>> g_smem_set;
+
+int ensure_dyn_smem(const void* kernel, int bytes) {
+  int dev = 0;
+  B200SD_CUDA_CHECK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(g_mu);
+  const auto key = std::make_pair(dev, kernel);
+  if (g_smem_set.count(key)) return B200SD_OK;
+  B200SD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  g_smem_set.insert(key);
+  return B200SD_OK;
+}
+
+static std::mutex g_cache_mu;
+static std::unordered_map<std::string, std::vector<unsigned char>> g_launch_cache;
+static const size_t kLaunchCacheMax = 8192;
+
+static std::string cache_key(int family, const void* params, size_t n) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::string k(reinterpret_cast<const char*>(params), n);
+  k.push_back(static_cast<char>(family));
+  k.push_back(static_cast<char>(dev));
+  return k;
+}
+
+bool launch_cache_get(int family, const void* params, size_t params_bytes, void* out, size_t out_bytes) {
+  const std::string k = cache_key(family, params, params_bytes);
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  auto it = g_launch_cache.find(k);
+  if (it == g_launch_cache.end() || it->second.size() != out_bytes) return false;
+  memcpy(out, it->second.data(), out_bytes);
+  return true;
+}
+
+void launch_cache_put(int family, const void* params, size_t params_bytes, const void* val, size_t val_bytes) {
+  const std::string k = cache_key(family, params, params_bytes);
+  std::lock_guard<std::mutex> lk(g_cache_mu);
+  if (g_launch_cache.size() >= kLaunchCacheMax) g_launch_cache.clear();
+  const unsigned char* v = static_cast<const unsigned char*>(val);
+  g_launch_cache[k] = std::vector<unsigned char>(v, v + val_bytes);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

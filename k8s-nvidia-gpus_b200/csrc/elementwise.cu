@@ -49,6 +49,7 @@ __global__ void cfg_sched_kernel(const float* __restrict__ eps, float4* __restri
                                  int cfg, float gs) {
   const int step = counter[0];
   const float* T = table + step * B200SD_ST_WIDTH;
+  if (T[B200SD_ST_GUIDANCE] != 0.f) gs = T[B200SD_ST_GUIDANCE];  // per-call guidance travels in the step table
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < npix) {
     const float* eu = eps + static_cast<size_t>(i) * ld_eps;

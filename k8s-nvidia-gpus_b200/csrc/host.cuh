@@ -45,6 +45,17 @@ int encode_tmap_act(CUtensorMap* tm, const void* base, int rank, const uint64_t*
 int encode_tmap_f32(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box);
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE property of a kernel: set once per (current device,
+// kernel) under a lock, so a second GPU in the same process - or two host threads racing the first call - never
+// launch with the default 48 KB limit.
+int ensure_dyn_smem(const void* kernel, int bytes);
+
+// Launch-descriptor cache: building a launch costs 3-5 cuTensorMapEncodeTiled calls plus the tile
+// plan; a plan replays the same parameter blocks over and over, so the finished device-side descriptor block is kept,
+// keyed by (device, kernel family, the caller's parameter bytes).  Mutex-guarded, bounded (cleared when full).
+bool launch_cache_get(int family, const void* params, size_t params_bytes, void* out, size_t out_bytes);
+void launch_cache_put(int family, const void* params, size_t params_bytes, const void* val, size_t val_bytes);
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int pow2_ceil(int v) {

@@ -7,6 +7,8 @@ memory.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import lib as L
@@ -144,6 +146,12 @@ class Builder:
         self.stats = torch.zeros(stats_words, dtype=torch.int32, device=device)
         self.stats_off = 0
         self.plan.keep.append(self.stats)
+        # split-K policy (b200sd.h, split_k): "shape" (default) cuts the long reductions of the 8x8-level convolutions
+        # into 3 slices - a function of the per-image shape only, so an image's bytes do not depend on the batch it
+        # rides in; "auto" sizes the split from the tile count of the actual launch (best at batch 1-2, gives up that
+        # bitwise batch invariance); "0" turns it off.
+        self.split_policy = os.environ.get("B200SD_SPLITK", "shape")
+        self.split_calls = []
 
     # ------------------------------------------------------------------ memory
     def alloc(self, shape, dtype=None):
@@ -187,7 +195,33 @@ class Builder:
     def _pow2_ceil(v):
         return 1 << max(0, (v - 1).bit_length())
 
+    def split_k_for(self, rows_per_img: int, m_rows: int, n: int, nkb: int) -> int:
+        """Number of K slices for a GEMM of m_rows x n with nkb 64-deep K blocks (see split_policy)."""
+        if self.split_policy == "shape":
+            return 3 if (rows_per_img <= 64 and nkb >= 96) else 1
+        if self.split_policy == "auto":
+            tiles = -(-m_rows // 128) * -(-n // 256)
+            if tiles >= 90 or nkb < 32:
+                return 1
+            return max(1, min(8, nkb // 16, 148 // tiles))
+        return 1
+
+    def add_gemm(self, call, split_k: int):
+        """Queue a gemm call; split-K calls get the plan's shared workspace patched in by finish()."""
+        if split_k > 1:
+            self.split_calls.append(call)
+        self.add(call)
+
     def finish(self) -> Plan:
+        if self.split_calls:
+            # one zero-initialised workspace shared by every split-K call of the plan (stream order serialises them,
+            # and each call leaves the counters at zero)
+            need = max(ops.gemm_workspace_bytes(c) for c in self.split_calls)
+            ws = torch.zeros((need + 255) // 256 * 64, dtype=torch.int32, device=self.device)
+            self.plan.keep.append(ws)
+            for c in self.split_calls:
+                c.params.workspace, c.params.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+            self.split_calls = []
         if self.stats_off:
             self.plan.calls.insert(0, ops.memset_zero(self.stats, self.stats_off * 4))
         return self.plan
@@ -211,11 +245,13 @@ class Builder:
         if out is None:
             out = self.alloc((a0.nimg, a0.h, a0.w, cout), out_dtype)
         a1 = xs[1] if len(xs) > 1 else None
-        self.add(ops.gemm(a0.t, w, out, nimg=a0.nimg, h=a0.h, w_=a0.w, c0=a0.c, n=cout, ksize=ksize,
-                          a1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c, bias=b, rowbias=rowbias,
-                          ld_rowbias=ld_rowbias, residual=None if residual is None else residual.t,
-                          ldr=0 if residual is None else residual.c, ldc=ldc, act=act, gn_stats=st,
-                          gn_groups=gn_groups if st is not None else 0))
+        nkb = ksize * ksize * sum(-(-a.c // 64) for a in xs)
+        sk = self.split_k_for(a0.hw, a0.rows, cout, nkb) if out_dtype in (None, ops.act_dtype()) else 1
+        self.add_gemm(ops.gemm(a0.t, w, out, nimg=a0.nimg, h=a0.h, w_=a0.w, c0=a0.c, n=cout, ksize=ksize,
+                               a1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c, bias=b, rowbias=rowbias,
+                               ld_rowbias=ld_rowbias, residual=None if residual is None else residual.t,
+                               ldr=0 if residual is None else residual.c, ldc=ldc, act=act, gn_stats=st,
+                               gn_groups=gn_groups if st is not None else 0, split_k=sk), sk)
         return Act(out, a0.nimg, a0.h, a0.w, cout if ldc is None else ldc,
                    stats=None if st is None else (st, gn_groups))
 
@@ -228,9 +264,11 @@ class Builder:
             geo = dict(nimg=x.rows, h=1, w_=1)
         else:
             geo = dict(nimg=1, h=1, w_=x.rows)
-        self.add(ops.gemm(x.t, w, out, c0=x.c, n=n, ksize=1, bias=b, residual=None if residual is None else residual.t,
-                          ldr=0 if residual is None else residual.c, act=act, rowbias=rowbias, ld_rowbias=ld_rowbias,
-                          **geo))
+        sk = self.split_k_for(1 << 30, x.rows, n, -(-x.c // 64))  # (only the "auto" policy splits linear layers)
+        self.add_gemm(ops.gemm(x.t, w, out, c0=x.c, n=n, ksize=1, bias=b,
+                               residual=None if residual is None else residual.t,
+                               ldr=0 if residual is None else residual.c, act=act, rowbias=rowbias,
+                               ld_rowbias=ld_rowbias, split_k=sk, **geo), sk)
         return Act(out, x.nimg, x.h, x.w, n_out)
 
     def linear(self, W: DeviceWeights, name, x: Act, n, *, bias=True, **kw):
@@ -292,9 +330,10 @@ class Builder:
         if (self.fuse_gn_stats and gn_groups and cout % (2 * gn_groups) == 0 and 9 * x.c >= 24 * 64
                 and min(128, self._pow2_ceil(wo)) * self._pow2_ceil(ho) >= 32):
             st = self.stats_slice(x.nimg, gn_groups)
-        self.add(ops.gemm(x.t, W.conv(name), out, nimg=x.nimg, h=ho, w_=wo, c0=x.c, n=cout, ksize=3, kh=3, kw=3,
-                          off_h=-1, off_w=-1, stride=2, bias=W.vec(name + ".bias"), gn_stats=st,
-                          gn_groups=gn_groups if st is not None else 0))
+        sk = self.split_k_for(ho * wo, x.nimg * ho * wo, cout, 9 * -(-x.c // 64))
+        self.add_gemm(ops.gemm(x.t, W.conv(name), out, nimg=x.nimg, h=ho, w_=wo, c0=x.c, n=cout, ksize=3, kh=3, kw=3,
+                               off_h=-1, off_w=-1, stride=2, bias=W.vec(name + ".bias"), gn_stats=st,
+                               gn_groups=gn_groups if st is not None else 0, split_k=sk), sk)
         return Act(out, x.nimg, ho, wo, cout, stats=None if st is None else (st, gn_groups))
 
     # ------------------------------------------------------------------ composite blocks (UNet + VAE)

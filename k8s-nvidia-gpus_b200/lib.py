@@ -9,15 +9,18 @@ import ctypes as C
 from pathlib import Path
 
 _LIB_PATH = Path(__file__).resolve().parent / "libb200sd.so"
-_lib = None
+# one library image per 16-bit element type (build.py VARIANTS); "fp16" is the default image
+_LIB_PATHS = {"fp16": _LIB_PATH, "bf16": Path(__file__).resolve().parent / "libb200sd_bf16.so"}
+_libs = {}
+_current = "fp16"
 
 ACT_NONE, ACT_SILU, ACT_QUICK_GELU, ACT_GEGLU, ACT_GELU = 0, 1, 2, 3, 4
 ACT16, F32 = 0, 1
 BF16 = ACT16  # historical alias
 GN_NOALLOC_MAX_STATS = 16384  # B200SD_GN_NOALLOC_MAX_STATS (4-byte words)
 GN_STATS_WORDS = 8  # B200SD_GN_STATS_WORDS: 4-byte words of statistics scratch per (image, group)
-ST_TIMESTEP, ST_IN_SCALE, ST_KIND, ST_C0, ST_C1, ST_C2, ST_C3, ST_W0, ST_PNDM_MODE, ST_PUSH, ST_WIDTH = (
-    0, 1, 2, 3, 4, 5, 6, 7, 11, 12, 16)
+ST_TIMESTEP, ST_IN_SCALE, ST_KIND, ST_C0, ST_C1, ST_C2, ST_C3, ST_W0, ST_PNDM_MODE, ST_PUSH, ST_GUIDANCE, ST_WIDTH = (
+    0, 1, 2, 3, 4, 5, 6, 7, 11, 12, 13, 16)
 
 vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
@@ -28,7 +31,8 @@ class GemmParams(C.Structure):
                 ("n", i32), ("ksize", i32), ("ldc", i32), ("ldr", i32), ("ld_rowbias", i32), ("act", i32),
                 ("out_dtype", i32), ("bn_hint", i32), ("alpha", f32), ("gn_stats", vp), ("gn_groups", i32),
                 ("gn_rows_per_img", i32), ("kh", i32), ("kw", i32), ("off_h", i32), ("off_w", i32), ("stride", i32),
-                ("out_pix_stride", i32), ("out_row_stride", i32), ("out_img_stride", i32)]
+                ("out_pix_stride", i32), ("out_row_stride", i32), ("out_img_stride", i32), ("split_k", i32),
+                ("workspace", vp), ("workspace_bytes", i64)]
 
 
 class AttnParams(C.Structure):
@@ -94,6 +98,7 @@ ENTRY_POINTS = {
     "b200sd_device_info": None,
     "b200sd_struct_sizes": None,
     "b200sd_gemm": GemmParams,
+    "b200sd_gemm_workspace_bytes": None,
     "b200sd_attention": AttnParams,
     "b200sd_groupnorm_stats": GroupNormParams,
     "b200sd_groupnorm_apply": GroupNormParams,
@@ -119,16 +124,38 @@ def lib_path() -> Path:
     return _LIB_PATH
 
 
-def load():
-    """Load libb200sd.so (once).  Raises if it has not been built — there is no other execution path."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not _LIB_PATH.exists():
+class use:
+    """`with lib.use("bf16"):` - calls prepared inside the block bind to that image of the library (a plan is built
+    once, so this is a per-plan choice of the 16-bit type: the SDXL VAE decoder runs bf16 beside an fp16 UNet)."""
+
+    def __init__(self, variant: str):
+        if variant not in _LIB_PATHS:
+            raise ValueError(f"unknown library variant {variant!r} ({sorted(_LIB_PATHS)})")
+        self.variant = variant
+
+    def __enter__(self):
+        global _current
+        self.prev, _current = _current, self.variant
+        return self
+
+    def __exit__(self, *exc):
+        global _current
+        _current = self.prev
+        return False
+
+
+def load(variant: str | None = None):
+    """Load the library image (once per variant; default: the current one).  Raises if it has not been built — there
+    is no other execution path."""
+    variant = variant or _current
+    if variant in _libs:
+        return _libs[variant]
+    path = _LIB_PATHS[variant]
+    if not path.exists():
         raise B200SDError(
-            f"{_LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(nvcc, sm_100a). b200sd has no CPU or library fallback.")
-    lib = C.CDLL(str(_LIB_PATH))
+    lib = C.CDLL(str(path))
     lib.b200sd_version.restype = C.c_int
     lib.b200sd_act_dtype.restype = C.c_int
     lib.b200sd_last_error.restype = C.c_char_p
@@ -140,9 +167,11 @@ def load():
         fn = getattr(lib, name)
         fn.argtypes = [C.POINTER(st), vp]
         fn.restype = C.c_int
+    lib.b200sd_gemm_workspace_bytes.argtypes = [C.POINTER(GemmParams)]
+    lib.b200sd_gemm_workspace_bytes.restype = C.c_size_t
     lib.b200sd_groupnorm_workspace_bytes.argtypes = [C.POINTER(GroupNormParams)]
     lib.b200sd_groupnorm_workspace_bytes.restype = C.c_size_t
-    _lib = lib
+    _libs[variant] = lib
     return lib
 
 

@@ -79,7 +79,8 @@ def geglu_perm(n2: int) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------ call builders
 def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld1=None, bias=None, rowbias=None,
          ld_rowbias=0, residual=None, ldr=0, ldc=None, act=L.ACT_NONE, out_dtype=None, alpha=1.0, bn_hint=0,
-         gn_stats=None, gn_groups=0, gn_rows_per_img=0, kh=0, kw=0, off_h=0, off_w=0, stride=0, out_strides=None):
+         gn_stats=None, gn_groups=0, gn_rows_per_img=0, kh=0, kw=0, off_h=0, off_w=0, stride=0, out_strides=None,
+         split_k=0, workspace=None):
     """out_strides: (pixel, row, image) strides of the output in elements when its pixels are interleaved into a larger
     tensor (pass the strided VIEW as `out`: its data_ptr is the first pixel)."""
     p = L.GemmParams()
@@ -103,7 +104,15 @@ def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld
     p.kh, p.kw, p.off_h, p.off_w, p.stride = kh, kw, off_h, off_w, stride
     if out_strides is not None:
         p.out_pix_stride, p.out_row_stride, p.out_img_stride = out_strides
-    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual, gn_stats))
+    p.split_k = split_k
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
+    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual, gn_stats, workspace))
+
+
+def gemm_workspace_bytes(call) -> int:
+    """Split-K workspace bytes a prepared gemm Call needs (0 without split_k)."""
+    return int(L.load().b200sd_gemm_workspace_bytes(C.byref(call.params)))
 
 
 def attention(q, k, v, out, *, batch, heads, nq, nk, d, ldq, ldk, ldv, ldo, scale, causal=False):

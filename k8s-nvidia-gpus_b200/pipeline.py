@@ -12,11 +12,14 @@ uint8 image runs as b200sd CUDA kernels; there is no CPU or library fallback.
 """
 from __future__ import annotations
 
+import collections
+import logging
 import os
 
 import numpy as np
 import torch
 
+from . import lib as L
 from . import ops
 from . import schedulers as S
 from . import checkpoint as Ck
@@ -27,6 +30,8 @@ from .unet import UNetEngine
 from .vae import VAEDecoderEngine
 
 MAX_EVALS = 1024
+MAX_JOBS = int(os.environ.get("B200SD_MAX_JOBS", "4"))  # prepared (batch, size) shapes kept per pipeline (LRU)
+logger = logging.getLogger("b200sd")
 
 
 def sinusoid(values: torch.Tensor, dim: int) -> torch.Tensor:
@@ -153,7 +158,7 @@ class Job:
 
 class StableDiffusionPipeline:
     def __init__(self, cfg: dict, unet_sd: dict, vae_sd: dict, text_sd, tokenizer: CLIPTokenizer | None = None,
-                 device: str = "cuda", scheduler: str | None = None):
+                 device: str = "cuda", scheduler: str | None = None, vae_dtype: str | None = None):
         """text_sd: one state dict, or a list with one per entry of cfg["text_encoders"] (SDXL: CLIP-L, OpenCLIP-bigG
         with text_projection)."""
         if not torch.cuda.is_available():
@@ -168,7 +173,10 @@ class StableDiffusionPipeline:
         self.device = dev
         torch.cuda.set_device(self.device)
         self.unet = UNetEngine(cfg["unet"], unet_sd, self.device)
-        self.vae_engine = VAEDecoderEngine(cfg["vae"], vae_sd, self.device)
+        # 16-bit type of the VAE decoder ("fp16" | "bf16"): configs/sdxl.json asks for bf16 (fp32 exponent range: real
+        # SDXL VAE activations overflow fp16, upstream force_upcasts that decoder to fp32); the UNet / text encoders
+        # stay fp16, whose 11-bit significand the CFG-amplified latents need
+        self.vae_engine = VAEDecoderEngine(cfg["vae"], vae_sd, self.device, variant=vae_dtype)
         self.vae = _VaeHandle(self.vae_engine)
         self.text_encoders = [CLIPTextEngine(c, sd, self.device) for c, sd in zip(cfg["text_encoders"], text_sds)]
         self.text_encoder = self.text_encoders[0]
@@ -184,18 +192,20 @@ class StableDiffusionPipeline:
         self.scheduler_kind = (scheduler or cfg["scheduler"]["type"]).lower()
         self.vae_scale_factor = self.vae_engine.scale_factor
         self.use_cuda_graph = os.environ.get("B200SD_NO_GRAPH", "0") != "1"
-        self._jobs = {}
+        self._jobs = collections.OrderedDict()
         self.last_timings = {}
         self.model_id = cfg.get("name", "?")
 
     # ------------------------------------------------------------------ construction (reference configmap.yaml:41)
     @classmethod
     def from_pretrained(cls, model_id: str = "sd15", torch_dtype=None, device: str = "cuda", seed: int = 0,
-                        scheduler: str | None = None, **_ignored):
+                        scheduler: str | None = None, random_init: bool | None = None, **_ignored):
         """model_id: a checkpoint directory in diffusers layout (model_index.json, */config.json, *.safetensors,
         tokenizer/, scheduler/ - loaded as is), a config name under configs/ ("sd15", "tiny", "sdxl"), a config .json
-        path, or a hub-style id such as "runwayml/stable-diffusion-v1-5" (mapped to the sd15 architecture).  Without a
-        checkpoint directory the weights are random-init (seeded) in the diffusers key layout; `torch_dtype` is accepted for signature
+        path.  Architecture names give random-init weights (seeded, diffusers key layout; a WARNING is logged).  Anything
+        else - a hub-style id such as "runwayml/stable-diffusion-v1-5", a mistyped or unmounted path - raises
+        FileNotFoundError unless random_init=True / B200SD_RANDOM_WEIGHTS=1 maps it to the sd15 / sdxl architecture with
+        random weights; `torch_dtype` is accepted for signature
         compatibility (compute is 16-bit operands with fp32 accumulation and statistics; lib.act_dtype())."""
         if Ck.is_checkpoint_dir(model_id):
             # a real checkpoint in diffusers layout (SURVEY §8(f) rank 3): configs, safetensors weights, scheduler
@@ -206,12 +216,28 @@ class StableDiffusionPipeline:
             pipe.model_id = model_id
             return pipe
         name = model_id
-        if not os.path.exists(model_id) and not os.path.exists(os.path.join(Wt.CONFIG_DIR, f"{model_id}.json")):
+        explicit = os.path.isfile(model_id) or os.path.exists(os.path.join(Wt.CONFIG_DIR, f"{model_id}.json"))
+        if not explicit:
+            # neither a checkpoint directory nor an architecture name: a hub id, or a mistyped / unmounted path.  Never
+            # answer requests with noise silently - random weights need an explicit opt-in.
+            if random_init is None:
+                random_init = os.environ.get("B200SD_RANDOM_WEIGHTS", "0") == "1"
+            if not random_init:
+                raise FileNotFoundError(
+                    f"{model_id!r} is neither a checkpoint directory in diffusers layout (model_index.json) nor an "
+                    f"architecture name under configs/ ({', '.join(sorted(Wt.config_names()))}); hub ids cannot be "
+                    "downloaded here.  Pass random_init=True (or B200SD_RANDOM_WEIGHTS=1) to run that architecture "
+                    "with random-init weights.")
             name = "sdxl" if "xl" in model_id.lower() else "sd15"
+        logger.warning("b200sd: %r -> architecture %r with RANDOM-INIT weights (seed %d); images are noise",
+                       model_id, name, seed)
         cfg = Wt.load_config(name)
         kw = dict(round_dtype=ops.act_dtype(), device=device, store_dtype=ops.act_dtype())  # drawn on the GPU
         unet_sd = Wt.random_state_dict(Wt.unet_schema(cfg["unet"]), seed, **kw)
-        vae_sd = Wt.random_state_dict(Wt.vae_decoder_schema(cfg["vae"]), seed + 1, **kw)
+        vkw = dict(kw)
+        if cfg["vae"].get("dtype") == "bf16":
+            vkw.update(round_dtype=torch.bfloat16, store_dtype=torch.bfloat16)
+        vae_sd = Wt.random_state_dict(Wt.vae_decoder_schema(cfg["vae"]), seed + 1, **vkw)
         text_sd = [Wt.random_state_dict(Wt.clip_text_schema(c), seed + 2 + i, **kw)
                    for i, c in enumerate(cfg["text_encoders"])]
         pipe = cls(cfg, unet_sd, vae_sd, text_sd, device=device, scheduler=scheduler)
@@ -230,10 +256,18 @@ class StableDiffusionPipeline:
 
     # ------------------------------------------------------------------ stages
     def job(self, batch, h, w, guidance_scale, cfg_on, zero_negative=False) -> Job:
-        key = (batch, h, w, float(guidance_scale), cfg_on, bool(zero_negative))
-        if key not in self._jobs:
-            self._jobs[key] = Job(self, batch, h, w, guidance_scale, cfg_on, zero_negative)
-        return self._jobs[key]
+        """The prepared plans / buffers / captured graph for one SHAPE.  The guidance scale is not part of the key: it
+        travels in the device step table (B200SD_ST_GUIDANCE).  At most MAX_JOBS shapes are kept (least recently used
+        is dropped, its buffers go back to the allocator) so that client-chosen sizes cannot exhaust HBM."""
+        key = (batch, h, w, cfg_on, bool(zero_negative))
+        job = self._jobs.get(key)
+        if job is None:
+            while len(self._jobs) >= max(1, MAX_JOBS):
+                self._jobs.popitem(last=False)
+                torch.cuda.empty_cache()
+            job = self._jobs[key] = Job(self, batch, h, w, guidance_scale, cfg_on, zero_negative)
+        self._jobs.move_to_end(key)
+        return job
 
     def make_schedule(self, num_inference_steps, scheduler=None):
         kind = (scheduler or self.scheduler_kind).lower()
@@ -315,6 +349,7 @@ class StableDiffusionPipeline:
             lat = latents.to(torch.float32).cpu() * sched.init_noise_sigma
         job.lat_host.copy_(lat.permute(0, 2, 3, 1).reshape(batch, h * w, 4))
         job.table_host[: sched.num_evals].copy_(sched.table)
+        job.table_host[: sched.num_evals, L.ST_GUIDANCE] = float(guidance_scale)
 
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         ev[0].record()

@@ -33,6 +33,7 @@ from pydantic import BaseModel
 logger = logging.getLogger("sd15-api")
 
 DEFAULT_STEPS, DEFAULT_GUIDANCE, DEFAULT_SIZE = 30, 7.5, 512
+MIN_SIZE, MAX_SIZE, MAX_STEPS = 8, int(os.getenv("B200SD_MAX_SIZE", "2048")), 1000
 
 
 class GenReq(BaseModel):
@@ -90,6 +91,14 @@ def create_app(pipe=None, pipe_factory=None, max_batch: int | None = None, max_w
         steps = req.steps or DEFAULT_STEPS
         gs = req.guidance_scale or DEFAULT_GUIDANCE
         width, height = req.width or DEFAULT_SIZE, req.height or DEFAULT_SIZE
+        # client-controlled shapes are bounded BEFORE they reach the GPU (each new size builds plans and a CUDA graph):
+        # upstream's own rule (multiples of 8) plus a size / step range; errors are 400s, not 500s
+        if width % 8 or height % 8 or not (MIN_SIZE <= width <= MAX_SIZE) or not (MIN_SIZE <= height <= MAX_SIZE):
+            raise HTTPException(400, f"width and height must be multiples of 8 in [{MIN_SIZE}, {MAX_SIZE}]")
+        if not (1 <= steps <= MAX_STEPS):
+            raise HTTPException(400, f"steps must be in [1, {MAX_STEPS}]")
+        if not (0.0 <= gs <= 100.0):
+            raise HTTPException(400, "guidance_scale must be in [0, 100]")
         t0 = time.time()
         logger.info("Generating prompt='%s' steps=%s guidance=%.2f seed=%s size=%sx%s", req.prompt, steps, gs,
                     req.seed if req.seed is not None else "auto", width, height)
@@ -109,7 +118,9 @@ def create_app(pipe=None, pipe_factory=None, max_batch: int | None = None, max_w
 
 def _default_factory():
     from .pipeline import StableDiffusionPipeline
-    model_id = os.getenv("MODEL_ID", "runwayml/stable-diffusion-v1-5")
+    # MODEL_ID: a checkpoint directory in diffusers layout (what the reference's HF cache holds) or an architecture
+    # name; a hub id / missing path raises (no silent random weights - see from_pretrained)
+    model_id = os.getenv("MODEL_ID", "/models/stable-diffusion-v1-5")
     pipe = StableDiffusionPipeline.from_pretrained(model_id)
     pipe.enable_attention_slicing()
     pipe.enable_vae_slicing()

@@ -8,7 +8,12 @@ of HBM the decoder runs batched.
 The single-head mid-block attention has head dim 512 (> the flash kernel's 160 limit and > one SM's TMEM/smem budget
 for a fused tile), so it runs unfused on the same GEMM kernel: S = QK^T (alpha = 1/sqrt(C)) -> row softmax ->
 O = P V with V^T produced directly by a GEMM with swapped operand roles (V^T = W_v X^T); V's bias is added after the
-product (rows of P sum to 1).
+product (rows of P sum to 1).  The fp32 logits are produced in blocks of query rows (at most ATTN_LOGIT_BYTES at a
+time, reused for every block and image), so no [hw, hw] matrix is ever materialised: at 1024x1024 (16 384 tokens) the
+full matrix would be 1 GiB per image.
+
+The 16-bit type of the decoder is a per-engine choice (`variant`): "bf16" binds the plan to the bfloat16 image of the
+library - the SDXL VAE needs fp32's exponent range (upstream `force_upcast`s it to fp32), while the UNet stays fp16.
 """
 from __future__ import annotations
 
@@ -19,11 +24,15 @@ from . import ops
 from .engine import Act, Builder, DeviceWeights
 
 
+ATTN_LOGIT_BYTES = 64 << 20
+
+
 class VAEDecoderEngine:
-    def __init__(self, cfg: dict, state_dict: dict, device="cuda"):
+    def __init__(self, cfg: dict, state_dict: dict, device="cuda", variant: str | None = None):
         self.cfg = cfg
         self.device = torch.device(device)
         self.W = DeviceWeights(state_dict, self.device)
+        self.variant = variant or cfg.get("dtype", "fp16")
 
     @property
     def scale_factor(self):
@@ -39,16 +48,19 @@ class VAEDecoderEngine:
         # V^T[c_out, token] = W_v[c_out, :] . X[token, :]  — weights play the A role, activations the B role
         wv = W.act16(p + ".to_v.weight")
         vt = bld.alloc((n, c, hw))
-        s = bld.alloc((hw, hw), torch.float32)
-        pm = bld.alloc((hw, hw))
+        rb = max(128, min(hw, (ATTN_LOGIT_BYTES // (4 * hw)) // 128 * 128))  # query rows per logit block
+        s = bld.alloc((rb, hw), torch.float32)
+        pm = bld.alloc((rb, hw))
         o = bld.alloc((n, x.h, x.w, c))
-        q2, k2, gn2 = q.t.view(n, hw, c), k.t.view(n, hw, c), gn.t.view(n, hw, c)
+        q2, k2, gn2, o2 = q.t.view(n, hw, c), k.t.view(n, hw, c), gn.t.view(n, hw, c), o.view(n, hw, c)
         for i in range(n):
             bld.add(ops.gemm(wv, gn2[i], vt[i], nimg=1, h=1, w_=c, c0=c, n=hw, ksize=1))
-            bld.add(ops.gemm(q2[i], k2[i], s, nimg=1, h=1, w_=hw, c0=c, n=hw, ksize=1, alpha=c ** -0.5))
-            bld.add(ops.softmax_rows(s, pm, rows=hw, cols=hw))
-            bld.add(ops.gemm(pm, vt[i], o.view(n, hw, c)[i], nimg=1, h=1, w_=hw, c0=hw, n=c, ksize=1,
-                             bias=W.vec(p + ".to_v.bias")))
+            for r0 in range(0, hw, rb):
+                r = min(rb, hw - r0)
+                bld.add(ops.gemm(q2[i, r0:r0 + r], k2[i], s, nimg=1, h=1, w_=r, c0=c, n=hw, ksize=1, alpha=c ** -0.5))
+                bld.add(ops.softmax_rows(s, pm, rows=r, cols=hw))
+                bld.add(ops.gemm(pm, vt[i], o2[i, r0:r0 + r], nimg=1, h=1, w_=r, c0=hw, n=c, ksize=1,
+                                 bias=W.vec(p + ".to_v.bias")))
         bld.free(gn, q, k, vt, s, pm)
         oa = Act(o, n, x.h, x.w, c)
         out = bld.linear(W, p + ".to_out.0", oa, c, residual=x)
@@ -57,6 +69,10 @@ class VAEDecoderEngine:
 
     def build_plan(self, batch: int, h: int, w: int, latents: torch.Tensor):
         """latents f32 NHWC [batch, h*w, 4] -> (plan, uint8 images [batch, h*f, w*f, 3])."""
+        with L.use(self.variant):  # every call of this plan binds to the engine's image of the library
+            return self._build_plan(batch, h, w, latents)
+
+    def _build_plan(self, batch: int, h: int, w: int, latents: torch.Tensor):
         cfg, W = self.cfg, self.W
         ch = cfg["block_out_channels"]
         g = cfg["norm_num_groups"]

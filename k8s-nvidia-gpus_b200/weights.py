@@ -16,6 +16,11 @@ import torch
 CONFIG_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "configs")
 
 
+def config_names():
+    """Architecture names available under configs/."""
+    return [f[:-5] for f in os.listdir(CONFIG_DIR) if f.endswith(".json")]
+
+
 def load_config(name_or_path: str) -> dict:
     path = name_or_path if os.path.exists(name_or_path) else os.path.join(CONFIG_DIR, f"{name_or_path}.json")
     with open(path) as f:

@@ -290,6 +290,69 @@ def test_upsample_conv_folded_into_four_phase_convs(cuda_lib, b200sd, nimg, H, W
         assert (got - want).abs().max().item() <= 2e-4 * want.abs().max().item() + 1e-2
 
 
+@pytest.mark.parametrize("split", [2, 3, 5])
+def test_split_k_conv_and_linear(cuda_lib, b200sd, split):
+    """Split-K: the reduction cut into slices on different thread blocks, slices added in index order by whichever
+    block arrives last.  8x8-level conv (bias + time-embedding row bias + residual + fused GroupNorm statistics), a
+    GEGLU linear and an fp32-output linear - each against torch, and bit-identical across repeated runs on a SHARED
+    workspace (the counters re-arm themselves)."""
+    torch.manual_seed(30 + split)
+    ops, L = b200sd.ops, b200sd.lib
+    s = ops.current_stream()
+    nimg, H, W, cin, cout, groups = 6, 8, 8, 640, 320, 32
+    x, w = _rand(nimg, H, W, cin), _rand(cout, cin, 3, 3, scale=(9 * cin) ** -0.5)
+    bias, res, temb = torch.randn(cout, device="cuda"), _rand(nimg, H, W, cout), torch.randn(nimg, cout, device="cuda")
+    wp = ops.pack_conv_weight(w.float().cpu()).cuda()
+    M, K, Fh = 300, 1280, 256
+    xl = _rand(M, K)
+    w2, b2 = _rand(2 * Fh, K, scale=K ** -0.5), torch.randn(2 * Fh, device="cuda")
+    perm = ops.geglu_perm(2 * Fh)
+    w2p = ops.pack_linear_weight(w2.float().cpu()[perm]).cuda()
+    b2p = b2[perm.cuda()].contiguous()
+    wl = _rand(200, K, scale=K ** -0.5)
+    wlp = ops.pack_linear_weight(wl.float().cpu()).cuda()
+
+    def calls():
+        out = torch.full((nimg, H, W, cout), float("nan"), device="cuda", dtype=ACT())
+        stats = ops.groupnorm_stats_buffer(nimg, groups)
+        outg = torch.full((M, Fh), float("nan"), device="cuda", dtype=ACT())
+        out32 = torch.full((M, 200), float("nan"), device="cuda", dtype=torch.float32)
+        cs = [ops.gemm(x, wp, out, nimg=nimg, h=H, w_=W, c0=cin, n=cout, ksize=3, bias=bias, residual=res, rowbias=temb,
+                       ld_rowbias=cout, gn_stats=stats, gn_groups=groups, split_k=split),
+              ops.gemm(xl, w2p, outg, nimg=1, h=1, w_=M, c0=K, n=2 * Fh, bias=b2p, act=L.ACT_GEGLU, split_k=split),
+              ops.gemm(xl, wlp, out32, nimg=1, h=1, w_=M, c0=K, n=200, split_k=split)]
+        return cs, (out, stats, outg, out32)
+
+    cs, _ = calls()
+    need = max(ops.gemm_workspace_bytes(c) for c in cs)
+    assert need > 0
+    ws = torch.zeros((need + 255) // 256 * 64, dtype=torch.int32, device="cuda")  # zeroed once, shared by every call
+    results = []
+    for _ in range(3):
+        cs, outs = calls()
+        for c in cs:
+            c.params.workspace, c.params.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+            c(s)
+        torch.cuda.synchronize()
+        results.append(outs)
+    out, stats, outg, out32 = results[0]
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), bias, padding=1).permute(0, 2, 3, 1) + res.float() \
+        + temb[:, None, None, :]
+    _report(f"split-{split} conv3x3 + temb + residual", out, ref, 1e-2)
+    g = out.float().reshape(nimg, H * W, groups, cout // groups)
+    want = torch.stack([g.sum(dim=(1, 3)), (g * g).sum(dim=(1, 3))], dim=-1).double()
+    assert (ops.groupnorm_stats_values(stats) - want).abs().max().item() <= 2e-4 * want.abs().max().item() + 1e-2
+    z = xl.float() @ w2.float().t() + b2
+    _report(f"split-{split} geglu", outg, z[:, :Fh] * F.gelu(z[:, Fh:]), 1e-2)
+    _report(f"split-{split} fp32 out", out32, xl.float() @ wl.float().t(), 1e-3)
+    for other in results[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(results[0], other))   # order-independent slice reduction
+    # without a workspace the call is rejected, nothing is launched
+    bad = ops.gemm(xl, wlp, out32, nimg=1, h=1, w_=M, c0=K, n=200, split_k=split)
+    with pytest.raises(Exception, match="workspace"):
+        bad(s)
+
+
 def test_gemm_rejects_bad_arguments(cuda_lib, b200sd):
     ops = b200sd.ops
     x = _rand(64, 60)

@@ -418,3 +418,62 @@ def test_sharded_generation_is_world_size_invariant(tmp_path, n_prompts):
     prompts = [f"prompt {'x' * i}" for i in range(n_prompts)]
     one = D.generate_sharded(FakePipe(), prompts, base_seed=1234, max_batch=2, num_inference_steps=2, width=16, height=16)
     assert np.array_equal(one.numpy(), r0)
+
+
+# ------------------------------------------------------------------------------------------------ robustness
+def test_server_rejects_bad_sizes_and_steps_before_the_gpu(b200sd):
+    from fastapi.testclient import TestClient
+    import importlib
+    server = importlib.import_module("k8s-nvidia-gpus_b200.server")
+    fake = FakePipe()
+    c = TestClient(server.create_app(pipe=fake))
+    for body in ({"prompt": "x", "width": 60}, {"prompt": "x", "height": 100000}, {"prompt": "x", "steps": 5000},
+                 {"prompt": "x", "guidance_scale": 1e9}):
+        assert c.post("/generate", json=body).status_code == 400, body
+    assert fake.calls == []                                   # nothing reached the pipeline
+    assert c.post("/generate", json={"prompt": "x", "width": 16, "height": 16, "steps": 2}).status_code == 200
+
+
+def test_scheduler_config_with_unsupported_options_is_refused(b200sd):
+    C = b200sd.checkpoint
+    base = {"_class_name": "PNDMScheduler", "beta_start": 0.00085, "beta_end": 0.012, "beta_schedule": "scaled_linear",
+            "skip_prk_steps": True, "steps_offset": 1, "set_alpha_to_one": False}
+    assert C.scheduler_config(base)["type"] == "pndm"
+    for k, v in (("timestep_spacing", "trailing"), ("skip_prk_steps", False), ("set_alpha_to_one", True),
+                 ("prediction_type", "v_prediction")):
+        with pytest.raises(NotImplementedError):
+            C.scheduler_config(dict(base, **{k: v}))
+    ddim = dict(base, _class_name="DDIMScheduler")
+    with pytest.raises(NotImplementedError):      # upstream DDIM default clip_sample=True must not load silently
+        C.scheduler_config(ddim)
+    assert C.scheduler_config(dict(ddim, clip_sample=False))["type"] == "ddim"
+    with pytest.raises(NotImplementedError):
+        C.scheduler_config(dict(base, _class_name="EulerDiscreteScheduler", use_karras_sigmas=True))
+
+
+def test_from_pretrained_never_falls_back_to_random_weights_silently(b200sd, monkeypatch):
+    """A hub id or a mistyped / unmounted path must raise, not serve noise (the pod's MODEL_ID default was a hub id).
+    The check runs before any CUDA work, so it is testable here."""
+    P = b200sd.pipeline
+    monkeypatch.delenv("B200SD_RANDOM_WEIGHTS", raising=False)
+    for bad in ("runwayml/stable-diffusion-v1-5", "/models/not-mounted"):
+        with pytest.raises(FileNotFoundError, match="random_init"):
+            P.StableDiffusionPipeline.from_pretrained(bad)
+
+
+def test_integration_md_ctypes_stub_runs(b200sd):
+    """The ctypes stub printed in INTEGRATION.md §4 is executed (up to the GPU call) against the built library: its
+    struct mirror must match sizeof(b200sd_gemm_params)."""
+    text = (ROOT / "INTEGRATION.md").read_text()
+    sec = text[text.index("## 4."):]
+    code = sec[sec.index("```python") + len("```python"):]
+    code = code[:code.index("```")]
+    head = code[:code.index("# --- GPU part")]
+    ns = {}
+    cwd = os.getcwd()
+    os.chdir(ROOT)
+    try:
+        exec(compile(head, "INTEGRATION.md#4", "exec"), ns)
+    finally:
+        os.chdir(cwd)
+    assert ns["ctypes"].sizeof(ns["GemmParams"]) == b200sd.lib.struct_sizes()[0]

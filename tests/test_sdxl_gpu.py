@@ -91,3 +91,60 @@ def test_sdxl_denoise_and_image_parity(tiny_xl, negative):
     psnr = [_psnr(out.images[i], ref["images"][i]) for i in range(len(PROMPTS))]
     print("xl PSNR", psnr)
     assert min(psnr) >= 30.0, psnr
+
+
+def test_sdxl_bf16_vae_beside_fp16_unet(tiny_xl, b200sd):
+    """Per-plan 16-bit type: the VAE decoder bound to the bfloat16 image of the library (what configs/sdxl.json and a
+    force_upcast checkpoint select - fp32's exponent range), the UNet and text encoders on the fp16 image, in one
+    pipeline.  Weights rounded to bf16 for both sides; image PSNR >= 30 dB against the fp32 oracle, latents as before."""
+    W, T, P = b200sd.weights, b200sd.tokenizer, b200sd.pipeline
+    from oracle.pipeline import OraclePipeline
+    cfg, oracle0, _ = tiny_xl
+    usd = W.random_state_dict(W.unet_schema(cfg["unet"]), 0)
+    vsd = W.random_state_dict(W.vae_decoder_schema(cfg["vae"]), 1, round_dtype=torch.bfloat16)
+    tsd = [W.random_state_dict(W.clip_text_schema(c), 2 + i) for i, c in enumerate(cfg["text_encoders"])]
+    oracle = OraclePipeline(cfg, usd, vsd, tsd, oracle0.tokenizers, eos_token_id=oracle0.eos_token_id)
+    pipe = P.StableDiffusionXLPipeline(cfg, usd, vsd, tsd, tokenizer=oracle0.tokenizers[0], vae_dtype="bf16")
+    assert pipe.vae_engine.variant == "bf16"
+    kw = dict(num_inference_steps=3, guidance_scale=5.0, width=64, height=64)
+    ref = oracle(PROMPTS, generator=_gens(), **kw)
+    out = pipe(PROMPTS, generator=_gens(), output_type="u8", **kw)
+    psnr = [_psnr(out.images[i], ref["images"][i]) for i in range(len(PROMPTS))]
+    print("xl bf16-VAE PSNR", psnr)
+    assert min(psnr) >= 30.0, psnr
+    # large-magnitude latents: fp16 would overflow inside the decoder (activations ~1e5), bf16 must stay finite
+    job = pipe.job(len(PROMPTS), 32, 32, 5.0, True, zero_negative=True)
+    job.latents.normal_(0, 3000.0)
+    job.vae_plan.run()
+    torch.cuda.synchronize()
+    assert torch.isfinite(pipe.vae_engine.last_rgb).all()
+
+
+def test_sdxl_full_size_one_step_vs_oracle(b200sd, cuda_lib):
+    """BASELINE.json configs[3] at FULL size: SDXL-base architecture (2.57 B-parameter UNet, CLIP-L + OpenCLIP-bigG,
+    VAE at 1024x1024 with its 16 384-token d=512 attention, bf16 decoder), one prompt, one Euler step + decode, against
+    the fp32 CPU oracle (about 8x the SD1.5 cost per evaluation - hence one step)."""
+    W, T, P = b200sd.weights, b200sd.tokenizer, b200sd.pipeline
+    from oracle.pipeline import OraclePipeline
+    cfg = W.load_config("sdxl")
+    usd = W.random_state_dict(W.unet_schema(cfg["unet"]), 0)
+    vsd = W.random_state_dict(W.vae_decoder_schema(cfg["vae"]), 1, round_dtype=torch.bfloat16)
+    tsd = [W.random_state_dict(W.clip_text_schema(c), 2 + i) for i, c in enumerate(cfg["text_encoders"])]
+    tok = T.CLIPTokenizer.synthetic(cfg["text_encoders"][0]["vocab_size"])
+    tok2 = copy.copy(tok)
+    tok2.pad_token_id = 0
+    pipe = P.StableDiffusionXLPipeline(cfg, usd, vsd, tsd, tokenizer=tok)
+    assert pipe.vae_engine.variant == "bf16"
+    kw = dict(num_inference_steps=1, guidance_scale=5.0, width=1024, height=1024)
+    steps = []
+    out = pipe(PROMPTS[0], generator=torch.Generator().manual_seed(1234), output_type="u8",
+               callback_on_step_end=lambda p, i, t, k: steps.append(k["latents"]), **kw)
+    img = out.images[0].copy()
+    del pipe
+    torch.cuda.empty_cache()
+    oracle = OraclePipeline(cfg, usd, vsd, tsd, [tok, tok2], eos_token_id=tok.eos_token_id)
+    ref = oracle(PROMPTS[0], generator=torch.Generator().manual_seed(1234), **kw)
+    rel = _rel(steps[0], ref["per_step"][0])
+    psnr = _psnr(img, ref["images"][0])
+    print("sdxl full size: latent rel err %.2e, PSNR %.1f dB" % (rel, psnr))
+    assert rel <= 1e-2 and psnr >= 30.0
