@@ -34,7 +34,8 @@ def write_diffusers_dir(root, cfg, unet_sd, vae_sd, text_sds, tokenizer_mod, dty
     _dump(os.path.join(root, "vae", "config.json"), {
         "_class_name": "AutoencoderKL", "latent_channels": v["latent_channels"], "out_channels": v["out_channels"],
         "in_channels": 3, "block_out_channels": v["block_out_channels"], "layers_per_block": v["layers_per_block"],
-        "norm_num_groups": v["norm_num_groups"], "scaling_factor": v["scaling_factor"]})
+        "norm_num_groups": v["norm_num_groups"], "scaling_factor": v["scaling_factor"],
+        "force_upcast": v.get("dtype") == "bf16"})
     _dump(os.path.join(root, "scheduler", "scheduler_config.json"), {
         "_class_name": scheduler_class, "beta_start": cfg["scheduler"]["beta_start"], "beta_end": cfg["scheduler"]["beta_end"],
         "beta_schedule": "scaled_linear", "num_train_timesteps": 1000, "steps_offset": 1, "skip_prk_steps": True,
