@@ -122,6 +122,20 @@ typedef struct {
   int32_t split_k;
   void* workspace;
   int64_t workspace_bytes;
+  /* LayerNorm folded into the layers around it (nn.LayerNorm norm1-3 of BasicTransformerBlock; K9): no normalised
+   * tensor is written or re-read.
+   *   ln_out_stats: the PRODUCER of a LayerNorm input adds sum and sum of squares of every output row to
+   *       ln_out_stats [M, B200SD_GN_STATS_WORDS 4-byte words] (same integer format as the GroupNorm statistics; the
+   *       caller zeroes it; sums over the rounded 16-bit outputs, all column tiles of the row).
+   *   ln_in_stats + ln_colsum + ln_eps: the CONSUMER (a linear layer whose input x is to be normalised) runs on the
+   *       RAW x with weights W' = gamma (.) W and computes
+   *           out[m, n] = rstd_m * (x W'^T)[m, n] - rstd_m * mean_m * ln_colsum[n] + bias[n]
+   *       with (mean_m, rstd_m) from ln_in_stats (c0 = the normalised width), ln_colsum[n] = sum_k W'[n, k] (of the
+   *       16-bit weights as stored) and bias = b + W beta precomputed by the caller.  Exact in real arithmetic. */
+  void* ln_out_stats;
+  const void* ln_in_stats;
+  const float* ln_colsum;
+  float ln_eps;
 } b200sd_gemm_params;
 int b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream stream);
 /* bytes of split-K workspace these parameters need (0 when split_k <= 1 or the parameters are rejected) */

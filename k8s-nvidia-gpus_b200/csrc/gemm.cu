@@ -89,6 +89,13 @@ struct alignas(64) GemmDev {
   int ld_rowbias;
   int act;
   float alpha;
+  // LayerNorm folded into the GEMM on both sides (b200sd.h: ln_*):
+  //   consumer: out = rstd_m * acc_mn - rstd_m * mean_m * ln_colsum[n] + bias[n], (mean, rstd) of A's row m from ln_in
+  //   producer: sum / sum of squares of every OUTPUT row added to ln_out (the next LayerNorm's input statistics)
+  const unsigned long long* ln_in;
+  unsigned long long* ln_out;
+  const float* ln_colsum;
+  float ln_inv_k, ln_eps;
   // split-K: the reduction of every tile is cut into split_k slices that run as separate work units (on different
   // CTAs when there are CTAs to spare); each unit writes its raw fp32 accumulator tile to `ws`, the unit that arrives
   // last at the tile's counter adds the slices IN INDEX ORDER (so the result does not depend on who arrives when) and
@@ -392,6 +399,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         ws_tile = p.ws + (static_cast<size_t>(tile) * p.split_k * kBlockM + r) * p.BN;
       }
 
+      // global row index of my accumulator row (row-major over [nimg, H, W]); used by the folded LayerNorm
+      const long long grow = (static_cast<long long>(n0 + in) * p.H + (h0 + ih)) * p.W + (w0 + iw);
+      // folded LayerNorm, consumer side: my row's mean and 1/std from the producer's integer sums
+      float ln_a = 1.f, ln_b = 0.f;
+      if (p.ln_in != nullptr && gn_row_ok) {
+        const unsigned long long* sl = p.ln_in + grow * kGnSlotWords64;
+        const ulonglong2 a2 = __ldcg(reinterpret_cast<const ulonglong2*>(sl));
+        const ulonglong2 b2 = __ldcg(reinterpret_cast<const ulonglong2*>(sl + 2));
+        const unsigned long long sw2[2] = {a2.x, a2.y}, qw2[2] = {b2.x, b2.y};
+        const double m = fixed_value(sw2) * static_cast<double>(p.ln_inv_k);
+        const double var = fmax(fixed_value(qw2) * static_cast<double>(p.ln_inv_k) - m * m, 0.0);
+        ln_a = rsqrtf(static_cast<float>(var) + p.ln_eps);
+        ln_b = -ln_a * static_cast<float>(m);
+      }
+
       // accumulator columns [ac, ac+32) -> f[] = alpha * acc + bias
       auto load_chunk = [&](int ac, float(&f)[32]) {
         uint32_t v[32];
@@ -420,6 +442,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         } else {
 #pragma unroll
           for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(v[k]);
+        }
+        if (p.ln_in != nullptr) {
+          // LN(x) W^T = rstd * (x (gamma W)^T) - rstd * mean * colsum(gamma W)   (+ W beta + b, folded into bias)
+          const int col = col0 + ac;
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            const float sn = (col + k < p.N) ? __ldg(p.ln_colsum + col + k) : 0.f;
+            f[k] = fmaf(f[k], ln_a, ln_b * sn);
+          }
         }
         if (p.bias != nullptr) {
           const int col = col0 + ac;
@@ -518,6 +549,27 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           } else {
 #pragma unroll
             for (int k = 0; k < 16; ++k) w[hh * 16 + k] = pack_act2(f[2 * k], f[2 * k + 1]);
+          }
+        }
+        if (!kOutF32) {
+          if (p.ln_out != nullptr) {
+            // folded LayerNorm, producer side: sum / sum of squares of my row's 64 (rounded) outputs of this group,
+            // added as integers to the row's slot (order-independent across column groups and tiles)
+            const int n_valid = (kGeglu ? p.N / 2 : p.N) - ocol0;
+            float rs = 0.f, rq = 0.f;
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+              const float2 v = unpack_act2(w[k]);
+              if (2 * k < n_valid) {
+                rs += v.x + v.y;
+                rq = fmaf(v.x, v.x, fmaf(v.y, v.y, rq));
+              }
+            }
+            if (gn_row_ok) {
+              unsigned long long* sl = p.ln_out + grow * kGnSlotWords64;
+              fixed_add_global(sl, rs);
+              fixed_add_global(sl + 2, rq);
+            }
           }
         }
         // staging tile free: residual consumed by everyone (kRes) / previous store has finished reading it
@@ -828,6 +880,22 @@ static int gemm_impl(const b200sd_gemm_params* hp, b200sd_stream stream_, size_t
   d.ld_rowbias = h.ld_rowbias;
   d.act = h.act;
   d.alpha = h.alpha;
+  if (h.ln_in_stats != nullptr) {
+    B200SD_REQUIRE(h.ln_colsum != nullptr && h.ksize == 1 && !custom && h.c1 == 0 && h.rowbias == nullptr &&
+                       h.alpha == 1.f && aligned16(h.ln_in_stats),
+                   B200SD_ERR_BAD_ARGUMENT,
+                   "gemm: a folded LayerNorm input needs ln_colsum, a plain linear / 1x1 layer over one source, no "
+                   "rowbias and alpha = 1");
+    d.ln_in = static_cast<const unsigned long long*>(h.ln_in_stats);
+    d.ln_colsum = h.ln_colsum;
+    d.ln_inv_k = 1.f / static_cast<float>(h.c0);
+    d.ln_eps = h.ln_eps;
+  }
+  if (h.ln_out_stats != nullptr) {
+    B200SD_REQUIRE(!f32 && aligned16(h.ln_out_stats), B200SD_ERR_BAD_ARGUMENT,
+                   "gemm: row statistics (ln_out_stats) need a 16-bit output");
+    d.ln_out = static_cast<unsigned long long*>(h.ln_out_stats);
+  }
   {
     // split-K workspace: [tiles] int32 counters (padded to 256 B), then [tiles][split][128][BN] fp32 slices
     const size_t ntiles = static_cast<size_t>(d.tiles_m) * d.tiles_ncol;

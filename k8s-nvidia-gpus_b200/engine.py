@@ -18,10 +18,11 @@ from . import ops
 class Act:
     """NHWC 16-bit activation: tensor [nimg, h, w, c] (contiguous).  `stats` = (statistics scratch slice, groups) when
     the kernel that produced it also accumulated its GroupNorm statistics (fused into the GEMM epilogue)."""
-    __slots__ = ("t", "nimg", "h", "w", "c", "stats")
+    __slots__ = ("t", "nimg", "h", "w", "c", "stats", "rowstats")
 
-    def __init__(self, t, nimg, h, w, c, stats=None):
+    def __init__(self, t, nimg, h, w, c, stats=None, rowstats=None):
         self.t, self.nimg, self.h, self.w, self.c, self.stats = t, nimg, h, w, c, stats
+        self.rowstats = rowstats  # per-row (sum, sum of squares) slots filled by the producing GEMM (folded LayerNorm)
 
     @property
     def hw(self):
@@ -126,6 +127,25 @@ class DeviceWeights:
             return torch.stack(ops.pack_upconv_weights(self.raw(name + ".weight")))
         return self._get(("upconv", name), f)
 
+    def ln_linear(self, ln_name, names, key=None, perm=None, bias=True):
+        """A linear layer (row-concatenated `names`) with the preceding LayerNorm `ln_name` folded in (b200sd.h, ln_*):
+        returns (packed W' = gamma (.) W, bias' = b + W beta (fp32), colsum[n] = sum_k W'[n, k] of the ROUNDED weights)."""
+        def f():
+            w = torch.cat([self.raw(n + ".weight") for n in names], dim=0)
+            b = (torch.cat([self.raw(n + ".bias") for n in names], dim=0) if bias
+                 else torch.zeros(w.shape[0], dtype=torch.float32, device=w.device))
+            gamma, beta = self.raw(ln_name + ".weight"), self.raw(ln_name + ".bias")
+            b = b + w @ beta
+            wq = (w * gamma[None, :]).to(ops.act_dtype())
+            if perm is not None:
+                wq, b = wq[perm], b[perm]
+            return {"w": ops.pack_linear_weight(wq.float()), "b": b.contiguous(),
+                    "s": wq.float().sum(dim=1).contiguous()}
+        key = ("lnlin", ln_name, tuple(names), key)
+        if key not in self.cache:
+            self.cache[key] = {k: v.to(self.device) for k, v in f().items()}
+        return self.cache[key]
+
     def vec(self, name):
         return self._get(("vec", name), lambda: self.raw(name).contiguous())
 
@@ -134,7 +154,7 @@ class DeviceWeights:
 
 
 class Builder:
-    def __init__(self, device, stats_words: int = 1 << 21, fuse_gn_stats: bool = False):
+    def __init__(self, device, stats_words: int = 1 << 22, fuse_gn_stats: bool = False):
         """fuse_gn_stats: let long-reduction 3x3 convs accumulate the GroupNorm statistics of their output in the
         epilogue.  Measured: the VAE decoder gains 9 % (its statistics passes stream 0.5 GB tensors), the UNet step
         about 1 % (43 of 61 passes go, the conv epilogues get longer)."""
@@ -143,9 +163,9 @@ class Builder:
         self.plan = Plan()
         self.pool = {}
         # GroupNorm statistics scratch of the whole plan (4-byte words; one memset per run)
-        self.stats = torch.zeros(stats_words, dtype=torch.int32, device=device)
-        self.stats_off = 0
-        self.plan.keep.append(self.stats)
+        # (handed out in chunks of stats_words; every used chunk is zeroed by one memset at the start of the plan)
+        self.stats_words = stats_words
+        self.stat_chunks = []   # [tensor, words used]
         # split-K policy (b200sd.h, split_k): "shape" (default) cuts the long reductions of the 8x8-level convolutions
         # into 3 slices - a function of the per-image shape only, so an image's bytes do not depend on the batch it
         # rides in; "auto" sizes the split from the tile count of the actual launch (best at batch 1-2, gives up that
@@ -185,10 +205,16 @@ class Builder:
         self.plan.calls.append(call)
 
     def stats_slice(self, nimg, groups):
+        """Zero-at-plan-start statistics slots: nimg * groups of them (GroupNorm: (image, group); folded LayerNorm:
+        (row, 1))."""
         nst = nimg * groups * L.GN_STATS_WORDS
-        assert self.stats_off + nst <= self.stats.numel(), "GroupNorm statistics scratch exhausted"
-        st = self.stats[self.stats_off:self.stats_off + nst]
-        self.stats_off += nst
+        if not self.stat_chunks or self.stat_chunks[-1][1] + nst > self.stat_chunks[-1][0].numel():
+            t = torch.zeros(max(self.stats_words, nst), dtype=torch.int32, device=self.device)
+            self.plan.keep.append(t)
+            self.stat_chunks.append([t, 0])
+        ch = self.stat_chunks[-1]
+        st = ch[0][ch[1]:ch[1] + nst]
+        ch[1] += nst
         return st
 
     @staticmethod
@@ -222,13 +248,14 @@ class Builder:
             for c in self.split_calls:
                 c.params.workspace, c.params.workspace_bytes = ws.data_ptr(), ws.numel() * 4
             self.split_calls = []
-        if self.stats_off:
-            self.plan.calls.insert(0, ops.memset_zero(self.stats, self.stats_off * 4))
+        for t, used in self.stat_chunks:
+            if used:
+                self.plan.calls.insert(0, ops.memset_zero(t, used * 4))
         return self.plan
 
     # ------------------------------------------------------------------ layers
     def conv(self, W: DeviceWeights, name, x, cout, ksize, *, bias=True, rowbias=None, ld_rowbias=0, residual=None,
-             act=L.ACT_NONE, out_dtype=None, out=None, ldc=None, wsplit=None, gn_groups=None):
+             act=L.ACT_NONE, out_dtype=None, out=None, ldc=None, wsplit=None, gn_groups=None, rowstats=False):
         """x: Act or (Act, Act) virtual concat.  Returns Act [nimg, h, w, cout].  gn_groups: also accumulate the
         GroupNorm statistics of the output in the epilogue (long reductions only - a 3x3 conv hides it completely;
         tiles must hold >= 32 pixels of an image, see b200sd.h)."""
@@ -251,13 +278,17 @@ class Builder:
                                a1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c, bias=b, rowbias=rowbias,
                                ld_rowbias=ld_rowbias, residual=None if residual is None else residual.t,
                                ldr=0 if residual is None else residual.c, ldc=ldc, act=act, gn_stats=st,
-                               gn_groups=gn_groups if st is not None else 0, split_k=sk), sk)
+                               gn_groups=gn_groups if st is not None else 0, split_k=sk,
+                               ln_out_stats=(rs := self.stats_slice(a0.rows, 1) if rowstats else None)), sk)
         return Act(out, a0.nimg, a0.h, a0.w, cout if ldc is None else ldc,
-                   stats=None if st is None else (st, gn_groups))
+                   stats=None if st is None else (st, gn_groups), rowstats=rs)
 
     def linear_w(self, x: Act, w, b, n, *, residual=None, act=L.ACT_NONE, out_dtype=None, rowbias=None,
-                 ld_rowbias=0, per_image_rows=False):
-        """Linear layer over the rows of x with an already packed weight."""
+                 ld_rowbias=0, per_image_rows=False, rowstats=False, ln=None, ln_eps=1e-5):
+        """Linear layer over the rows of x with an already packed weight.  rowstats: also emit the per-row statistics of
+        the output (it feeds a folded LayerNorm).  ln: colsum vector - x is the RAW input of a LayerNorm folded into
+        this layer (w, b from DeviceWeights.ln_linear; x.rowstats from its producer)."""
+        assert ln is None or x.rowstats is not None, "folded LayerNorm: the input carries no row statistics"
         n_out = n // 2 if act == L.ACT_GEGLU else n
         out = self.alloc((x.nimg, x.h, x.w, n_out), out_dtype)
         if per_image_rows:
@@ -268,11 +299,19 @@ class Builder:
         self.add_gemm(ops.gemm(x.t, w, out, c0=x.c, n=n, ksize=1, bias=b,
                                residual=None if residual is None else residual.t,
                                ldr=0 if residual is None else residual.c, act=act, rowbias=rowbias,
-                               ld_rowbias=ld_rowbias, split_k=sk, **geo), sk)
-        return Act(out, x.nimg, x.h, x.w, n_out)
+                               ld_rowbias=ld_rowbias, split_k=sk,
+                               ln_out_stats=(rs := self.stats_slice(x.rows, 1) if rowstats else None),
+                               ln_in_stats=x.rowstats if ln is not None else None, ln_colsum=ln, ln_eps=ln_eps,
+                               **geo), sk)
+        return Act(out, x.nimg, x.h, x.w, n_out, rowstats=rs)
 
     def linear(self, W: DeviceWeights, name, x: Act, n, *, bias=True, **kw):
         return self.linear_w(x, W.conv(name), W.vec(name + ".bias") if bias else None, n, **kw)
+
+    def ln_linear(self, W: DeviceWeights, ln_name, names, x: Act, n, *, bias=True, key=None, perm=None, eps=1e-5, **kw):
+        """LayerNorm(ln_name) -> Linear(names...) without a normalised tensor: see b200sd.h (ln_*)."""
+        f = W.ln_linear(ln_name, names, key=key, perm=perm, bias=bias)
+        return self.linear_w(x, f["w"], f["b"], n, ln=f["s"], ln_eps=eps, **kw)
 
     def groupnorm(self, W: DeviceWeights, name, x, groups, eps, silu):
         xs = x if isinstance(x, tuple) else (x,)

@@ -32,7 +32,8 @@ class GemmParams(C.Structure):
                 ("out_dtype", i32), ("bn_hint", i32), ("alpha", f32), ("gn_stats", vp), ("gn_groups", i32),
                 ("gn_rows_per_img", i32), ("kh", i32), ("kw", i32), ("off_h", i32), ("off_w", i32), ("stride", i32),
                 ("out_pix_stride", i32), ("out_row_stride", i32), ("out_img_stride", i32), ("split_k", i32),
-                ("workspace", vp), ("workspace_bytes", i64)]
+                ("workspace", vp), ("workspace_bytes", i64), ("ln_out_stats", vp), ("ln_in_stats", vp),
+                ("ln_colsum", vp), ("ln_eps", f32)]
 
 
 class AttnParams(C.Structure):

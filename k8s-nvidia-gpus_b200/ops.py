@@ -80,7 +80,7 @@ def geglu_perm(n2: int) -> torch.Tensor:
 def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld1=None, bias=None, rowbias=None,
          ld_rowbias=0, residual=None, ldr=0, ldc=None, act=L.ACT_NONE, out_dtype=None, alpha=1.0, bn_hint=0,
          gn_stats=None, gn_groups=0, gn_rows_per_img=0, kh=0, kw=0, off_h=0, off_w=0, stride=0, out_strides=None,
-         split_k=0, workspace=None):
+         split_k=0, workspace=None, ln_out_stats=None, ln_in_stats=None, ln_colsum=None, ln_eps=1e-5):
     """out_strides: (pixel, row, image) strides of the output in elements when its pixels are interleaved into a larger
     tensor (pass the strided VIEW as `out`: its data_ptr is the first pixel)."""
     p = L.GemmParams()
@@ -105,9 +105,11 @@ def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld
     if out_strides is not None:
         p.out_pix_stride, p.out_row_stride, p.out_img_stride = out_strides
     p.split_k = split_k
+    p.ln_out_stats, p.ln_in_stats, p.ln_colsum, p.ln_eps = _ptr(ln_out_stats), _ptr(ln_in_stats), _ptr(ln_colsum), ln_eps
     if workspace is not None:
         p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()
-    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual, gn_stats, workspace))
+    return L.Call("b200sd_gemm", p, keep=(a0, a1, w, out, bias, rowbias, residual, gn_stats, workspace, ln_out_stats,
+                                          ln_in_stats, ln_colsum))
 
 
 def gemm_workspace_bytes(call) -> int:

@@ -57,6 +57,9 @@ class UNetEngine:
         self.device = torch.device(device)
         self.W = DeviceWeights(state_dict, self.device)
         self.seq = 77
+        # LayerNorm folded into the neighbouring GEMMs (no layernorm kernel in the denoise step); B200SD_UNET_FOLD_LN=0
+        # brings the standalone kernel back for A/B measurements
+        self.fold_ln = os.environ.get("B200SD_UNET_FOLD_LN", "1") == "1"
 
     # ------------------------------------------------------------------ prompt-dependent precompute
     def build_kv_plan(self, nctx: int, ctx, text_embeds: torch.Tensor | None = None,
@@ -150,35 +153,48 @@ class UNetEngine:
             c = x.c
             d = c // nheads
             gn = bld.groupnorm(W, p + ".norm", x, g, 1e-6, silu=False)
-            t = bld.conv(W, p + ".proj_in", gn, c, 1)
+            # Every LayerNorm of the block is folded into the layers around it (engine.Builder.ln_linear): its producer
+            # emits per-row statistics, its consumer runs on the raw residual stream with gamma-scaled weights.
+            fold = self.fold_ln
+            t = bld.conv(W, p + ".proj_in", gn, c, 1, rowstats=fold)
             bld.free(gn)
             for l in range(ndepth):
                 b = f"{p}.transformer_blocks.{l}"
-                ln = bld.layernorm(W, b + ".norm1", t)
-                qkv = bld.linear_w(ln, W.cat_linear([b + ".attn1.to_q", b + ".attn1.to_k", b + ".attn1.to_v"]), None,
-                                   3 * c)
-                bld.free(ln)
+                qkv_names = [b + ".attn1.to_q", b + ".attn1.to_k", b + ".attn1.to_v"]
+                if fold:
+                    qkv = bld.ln_linear(W, b + ".norm1", qkv_names, t, 3 * c, bias=False)
+                else:
+                    ln = bld.layernorm(W, b + ".norm1", t)
+                    qkv = bld.linear_w(ln, W.cat_linear(qkv_names), None, 3 * c)
+                    bld.free(ln)
                 q2 = qkv.t.view(-1, 3 * c)
                 a = bld.attention(q2, q2[:, c:], q2[:, 2 * c:], batch=n, heads=nheads, nq=x.hw, nk=x.hw, d=d, ldq=3 * c,
                                   ldk=3 * c, ldv=3 * c, like=t)
                 bld.free(qkv)
-                t2 = bld.linear(W, b + ".attn1.to_out.0", a, c, residual=t)
+                t2 = bld.linear(W, b + ".attn1.to_out.0", a, c, residual=t, rowstats=fold)
                 bld.free(a, t)
-                ln = bld.layernorm(W, b + ".norm2", t2)
-                q = bld.linear(W, b + ".attn2.to_q", ln, c, bias=False)
-                bld.free(ln)
+                if fold:
+                    q = bld.ln_linear(W, b + ".norm2", [b + ".attn2.to_q"], t2, c, bias=False)
+                else:
+                    ln = bld.layernorm(W, b + ".norm2", t2)
+                    q = bld.linear(W, b + ".attn2.to_q", ln, c, bias=False)
+                    bld.free(ln)
                 kvt = kv[b + ".attn2"].view(-1, 2 * c)
                 a = bld.attention(q.t, kvt, kvt[:, c:], batch=n, heads=nheads, nq=x.hw, nk=self.seq, d=d, ldq=c,
                                   ldk=2 * c, ldv=2 * c, like=t2)
                 bld.free(q)
-                t3 = bld.linear(W, b + ".attn2.to_out.0", a, c, residual=t2)
+                t3 = bld.linear(W, b + ".attn2.to_out.0", a, c, residual=t2, rowstats=fold)
                 bld.free(a, t2)
-                ln = bld.layernorm(W, b + ".norm3", t3)
                 perm = ops.geglu_perm(8 * c)
-                hg = bld.linear_w(ln, W.cat_linear([b + ".ff.net.0.proj"], "geglu", perm),
-                                  W.cat_bias([b + ".ff.net.0.proj"], "geglu", perm), 8 * c, act=L.ACT_GEGLU)
-                bld.free(ln)
-                t = bld.linear(W, b + ".ff.net.2", hg, c, residual=t3)
+                if fold:
+                    hg = bld.ln_linear(W, b + ".norm3", [b + ".ff.net.0.proj"], t3, 8 * c, key="geglu", perm=perm,
+                                       act=L.ACT_GEGLU)
+                else:
+                    ln = bld.layernorm(W, b + ".norm3", t3)
+                    hg = bld.linear_w(ln, W.cat_linear([b + ".ff.net.0.proj"], "geglu", perm),
+                                      W.cat_bias([b + ".ff.net.0.proj"], "geglu", perm), 8 * c, act=L.ACT_GEGLU)
+                    bld.free(ln)
+                t = bld.linear(W, b + ".ff.net.2", hg, c, residual=t3, rowstats=fold and l + 1 < ndepth)
                 bld.free(hg, t3)
             out = bld.conv(W, p + ".proj_out", t, c, 1, residual=x)
             bld.free(t)

@@ -353,6 +353,44 @@ def test_split_k_conv_and_linear(cuda_lib, b200sd, split):
         bad(s)
 
 
+@pytest.mark.parametrize("M,C,N,geglu", [(4096, 320, 960, False), (1000, 640, 640, False), (4096, 320, 2560, True),
+                                         (300, 1280, 10240, True)])
+def test_layernorm_folded_into_producer_and_consumer(cuda_lib, b200sd, M, C, N, geglu):
+    """nn.LayerNorm between two linear layers without a normalised tensor: the producer (linear + residual) adds every
+    output row's sum / sum of squares to integer slots, the consumer runs on the raw rows with gamma-scaled weights and
+    applies rstd_m * acc - rstd_m * mean_m * colsum_n + (b + W beta) in its epilogue - against
+    F.linear(F.layer_norm(y)) (and GEGLU of it) on the same 16-bit-rounded y."""
+    torch.manual_seed(40)
+    ops, L = b200sd.ops, b200sd.lib
+    s = ops.current_stream()
+    x0, res = _rand(M, C), _rand(M, C, scale=2.0)
+    w0, b0 = _rand(C, C, scale=C ** -0.5), torch.randn(C, device="cuda")
+    y = torch.empty(M, C, device="cuda", dtype=ACT())
+    rows = ops.groupnorm_stats_buffer(M, 1)
+    ops.gemm(x0, ops.pack_linear_weight(w0.float().cpu()).cuda(), y, nimg=1, h=1, w_=M, c0=C, n=C, bias=b0, residual=res,
+             ln_out_stats=rows)(s)
+    torch.cuda.synchronize()
+    yf = y.float()
+    want = torch.stack([yf.sum(dim=1), (yf * yf).sum(dim=1)], dim=-1).double()[:, None, :]
+    got = ops.groupnorm_stats_values(rows)
+    assert ((got - want).abs() <= 1e-5 * want.abs() + 1e-3).all()
+    # consumer
+    gamma, beta = torch.randn(C, device="cuda") * 0.5 + 1.0, torch.randn(C, device="cuda") * 0.3
+    w1, b1 = _rand(N, C, scale=C ** -0.5).float(), torch.randn(N, device="cuda")
+    wq = (w1 * gamma[None, :]).to(ACT())
+    bq = b1 + w1 @ beta
+    colsum = wq.float().sum(dim=1).contiguous()
+    perm = ops.geglu_perm(N).cuda() if geglu else torch.arange(N, device="cuda")
+    out = torch.empty(M, N // 2 if geglu else N, device="cuda", dtype=ACT())
+    ops.gemm(y, ops.pack_linear_weight(wq.float().cpu()[perm.cpu()]).cuda(), out, nimg=1, h=1, w_=M, c0=C, n=N,
+             bias=bq[perm].contiguous(), act=L.ACT_GEGLU if geglu else L.ACT_NONE, ln_in_stats=rows,
+             ln_colsum=colsum[perm].contiguous(), ln_eps=1e-5)(s)
+    torch.cuda.synchronize()
+    z = F.linear(F.layer_norm(yf, (C,), gamma, beta, 1e-5), w1, b1)
+    ref = z[:, :N // 2] * F.gelu(z[:, N // 2:]) if geglu else z
+    _report(f"LN folded {M}x{C}x{N} geglu={geglu}", out, ref, 1e-2)
+
+
 def test_gemm_rejects_bad_arguments(cuda_lib, b200sd):
     ops = b200sd.ops
     x = _rand(64, 60)
