@@ -28,6 +28,8 @@
 //   softmax warps then wait for V to land) and an extra P x ONES product with N = 16 (0.843 ms) against 0.735 ms -
 //   every tcgen05.mma re-reads its 128 x 16 A slice (4 KB) from shared memory whatever N is, and the shared-memory
 //   port (operand reads + P stores + TMA writes) is as loaded as the MUFU pipe in this kernel.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "host.cuh"
 
@@ -439,6 +441,14 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
                  "attention: pointers must be 16-byte aligned");
   B200SD_REQUIRE(h.heads <= 65535 && h.batch <= 65535, B200SD_ERR_TOO_LARGE, "attention: grid too large");
   B200SD_REQUIRE(h.scale > 0.f, B200SD_ERR_BAD_ARGUMENT, "attention: scale must be positive");
+  if (!h.causal && h.nk <= 128) {
+    // the whole key set is one tile (cross-attention against the 77 text tokens): persistent short-KV kernel
+    const char* sw = getenv("B200SD_XATTN");  // "0": general kernel (A/B measurements)
+    if (sw == nullptr || sw[0] != '0') {
+      const int rc = launch_cross_attention(h, di, static_cast<cudaStream_t>(stream_));
+      if (rc <= 0) return rc;
+    }
+  }
 
   AttnDev d;
   memset(&d, 0, sizeof(d));

@@ -53,12 +53,14 @@ struct alignas(64) XAttnDev {
   float scale_log2;
 };
 
+// non-blocking phase test (try_wait may park the thread for a system-dependent time before it answers "not yet" -
+// a polling scheduler must not)
 __device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {
   uint32_t done;
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
       "selp.b32 %0, 1, 0, p;\n"
       "}\n"
       : "=r"(done)
@@ -73,7 +75,10 @@ __device__ __forceinline__ float x_ex2(float x) {
   return y;
 }
 
-__global__ void __launch_bounds__(128 + 128 * kXMaxPipes, 1) xattn_kernel(const __grid_constant__ XAttnDev p) {
+// kCh: 16-column score chunks a row holds in registers (5 = up to 80 keys: the 77 text tokens; 8 = up to 128 keys);
+// kPipes: most pipelines the launch may use (sets the register budget per thread).
+template <int kCh, int kPipes>
+__global__ void __launch_bounds__(128 + 128 * kPipes, 1) xattn_kernel(const __grid_constant__ XAttnDev p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[kXNumBars];
   __shared__ uint32_t tmem_base_s;
@@ -240,14 +245,14 @@ __global__ void __launch_bounds__(128 + 128 * kXMaxPipes, 1) xattn_kernel(const 
       mbar_wait_spin(bar0 + 8 * (kXSFull + pipe), use & 1);
       tc_fence_after();
       // the whole score row: up to 128 fp32 (only the chunks that exist are loaded)
-      uint32_t sc[8][16];
+      uint32_t sc[kCh][16];
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
+      for (int c = 0; c < kCh; ++c)
         if (c < nchunks) tmem_ld16(tS + c * 16, sc[c]);
       tmem_ld_wait();
       float mx = -INFINITY;
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
+      for (int c = 0; c < kCh; ++c)
         if (c < nchunks) {
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
@@ -258,7 +263,7 @@ __global__ void __launch_bounds__(128 + 128 * kXMaxPipes, 1) xattn_kernel(const 
       const float mb = mx * p.scale_log2;
       float sum = 0.f;
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
+      for (int c = 0; c < kCh; ++c)
         if (c < nchunks) {
           uint32_t w[8];
 #pragma unroll
@@ -324,13 +329,18 @@ struct XAttnLaunch {
 // nk <= 128, not causal: the persistent short-KV kernel.  Returns B200SD_OK after launching, or a positive value when
 // the shape does not fit (the caller then uses the general kernel).
 int launch_cross_attention(const b200sd_attn_params& h, const DeviceInfo& di, cudaStream_t stream) {
-  if (int e = ensure_dyn_smem(reinterpret_cast<const void*>(&xattn_kernel), di.max_smem_optin - 512)) return e;
-  XAttnLaunch L;
-  if (launch_cache_get(2, &h, sizeof(h), &L, sizeof(L))) {
-    xattn_kernel<<<L.grid, L.threads, L.smem_bytes, stream>>>(L.d);
+  if (int e = ensure_dyn_smem(reinterpret_cast<const void*>(&xattn_kernel<5, 3>), di.max_smem_optin - 512)) return e;
+  if (int e = ensure_dyn_smem(reinterpret_cast<const void*>(&xattn_kernel<8, 2>), di.max_smem_optin - 512)) return e;
+  auto launch = [&](const XAttnLaunch& X) -> int {
+    if (X.d.KP <= 80)
+      xattn_kernel<5, 3><<<X.grid, X.threads, X.smem_bytes, stream>>>(X.d);
+    else
+      xattn_kernel<8, 2><<<X.grid, X.threads, X.smem_bytes, stream>>>(X.d);
     B200SD_CUDA_CHECK(cudaGetLastError());
     return B200SD_OK;
-  }
+  };
+  XAttnLaunch L;
+  if (launch_cache_get(2, &h, sizeof(h), &L, sizeof(L))) return launch(L);
   memset(&L, 0, sizeof(L));
   XAttnDev& d = L.d;
   d.out = static_cast<act_t*>(h.out);
@@ -351,7 +361,7 @@ int launch_cross_attention(const b200sd_attn_params& h, const DeviceInfo& di, cu
   const int kv_bytes = d.nd * d.KP * 128;
   const int per_pipe = d.nd * static_cast<int>(kXQAtom) + ceil_div(d.KP, 64) * static_cast<int>(kXQAtom);
   const int budget = di.max_smem_optin - 2048 - 4 * kv_bytes;
-  d.np = min(kXMaxPipes, min(512 / d.tstride, budget / per_pipe));
+  d.np = min(d.KP <= 80 ? 3 : 2, min(512 / d.tstride, budget / per_pipe));
   if (d.np < 1) return 1;
   L.grid = min(d.items, di.sm_count);
   d.ipc = ceil_div(d.items, L.grid);
@@ -371,9 +381,7 @@ int launch_cross_attention(const b200sd_attn_params& h, const DeviceInfo& di, cu
   if (int e = enc(&d.tmK, h.k, h.nk, h.ldk, static_cast<uint32_t>(d.KP))) return e;
   if (int e = enc(&d.tmV, h.v, h.nk, h.ldv, static_cast<uint32_t>(d.KP))) return e;
   launch_cache_put(2, &h, sizeof(h), &L, sizeof(L));
-  xattn_kernel<<<L.grid, L.threads, L.smem_bytes, stream>>>(d);
-  B200SD_CUDA_CHECK(cudaGetLastError());
-  return B200SD_OK;
+  return launch(L);
 }
 
 }  // namespace b200sd

@@ -102,7 +102,7 @@ struct alignas(64) GemmDev {
   // runs the epilogue.  Counters are zero at rest (the finishing unit re-arms its tile).
   int split_k;
   FastDiv div_split;
-  float* ws;   // [tiles][split_k][128][BN] fp32
+  float* ws;   // [tiles][split_k] fp32 slices of 128 x BN, each stored [BN / 32 chunks][8 pieces][128 rows][4]
   int* cnt;    // [tiles]
 };
 
@@ -368,14 +368,18 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       // ---- split-K: park this unit's raw accumulator tile, count it, and go on unless it was the last slice
       const float* ws_tile = nullptr;
       if (p.split_k > 1) {
-        float* wrow = p.ws + ((static_cast<size_t>(tile) * p.split_k + split) * kBlockM + r) * p.BN;
+        // slice layout [32-column chunk][16-byte piece k][row] : the 32 lanes of a warp (consecutive rows) write 512
+        // contiguous bytes per store (row-major rows would make every lane's 16 bytes a request of its own: measured,
+        // the reduction then costs more than the split saves)
+        const size_t slice_u4 = static_cast<size_t>(kBlockM) * p.BN / 4;
+        uint4* wsl = reinterpret_cast<uint4*>(p.ws) + (static_cast<size_t>(tile) * p.split_k + split) * slice_u4 + r;
         for (int c = wg * 32; c < ncols; c += 64) {
           uint32_t v[32];
           tmem_ld32(taddr + c, v);
           tmem_ld_wait();
 #pragma unroll
           for (int k = 0; k < 8; ++k)
-            __stcg(reinterpret_cast<uint4*>(wrow + c) + k, make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]));
+            __stcg(wsl + ((c >> 5) * 8 + k) * kBlockM, make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]));
         }
         tc_fence_before();
         __syncwarp();
@@ -396,7 +400,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         named_bar_sync(3, 256);  // (split_last_s may be rewritten by the next unit only after everyone has read it)
         if (!last) continue;
         __threadfence();
-        ws_tile = p.ws + (static_cast<size_t>(tile) * p.split_k * kBlockM + r) * p.BN;
+        ws_tile = p.ws + (static_cast<size_t>(tile) * p.split_k * slice_u4 + r) * 4;
       }
 
       // global row index of my accumulator row (row-major over [nimg, H, W]); used by the folded LayerNorm
@@ -422,10 +426,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
 #pragma unroll
           for (int k = 0; k < 32; ++k) v[k] = 0u;
           for (int sl = 0; sl < p.split_k; ++sl) {
-            const uint4* src = reinterpret_cast<const uint4*>(ws_tile + static_cast<size_t>(sl) * kBlockM * p.BN + ac);
+            const uint4* src = reinterpret_cast<const uint4*>(ws_tile) + static_cast<size_t>(sl) * (kBlockM * p.BN / 4) +
+                               (ac >> 5) * 8 * kBlockM;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-              const uint4 u = __ldcg(src + k);
+              const uint4 u = __ldcg(src + k * kBlockM);
               v[4 * k + 0] = __float_as_uint(__uint_as_float(v[4 * k + 0]) + __uint_as_float(u.x));
               v[4 * k + 1] = __float_as_uint(__uint_as_float(v[4 * k + 1]) + __uint_as_float(u.y));
               v[4 * k + 2] = __float_as_uint(__uint_as_float(v[4 * k + 2]) + __uint_as_float(u.z));
@@ -446,10 +451,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         if (p.ln_in != nullptr) {
           // LN(x) W^T = rstd * (x (gamma W)^T) - rstd * mean * colsum(gamma W)   (+ W beta + b, folded into bias)
           const int col = col0 + ac;
+          if (col + 32 <= p.N) {
 #pragma unroll
-          for (int k = 0; k < 32; ++k) {
-            const float sn = (col + k < p.N) ? __ldg(p.ln_colsum + col + k) : 0.f;
-            f[k] = fmaf(f[k], ln_a, ln_b * sn);
+            for (int k = 0; k < 8; ++k) {
+              const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.ln_colsum + col) + k);
+              f[4 * k + 0] = fmaf(f[4 * k + 0], ln_a, ln_b * s4.x);
+              f[4 * k + 1] = fmaf(f[4 * k + 1], ln_a, ln_b * s4.y);
+              f[4 * k + 2] = fmaf(f[4 * k + 2], ln_a, ln_b * s4.z);
+              f[4 * k + 3] = fmaf(f[4 * k + 3], ln_a, ln_b * s4.w);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+              const float sn = (col + k < p.N) ? __ldg(p.ln_colsum + col + k) : 0.f;
+              f[k] = fmaf(f[k], ln_a, ln_b * sn);
+            }
           }
         }
         if (p.bias != nullptr) {
@@ -882,7 +898,7 @@ static int gemm_impl(const b200sd_gemm_params* hp, b200sd_stream stream_, size_t
   d.alpha = h.alpha;
   if (h.ln_in_stats != nullptr) {
     B200SD_REQUIRE(h.ln_colsum != nullptr && h.ksize == 1 && !custom && h.c1 == 0 && h.rowbias == nullptr &&
-                       h.alpha == 1.f && aligned16(h.ln_in_stats),
+                       h.alpha == 1.f && aligned16(h.ln_in_stats) && aligned16(h.ln_colsum),
                    B200SD_ERR_BAD_ARGUMENT,
                    "gemm: a folded LayerNorm input needs ln_colsum, a plain linear / 1x1 layer over one source, no "
                    "rowbias and alpha = 1");

@@ -56,6 +56,10 @@ int ensure_dyn_smem(const void* kernel, int bytes);
 bool launch_cache_get(int family, const void* params, size_t params_bytes, void* out, size_t out_bytes);
 void launch_cache_put(int family, const void* params, size_t params_bytes, const void* val, size_t val_bytes);
 
+// attention_cross.cu: persistent short-KV attention (nk <= 128, not causal).  B200SD_OK after launching, > 0 when the
+// shape does not fit that kernel (the caller falls through to the general flash kernel), < 0 on error.
+int launch_cross_attention(const b200sd_attn_params& h, const DeviceInfo& di, cudaStream_t stream);
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int pow2_ceil(int v) {

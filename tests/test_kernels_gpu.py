@@ -97,6 +97,15 @@ def test_softmax_rows(cuda_lib, b200sd):
     (3, 12, 77, 77, 64, True),       # CLIP causal
     (1, 2, 300, 300, 64, True),      # causal across tiles
     (1, 8, 4096, 4096, 40, False),   # SD1.5 64x64 level
+    # short-KV (nk <= 128, not causal): the persistent cross-attention kernel (attention_cross.cu)
+    (4, 8, 4096, 77, 40, False),     # SD1.5 64x64 cross-attention: 3 pipelines, many items per CTA
+    (2, 8, 1024, 77, 80, False),     # two d atoms, 2 pipelines
+    (2, 8, 256, 77, 160, False),     # three d atoms, 1 pipeline
+    (16, 8, 64, 77, 160, False),     # 8x8 level: one query tile per (batch, head) - a new K/V run every item
+    (2, 10, 300, 77, 64, False),     # SDXL head dim, ragged queries
+    (3, 4, 50, 5, 40, False),        # a handful of keys
+    (1, 2, 130, 128, 64, False),     # the most keys this kernel takes (8 score chunks)
+    (2, 3, 257, 100, 48, False),
 ])
 def test_attention(cuda_lib, b200sd, batch, heads, nq, nk, d, causal):
     torch.manual_seed(0)

@@ -78,6 +78,29 @@ def test_denoise_and_image_parity(tiny, kind, steps):
     assert min(psnr) >= 30.0, psnr
 
 
+def test_layernorm_fold_option_matches_oracle(b200sd, tiny, monkeypatch):
+    """B200SD_UNET_FOLD_LN=1: every LayerNorm of the UNet folded into the GEMMs around it (off by default - measured
+    slower on the SD1.5 step) gives the same latents / image as the oracle."""
+    cfg, oracle, _ = tiny
+    monkeypatch.setenv("B200SD_UNET_FOLD_LN", "1")
+    W, T, P = b200sd.weights, b200sd.tokenizer, b200sd.pipeline
+    usd = W.random_state_dict(W.unet_schema(cfg["unet"]), 0)
+    vsd = W.random_state_dict(W.vae_decoder_schema(cfg["vae"]), 1)
+    tsd = W.random_state_dict(W.clip_text_schema(cfg["text_encoders"][0]), 2)
+    pipe = P.StableDiffusionPipeline(cfg, usd, vsd, tsd, tokenizer=T.CLIPTokenizer.synthetic(cfg["text_encoders"][0]["vocab_size"]))
+    assert pipe.unet.fold_ln
+    ref = oracle(PROMPTS, num_inference_steps=3, guidance_scale=7.5, width=64, height=64, generator=_gens(),
+                 scheduler="ddim")
+    steps = []
+    out = pipe(PROMPTS, num_inference_steps=3, guidance_scale=7.5, width=64, height=64, generator=_gens(),
+               scheduler="ddim", output_type="u8", callback_on_step_end=lambda p, i, t, kw: steps.append(kw["latents"]))
+    assert not any(c.name == "b200sd_layernorm" for c in pipe.job(2, 32, 32, 7.5, True).step_plan.calls)
+    rels = [_rel(a, b) for a, b in zip(steps, ref["per_step"])]
+    print("LN-fold per-step latent rel err", ["%.2e" % r for r in rels])
+    assert max(rels) <= 1e-2
+    assert min(_psnr(out.images[i], ref["images"][i]) for i in range(2)) >= 30.0
+
+
 def test_single_prompt_single_generator_and_pil(tiny):
     """The exact call the reference server makes (configmap.yaml:105-112): one prompt, one generator, .images[0]."""
     cfg, oracle, pipe = tiny

@@ -291,3 +291,37 @@ def mode_sweep():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "sweep":
     mode_sweep()
+
+
+def mode_split():
+    """Split-K A/B on the 8x8-level convolutions (M = 1024 rows at batch 8): split_k = 1, 2, 3, 4, 6."""
+    import b200sd
+    ops = b200sd.ops
+    dt = b200sd.lib.act_dtype()
+    s = ops.current_stream()
+    for cin, cout, nimg, hw in [(1280, 1280, 16, 8), (2560, 1280, 16, 8), (1280, 1280, 2, 8), (1280, 1280, 2, 16)]:
+        x = torch.randn(nimg, hw, hw, cin, device="cuda").to(dt)
+        w = (torch.randn(cout, 9, cin, device="cuda") * (9 * cin) ** -0.5).to(dt)
+        out = torch.empty(nimg, hw, hw, cout, device="cuda", dtype=dt)
+        fl = 2.0 * nimg * hw * hw * cout * 9 * cin
+        for sk in (1, 2, 3, 4, 6, 8):
+            call = ops.gemm(x, w, out, nimg=nimg, h=hw, w_=hw, c0=cin, n=cout, ksize=3, split_k=sk)
+            if sk > 1:
+                need = ops.gemm_workspace_bytes(call)
+                ws = torch.zeros((need + 255) // 256 * 64, dtype=torch.int32, device="cuda")
+                call.params.workspace, call.params.workspace_bytes = ws.data_ptr(), ws.numel() * 4
+            for _ in range(3):
+                call(s)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                call(s)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / 20
+            print(f"conv3x3 {cin}->{cout} @{hw}x{hw} x{nimg} split_k={sk}: {ms * 1e3:7.1f} us  {fl / ms / 1e9:7.1f} TFLOP/s")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "split":
+    mode_split()
