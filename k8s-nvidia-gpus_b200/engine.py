@@ -154,12 +154,14 @@ class DeviceWeights:
 
 
 class Builder:
-    def __init__(self, device, stats_words: int = 1 << 22, fuse_gn_stats: bool = False):
+    def __init__(self, device, stats_words: int = 1 << 22, fuse_gn_stats: bool = False, gn_fuse_min_k: int = 24 * 64):
         """fuse_gn_stats: let long-reduction 3x3 convs accumulate the GroupNorm statistics of their output in the
         epilogue.  Measured: the VAE decoder gains 9 % (its statistics passes stream 0.5 GB tensors), the UNet step
         about 1 % (43 of 61 passes go, the conv epilogues get longer)."""
         self.device = device
         self.fuse_gn_stats = fuse_gn_stats
+        # shortest reduction (elements of K) whose conv epilogue also takes the GroupNorm statistics of its output
+        self.gn_fuse_min_k = gn_fuse_min_k
         self.plan = Plan()
         self.pool = {}
         # GroupNorm statistics scratch of the whole plan (4-byte words; one memset per run)
@@ -263,7 +265,7 @@ class Builder:
         a0 = xs[0]
         st = None
         if (self.fuse_gn_stats and gn_groups and ksize == 3 and out is None and ldc is None and out_dtype in (None, ops.act_dtype())
-                and cout % (2 * gn_groups) == 0 and 9 * sum(a.c for a in xs) >= 24 * 64  # long reductions only
+                and cout % (2 * gn_groups) == 0 and 9 * sum(a.c for a in xs) >= self.gn_fuse_min_k  # long reductions only
                 and min(128, self._pow2_ceil(a0.w)) * self._pow2_ceil(a0.h) >= 32):
             st = self.stats_slice(a0.nimg, gn_groups)
         split = wsplit or tuple(a.c for a in xs)  # wsplit: real weight channels when the activation is zero padded
@@ -366,7 +368,7 @@ class Builder:
         assert x.h % 2 == 0 and x.w % 2 == 0
         out = self.alloc((x.nimg, ho, wo, cout))
         st = None
-        if (self.fuse_gn_stats and gn_groups and cout % (2 * gn_groups) == 0 and 9 * x.c >= 24 * 64
+        if (self.fuse_gn_stats and gn_groups and cout % (2 * gn_groups) == 0 and 9 * x.c >= self.gn_fuse_min_k
                 and min(128, self._pow2_ceil(wo)) * self._pow2_ceil(ho) >= 32):
             st = self.stats_slice(x.nimg, gn_groups)
         sk = self.split_k_for(ho * wo, x.nimg * ho * wo, cout, 9 * -(-x.c // 64))

@@ -17,6 +17,8 @@ library - the SDXL VAE needs fp32's exponent range (upstream `force_upcast`s it 
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import lib as L
@@ -79,7 +81,9 @@ class VAEDecoderEngine:
         layers = cfg["layers_per_block"] + 1
         lc = cfg["latent_channels"]
         assert lc == 4
-        bld = Builder(self.device, fuse_gn_stats=True)
+        # (the decoder's statistics passes stream 0.5 GB tensors at 512x512: even the 128-channel convs, K = 1152, take
+        # the statistics of their output in the epilogue; B200SD_VAE_GN_MIN_K for A/B runs)
+        bld = Builder(self.device, fuse_gn_stats=True, gn_fuse_min_k=int(os.environ.get("B200SD_VAE_GN_MIN_K", 16 * 64)))
         z = bld.persistent((batch, h, w, 8))
         bld.add(ops.latent_to_act(latents, z, b=batch, hw=h * w, scale=1.0 / cfg["scaling_factor"]))
         # post_quant_conv 1x1 (4 -> 4) written into a zero-padded 8-channel buffer (TMA wants 16-byte pixels)
