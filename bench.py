@@ -510,8 +510,22 @@ def run_sweep(args):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    # the CPU baseline runs on rank 0 BEFORE the process group exists: the other ranks then sleep in the rendezvous
+    # instead of spinning in an NCCL barrier on the cores the baseline is using
+    cpu = None
+    Wt = importlib.import_module("k8s-nvidia-gpus_b200.weights")
+    cfg0 = Wt.load_config(args.model)
+    f0 = 2 ** (len(cfg0["vae"]["block_out_channels"]) - 1)
+    if rank == 0 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        unet, vae, clip = build_oracle(cfg0)
+        r = cpu_sample(cfg0, unet, vae, clip, 2, 1, args.inference_steps, args.height // f0, args.width // f0)
+        cpu = {"value": r["ips"], "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
+               "sample": "1 image: 2 timed + 1 warm-up CFG-paired UNet evaluations, 1 VAE decode, 1 CLIP pass"}
+        del unet, vae, clip
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(minutes=30))
     pipe = P.StableDiffusionPipeline.from_pretrained(args.model, device=f"cuda:{local}", scheduler=args.scheduler)
     cfg = pipe.cfg
     f = pipe.vae_scale_factor
@@ -519,14 +533,6 @@ def run_sweep(args):
     sched = pipe.make_schedule(args.inference_steps)
     evals = sched.num_evals
     dev = torch.device("cuda", local)
-    cpu = None
-    if rank == 0 and not args.no_cpu_baseline:
-        torch.set_num_threads(os.cpu_count() or 1)
-        unet, vae, clip = build_oracle(cfg)
-        r = cpu_sample(cfg, unet, vae, clip, 2, 1, args.inference_steps, h, w)
-        cpu = {"value": r["ips"], "unit": "images/s", "cores": torch.get_num_threads(), "kind": "port",
-               "sample": "1 image: 2 timed + 1 warm-up CFG-paired UNet evaluations, 1 VAE decode, 1 CLIP pass"}
-        del unet, vae, clip
 
     def sync_all():
         if world > 1:

@@ -33,7 +33,7 @@ for k, c in counts.items():
 path = os.path.join(ROOT, "profiles", f"{tag}_sass_summary.txt")
 open(path, "w").write("\n".join(out) + "\n")
 keep = ("void gemm_conv_kernel<false, false, true, true>", "void gemm_conv_kernel<false, true, false, false>",
-        "void attention_kernel<true>")
+        "attention_kernel", "void xattn_kernel<5, 3>")
 for k, ls in lines.items():
     if k not in keep:
         continue
