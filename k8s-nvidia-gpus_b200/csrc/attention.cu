@@ -66,6 +66,8 @@ struct alignas(64) AttnDev {
   int qtiles;     // query tiles per CTA (1 or 2)
   int o_col;      // first TMEM column of the O accumulators
   int o_stride;   // TMEM column stride between accumulators (two per query tile: even / odd KV tiles)
+  int p_col;      // >= 0: P travels through TMEM (A operand of P V read from tensor memory): first column of the
+                  // per-query-tile P buffers (32 columns each, 16-bit pairs); -1: P goes through shared memory
   int causal;
   float scale_log2;
 };
@@ -108,8 +110,8 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   const uint32_t sQ = base;                          // [qtiles][nd atoms of 16 KB]
   const uint32_t sK = sQ + p.qtiles * q_bytes;       // [stages][nd atoms of 8 KB]
   const uint32_t sV = sK + p.stages * kv_bytes;      // [stages][nd atoms of 8 KB]
-  const uint32_t sP = sV + p.stages * kv_bytes;      // [qtiles][2 buffers][16 KB]
-  const uint32_t sX = sP + p.qtiles * 2 * kQAtom;    // [qtiles][2 warpgroups][ref, sum][128] floats: final merge
+  const uint32_t sP = sV + p.stages * kv_bytes;      // [qtiles][2 buffers][16 KB]  (absent when P lives in TMEM)
+  const uint32_t sX = sP + (p.p_col >= 0 ? 0 : p.qtiles * 2 * kQAtom);  // [qtiles][2 warpgroups][ref, sum][128] floats
   int kv_end = p.nk;
   if (p.causal) kv_end = min(p.nk, q0 + kBQ * ntiles);  // keys beyond the last query row are fully masked
   const int T = (kv_end + kBKV - 1) / kBKV;
@@ -230,9 +232,16 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         const uint32_t a0 = p_lo + bf * (kQAtom >> 4);
         const uint32_t b0 = v_lo + vst * kv_u;
         const uint32_t tOa = tOt + bf * p.o_stride;  // accumulator of the warpgroup that owns tiles of parity bf
+        if (p.p_col >= 0) {
+          const uint32_t tP = tmem_base + p.p_col + 32 * t;  // 16 keys = 8 columns of 16-bit pairs per step
 #pragma unroll
-        for (int s = 0; s < kBKV / 16; ++s)  // 16 kv rows per step: +32 B along P's K, +2048 B down V's rows
-          umma_f16_ss_w(leader, tOa, a0 + s * 2, p_hi, b0 + s * 128, v_hi, idesc_o, (j >= 2) || (s != 0));
+          for (int s = 0; s < kBKV / 16; ++s)
+            umma_f16_ts_w(leader, tOa, tP + s * 8, b0 + s * 128, v_hi, idesc_o, (j >= 2) || (s != 0));
+        } else {
+#pragma unroll
+          for (int s = 0; s < kBKV / 16; ++s)  // 16 kv rows per step: +32 B along P's K, +2048 B down V's rows
+            umma_f16_ss_w(leader, tOa, a0 + s * 2, p_hi, b0 + s * 128, v_hi, idesc_o, (j >= 2) || (s != 0));
+        }
         umma_commit_w(leader, (bar0 + 8 * (kBarVEmpty + (vst))));
         umma_commit_w(leader, (bar0 + 8 * (kBarPVDone + 2 * (t) + (bf))));
         if (++vst == p.stages) {
@@ -334,15 +343,25 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
             w[q * 4 + e] = pack_act2(p0, p1);
           }
         }
-        // P(j-2) V(j-2) has read my P buffer (issued a whole tile ago - the wait is normally already satisfied)
-        if (j >= 2) mbar_wait_spin(pv_bar, pv_par);
-#pragma unroll
-        for (int q = 0; q < 8; ++q)  // 8 swizzled 16-byte chunks of my row
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((static_cast<uint32_t>(q) << 4) ^ swz)),
-                       "r"(w[q * 4]), "r"(w[q * 4 + 1]), "r"(w[q * 4 + 2]), "r"(w[q * 4 + 3])
-                       : "memory");
         l_run += psum;
-        fence_proxy_async_smem();
+        if (p.p_col >= 0) {
+          // P through tensor memory: my row's 64 probabilities as 32 packed columns of the query tile's P buffer, which
+          // the two warpgroups of the tile share - tile j may be written once P(j-1) V(j-1) (the other warpgroup's
+          // tile) has been consumed.  No shared-memory store, and P V reads its A operand from TMEM: half of this
+          // kernel's shared-memory traffic is gone.
+          if (j >= 1) mbar_wait_spin(bar0 + 8 * (kBarPVDone + 2 * t + (wg ^ 1)), ((j - 1) >> 1) & 1);
+          tmem_st32(tmem_base + p.p_col + 32 * t + lane_off, w);
+          tmem_st_wait();
+        } else {
+          // P(j-2) V(j-2) has read my P buffer (issued a whole tile ago - the wait is normally already satisfied)
+          if (j >= 2) mbar_wait_spin(pv_bar, pv_par);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)  // 8 swizzled 16-byte chunks of my row
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sPt + ((static_cast<uint32_t>(q) << 4) ^ swz)),
+                         "r"(w[q * 4]), "r"(w[q * 4 + 1]), "r"(w[q * 4 + 2]), "r"(w[q * 4 + 3])
+                         : "memory");
+          fence_proxy_async_smem();
+        }
         tc_fence_before();
         mbar_arrive((bar0 + 8 * (kBarPFull + 2 * (t) + (wg))));
       }
@@ -465,10 +484,21 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   // TMEM: S double-buffered per query tile (64 columns each), then the O accumulators
   d.o_col = d.qtiles * 128;
   d.o_stride = d.qtiles == 2 ? 64 : 192;  // 2 x (128 + 2 * 64) or 128 + 2 * 192 = 512 columns
+  // P through TMEM when 32 columns per query tile are left beside S and the accumulators (every head dim but 49..64)
+  d.p_col = -1;
+  {
+    const char* sw = getenv("B200SD_ATT_PTMEM");  // "0": P through shared memory (A/B measurements)
+    const int ostr = d.qtiles == 2 ? 48 : 160;
+    if ((sw == nullptr || sw[0] != '0') && d.dN <= ostr) {
+      d.o_stride = ostr;
+      d.p_col = d.o_col + 2 * d.qtiles * d.o_stride;  // 256 + 192 = 448 (+ 2 x 32) or 128 + 320 = 448 (+ 32)
+    }
+  }
   d.causal = h.causal;
   d.scale_log2 = h.scale * 1.4426950408889634f;
   // shared memory: Q + 2 P buffers per query tile are fixed; K/V rings take what is left (at most 4 stages)
-  const int fixed = d.qtiles * (d.nd * static_cast<int>(kQAtom) + 2 * static_cast<int>(kQAtom) + 2 * 2 * kBQ * 4) + 1024;
+  const int fixed = d.qtiles * (d.nd * static_cast<int>(kQAtom) + (d.p_col >= 0 ? 0 : 2 * static_cast<int>(kQAtom)) +
+                                2 * 2 * kBQ * 4) + 1024;
   const int per_stage = 2 * d.nd * static_cast<int>(kKVAtom);
   d.stages = min(kMaxStages, (di.max_smem_optin - 1024 - fixed) / per_stage);
   B200SD_REQUIRE(d.stages >= 2, B200SD_ERR_TOO_LARGE, "attention: shared memory budget");
