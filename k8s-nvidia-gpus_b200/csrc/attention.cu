@@ -44,7 +44,9 @@ static constexpr int kMaxStages = 4;
 // mbarrier indices inside the kernel's barrier block ([t] = query tile, [w] = KV-tile parity / warpgroup)
 enum : int {
   kBarQFull = 0,
-  kBarSFull = 1,                      // [t][w]  S tile written by the tensor pipe
+  kBarQFree = 1,                      // the item's S products have completed: Q may be overwritten
+  kBarOFree = 2,                      // [t]     the merge has read both accumulators of query tile t
+  kBarSFull = 4,                      // [t][w]  S tile written by the tensor pipe
   kBarSFree = kBarSFull + 4,          // [t][w]  S tile copied to registers
   kBarPFull = kBarSFree + 4,          // [t][w]  P tile in shared memory
   kBarPVDone = kBarPFull + 4,         // [t][w]  P V accumulated
@@ -69,6 +71,8 @@ struct alignas(64) AttnDev {
   int p_col;      // >= 0: P travels through TMEM (A operand of P V read from tensor memory): first column of the
                   // per-query-tile P buffers (32 columns each, 16-bit pairs); -1: P goes through shared memory
   int causal;
+  int nqblk;      // query blocks (of qtiles * 128 rows) per (batch, head)
+  int items;      // work items = batch * heads * nqblk
   float scale_log2;
 };
 
@@ -100,10 +104,6 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   const uint32_t bar0 = smem_u32(bars);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * kBQ * p.qtiles;
-  const int head = blockIdx.y;
-  const int b = blockIdx.z;
-  const int ntiles = (p.qtiles == 2 && q0 + kBQ < p.nq) ? 2 : 1;  // query tiles this CTA really has
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t q_bytes = p.nd * kQAtom;
   const uint32_t kv_bytes = p.nd * kKVAtom;
@@ -112,9 +112,23 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   const uint32_t sV = sK + p.stages * kv_bytes;      // [stages][nd atoms of 8 KB]
   const uint32_t sP = sV + p.stages * kv_bytes;      // [qtiles][2 buffers][16 KB]  (absent when P lives in TMEM)
   const uint32_t sX = sP + (p.p_col >= 0 ? 0 : p.qtiles * 2 * kQAtom);  // [qtiles][2 warpgroups][ref, sum][128] floats
-  int kv_end = p.nk;
-  if (p.causal) kv_end = min(p.nk, q0 + kBQ * ntiles);  // keys beyond the last query row are fully masked
-  const int T = (kv_end + kBKV - 1) / kBKV;
+
+  // PERSISTENT: the CTA walks work items (a block of 1-2 query tiles of one (batch, head)) with stride gridDim.x.
+  // TMEM, barriers and the K/V ring are set up once; every barrier parity below comes from a running count of that
+  // barrier's completions, so the Q load and the first Q K^T of the next item run under the last tiles, the merge and
+  // the store of the current one, and there is no per-item allocation, initialisation or drain.
+  // item -> (query block, head, batch), query block fastest (concurrent CTAs share a (batch, head)'s K/V in L2)
+  auto item_geom = [&](int item, int& q0, int& head, int& b, int& ntiles, int& T) {
+    const int qb = item % p.nqblk;
+    const int bh = item / p.nqblk;
+    head = bh % p.heads;
+    b = bh / p.heads;
+    q0 = qb * kBQ * p.qtiles;
+    ntiles = (p.qtiles == 2 && q0 + kBQ < p.nq) ? 2 : 1;  // query tiles this item really has
+    int kv_end = p.nk;
+    if (p.causal) kv_end = min(p.nk, q0 + kBQ * ntiles);  // keys beyond the last query row are fully masked
+    T = (kv_end + kBKV - 1) / kBKV;
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmQ);
@@ -123,18 +137,21 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   }
   if (warp == 1 && lane == 0) {
     mbar_init((bar0 + 8 * kBarQFull), 1);
-    for (int t = 0; t < 2; ++t)
+    mbar_init((bar0 + 8 * kBarQFree), p.qtiles);  // one commit per MMA issuer: the item's S products have read Q
+    for (int t = 0; t < 2; ++t) {
+      mbar_init((bar0 + 8 * (kBarOFree + t)), 256);  // both softmax warpgroups of the tile have read O out
       for (int i = 0; i < 2; ++i) {
         mbar_init((bar0 + 8 * (kBarSFull + 2 * (t) + (i))), 1);
         mbar_init((bar0 + 8 * (kBarPFull + 2 * (t) + (i))), 128);
         mbar_init((bar0 + 8 * (kBarSFree + 2 * (t) + (i))), 128);
         mbar_init((bar0 + 8 * (kBarPVDone + 2 * (t) + (i))), 1);
       }
+    }
     for (int s = 0; s < kMaxStages; ++s) {
       mbar_init((bar0 + 8 * (kBarKFull + (s))), 1);
       mbar_init((bar0 + 8 * (kBarVFull + (s))), 1);
-      mbar_init((bar0 + 8 * (kBarKEmpty + (s))), ntiles);  // one tcgen05.commit per MMA issuer (one issuer per query tile)
-      mbar_init((bar0 + 8 * (kBarVEmpty + (s))), ntiles);
+      mbar_init((bar0 + 8 * (kBarKEmpty + (s))), p.qtiles);  // one tcgen05.commit per MMA issuer warp (an issuer whose
+      mbar_init((bar0 + 8 * (kBarVEmpty + (s))), p.qtiles);  // query tile does not exist in an item still arrives)
     }
     fence_mbar_init();
   }
@@ -150,84 +167,119 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
     // ------------------------------------------------------------------ TMA producer (whole warp converged, one
     // elected lane issues - see the "_w" note in common.cuh)
     const uint32_t leader = elect_one();
-    mbar_arrive_expect_tx_w(leader, (bar0 + 8 * kBarQFull), ntiles * q_bytes);
-    for (int t = 0; t < ntiles; ++t)
-      for (int a = 0; a < p.nd; ++a)
-        tma_load_4d_w(leader, sQ + t * q_bytes + a * kQAtom, &p.tmQ, (bar0 + 8 * kBarQFull), a * 64, head, q0 + t * kBQ, b);
     int st = 0;
     uint32_t ph = 1;
-    for (int j = 0; j < T; ++j) {
-      mbar_wait((bar0 + 8 * (kBarKEmpty + (st))), ph);
-      mbar_arrive_expect_tx_w(leader, (bar0 + 8 * (kBarKFull + (st))), kv_bytes);
-      for (int a = 0; a < p.nd; ++a)
-        tma_load_4d_w(leader, sK + st * kv_bytes + a * kKVAtom, &p.tmK, (bar0 + 8 * (kBarKFull + (st))), a * 64, head, j * kBKV, b);
-      mbar_wait((bar0 + 8 * (kBarVEmpty + (st))), ph);
-      mbar_arrive_expect_tx_w(leader, (bar0 + 8 * (kBarVFull + (st))), kv_bytes);
-      for (int a = 0; a < p.nd; ++a)
-        tma_load_4d_w(leader, sV + st * kv_bytes + a * kKVAtom, &p.tmV, (bar0 + 8 * (kBarVFull + (st))), a * 64, head, j * kBKV, b);
-      if (++st == p.stages) {
-        st = 0;
-        ph ^= 1u;
+    int n = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n) {
+      int q0, head, b, ntiles, T;
+      item_geom(item, q0, head, b, ntiles, T);
+      if (n > 0) mbar_wait((bar0 + 8 * kBarQFree), (n - 1) & 1);  // the previous item's S products are done with Q
+      mbar_arrive_expect_tx_w(leader, (bar0 + 8 * kBarQFull), ntiles * q_bytes);
+      for (int t = 0; t < ntiles; ++t)
+        for (int a = 0; a < p.nd; ++a)
+          tma_load_4d_w(leader, sQ + t * q_bytes + a * kQAtom, &p.tmQ, (bar0 + 8 * kBarQFull), a * 64, head, q0 + t * kBQ, b);
+      for (int j = 0; j < T; ++j) {
+        mbar_wait((bar0 + 8 * (kBarKEmpty + (st))), ph);
+        mbar_arrive_expect_tx_w(leader, (bar0 + 8 * (kBarKFull + (st))), kv_bytes);
+        for (int a = 0; a < p.nd; ++a)
+          tma_load_4d_w(leader, sK + st * kv_bytes + a * kKVAtom, &p.tmK, (bar0 + 8 * (kBarKFull + (st))), a * 64, head, j * kBKV, b);
+        mbar_wait((bar0 + 8 * (kBarVEmpty + (st))), ph);
+        mbar_arrive_expect_tx_w(leader, (bar0 + 8 * (kBarVFull + (st))), kv_bytes);
+        for (int a = 0; a < p.nd; ++a)
+          tma_load_4d_w(leader, sV + st * kv_bytes + a * kKVAtom, &p.tmV, (bar0 + 8 * (kBarVFull + (st))), a * 64, head, j * kBKV, b);
+        if (++st == p.stages) {
+          st = 0;
+          ph ^= 1u;
+        }
       }
     }
-  } else if (warp == 1 || warp == 3) {
+  } else if ((warp == 1 || warp == 3) && (warp >> 1) < p.qtiles) {
     const int t = warp >> 1;  // warp 1 issues for query tile 0, warp 3 for query tile 1
-    if (t < ntiles) {
-      // ---------------------------------------------------------------- MMA issuer of query tile t
-      // Whole warp converged; descriptors are built once and only their low words (16-byte units) move.  K and V
-      // stages are consumed strictly in order, so each ring is tracked by a running (stage, phase) pair.
-      const uint32_t leader = elect_one();
-      const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 64] = Q (K-major) x K (K-major)
-      const uint32_t idesc_o = make_idesc_f16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
-      const int ksteps_s = p.dN / 16;
-      const uint64_t dQ = make_smem_desc_sw128(sQ + t * q_bytes, 16, 1024);
-      const uint64_t dK = make_smem_desc_sw128(sK, 16, 1024);
-      const uint64_t dV = make_smem_desc_sw128(sV, kKVAtom, 1024);  // MN-major: atoms kKVAtom apart
-      const uint64_t dP = make_smem_desc_sw128(sP + 2 * t * kQAtom, 16, 1024);
-      const uint32_t q_lo = static_cast<uint32_t>(dQ), q_hi = static_cast<uint32_t>(dQ >> 32);
-      const uint32_t k_lo = static_cast<uint32_t>(dK), k_hi = static_cast<uint32_t>(dK >> 32);
-      const uint32_t v_lo = static_cast<uint32_t>(dV), v_hi = static_cast<uint32_t>(dV >> 32);
-      const uint32_t p_lo = static_cast<uint32_t>(dP), p_hi = static_cast<uint32_t>(dP >> 32);
-      const uint32_t kv_u = kv_bytes >> 4;
-      const uint32_t tS0 = tmem_base + 2 * t * 64;
-      const uint32_t tOt = tmem_base + p.o_col + 2 * t * p.o_stride;
-      int kst = 0, vst = 0;
-      uint32_t kph = 0, vph = 0;
-      // S_t(jj) into buffer jj & 1 from the current K stage (MMAs only; the commits follow separately)
-      auto issue_s = [&](int bfs) {
-        const uint32_t b0 = k_lo + kst * kv_u;
-        for (int s = 0; s < ksteps_s; ++s) {
-          const uint32_t in_atom = (s & 3) * 2;
-          umma_f16_ss_w(leader, tS0 + bfs * 64, q_lo + (s >> 2) * (kQAtom >> 4) + in_atom, q_hi,
-                        b0 + (s >> 2) * (kKVAtom >> 4) + in_atom, k_hi, idesc_s, s != 0);
-        }
-      };
-      auto commit_s = [&](int bfs) {
-        umma_commit_w(leader, (bar0 + 8 * (kBarSFull + 2 * (t) + (bfs))));
-        umma_commit_w(leader, (bar0 + 8 * (kBarKEmpty + (kst))));
-        if (++kst == p.stages) {
-          kst = 0;
-          kph ^= 1u;
-        }
-      };
-      mbar_wait_spin((bar0 + 8 * kBarQFull), 0);
-      for (int jj = 0; jj < 2 && jj < T; ++jj) {  // prologue: both S buffers
-        mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
-        tc_fence_after();
-        issue_s(jj);
-        commit_s(jj);
+    // ---------------------------------------------------------------- MMA issuer of query tile t
+    // Whole warp converged; descriptors are built once and only their low words (16-byte units) move.  K and V
+    // stages are consumed strictly in order, so each ring is tracked by a running (stage, phase) pair.
+    const uint32_t leader = elect_one();
+    const uint32_t idesc_s = make_idesc_f16(kBQ, kBKV, 0, 0);  // S[128 x 64] = Q (K-major) x K (K-major)
+    const uint32_t idesc_o = make_idesc_f16(kBQ, p.dN, 0, 1);  // O[128 x dN] += P (K-major) x V (MN-major)
+    const int ksteps_s = p.dN / 16;
+    const uint64_t dQ = make_smem_desc_sw128(sQ + t * q_bytes, 16, 1024);
+    const uint64_t dK = make_smem_desc_sw128(sK, 16, 1024);
+    const uint64_t dV = make_smem_desc_sw128(sV, kKVAtom, 1024);  // MN-major: atoms kKVAtom apart
+    const uint64_t dP = make_smem_desc_sw128(sP + 2 * t * kQAtom, 16, 1024);
+    const uint32_t q_lo = static_cast<uint32_t>(dQ), q_hi = static_cast<uint32_t>(dQ >> 32);
+    const uint32_t k_lo = static_cast<uint32_t>(dK), k_hi = static_cast<uint32_t>(dK >> 32);
+    const uint32_t v_lo = static_cast<uint32_t>(dV), v_hi = static_cast<uint32_t>(dV >> 32);
+    const uint32_t p_lo = static_cast<uint32_t>(dP), p_hi = static_cast<uint32_t>(dP >> 32);
+    const uint32_t kv_u = kv_bytes >> 4;
+    const uint32_t tS0 = tmem_base + 2 * t * 64;
+    const uint32_t tOt = tmem_base + p.o_col + 2 * t * p.o_stride;
+    int kst = 0, vst = 0;
+    uint32_t kph = 0, vph = 0;
+    int cw[2] = {0, 0};  // completions so far of this tile's per-parity barriers (S full / free, P full, PV done)
+    int n = 0, n_act = 0;  // items seen / items in which this query tile existed
+    // S_t into buffer bfs from the current K stage (MMAs only; the commits follow separately)
+    auto issue_s = [&](int bfs) {
+      const uint32_t b0 = k_lo + kst * kv_u;
+      for (int s = 0; s < ksteps_s; ++s) {
+        const uint32_t in_atom = (s & 3) * 2;
+        umma_f16_ss_w(leader, tS0 + bfs * 64, q_lo + (s >> 2) * (kQAtom >> 4) + in_atom, q_hi,
+                      b0 + (s >> 2) * (kKVAtom >> 4) + in_atom, k_hi, idesc_s, s != 0);
       }
+    };
+    auto commit_s = [&](int bfs) {
+      umma_commit_w(leader, (bar0 + 8 * (kBarSFull + 2 * (t) + (bfs))));
+      umma_commit_w(leader, (bar0 + 8 * (kBarKEmpty + (kst))));
+      if (++kst == p.stages) {
+        kst = 0;
+        kph ^= 1u;
+      }
+    };
+    // S of tile jj of the current item: its buffer's previous use (this item or the one before) must have been read
+    auto s_tile = [&](int jj) {
+      const int bfs = jj & 1;
+      const int gi = cw[bfs] + (jj >> 1);  // how many times this buffer has been used before
+      if (gi > 0) mbar_wait_spin((bar0 + 8 * (kBarSFree + 2 * (t) + (bfs))), (gi - 1) & 1);
+      mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
+      tc_fence_after();
+      issue_s(bfs);
+      commit_s(bfs);
+    };
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n) {
+      int q0, head, b, ntiles, T;
+      item_geom(item, q0, head, b, ntiles, T);
+      mbar_wait_spin((bar0 + 8 * kBarQFull), n & 1);
+      if (t >= ntiles) {
+        // my query tile does not exist in this item (ragged last block): keep the shared barriers in step
+        umma_commit_w(leader, (bar0 + 8 * kBarQFree));
+        for (int j = 0; j < T; ++j) {
+          mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
+          umma_commit_w(leader, (bar0 + 8 * (kBarKEmpty + (kst))));
+          if (++kst == p.stages) {
+            kst = 0;
+            kph ^= 1u;
+          }
+          mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
+          umma_commit_w(leader, (bar0 + 8 * (kBarVEmpty + (vst))));
+          if (++vst == p.stages) {
+            vst = 0;
+            vph ^= 1u;
+          }
+        }
+        continue;
+      }
+      for (int jj = 0; jj < 2 && jj < T; ++jj) s_tile(jj);  // prologue: both S buffers
+      if (T <= 2) umma_commit_w(leader, (bar0 + 8 * kBarQFree));  // every S of the item has been issued
       for (int j = 0; j < T; ++j) {
         const int bf = j & 1;
+        const int gi = cw[bf] + (j >> 1);
         if (j + 2 < T) {
-          mbar_wait_spin((bar0 + 8 * (kBarSFree + 2 * (t) + (bf))), (j >> 1) & 1);  // S_t(j) is in its owner's registers
-          mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
-          tc_fence_after();
-          issue_s(bf);
-          commit_s(bf);
+          s_tile(j + 2);
+          if (j + 3 >= T) umma_commit_w(leader, (bar0 + 8 * kBarQFree));  // that was the item's last S
         }
-        mbar_wait_spin((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), (j >> 1) & 1);  // P_t(j) in smem
+        mbar_wait_spin((bar0 + 8 * (kBarPFull + 2 * (t) + (bf))), gi & 1);  // P_t(j) is ready
         mbar_wait_spin((bar0 + 8 * (kBarVFull + (vst))), vph);
+        // the first product into an accumulator overwrites it: the previous item's merge must have read it
+        if (j < 2 && n_act > 0) mbar_wait_spin((bar0 + 8 * (kBarOFree + t)), (n_act - 1) & 1);
         tc_fence_after();
         const uint32_t a0 = p_lo + bf * (kQAtom >> 4);
         const uint32_t b0 = v_lo + vst * kv_u;
@@ -249,6 +301,9 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           vph ^= 1u;
         }
       }
+      cw[0] += (T + 1) >> 1;
+      cw[1] += T >> 1;
+      ++n_act;
     }
   }
   } else {
@@ -256,25 +311,30 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
     const int g = (warp - 4) >> 2;  // warpgroup 0..3
     const int t = g >> 1;           // query tile
     const int wg = g & 1;           // parity of the KV tiles this warpgroup owns (and its S / P buffer, O accumulator)
-    if (t < ntiles) {
-      const int qd = warp & 3;
-      const int r = qd * 32 + lane;  // row in tile == TMEM lane
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;  // row in tile == TMEM lane
+    const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
+    const uint32_t tS = tmem_base + (2 * t + wg) * 64 + lane_off;
+    const uint32_t tO0 = tmem_base + p.o_col + (2 * t) * p.o_stride + lane_off;  // even-tile accumulator
+    const uint32_t tO = tO0 + wg * p.o_stride;                                   // mine
+    const uint32_t sPt = sP + (2 * t + wg) * kQAtom + r * 128;
+    const uint32_t swz = static_cast<uint32_t>(r & 7) << 4;
+    const int pair_bar = 1 + t * 4 + qd;  // named barrier shared by the two warps that own the same 32 rows
+    int cw[2] = {0, 0};  // completions so far of this tile's per-parity barriers (as in the issuer)
+    for (int item = blockIdx.x; t < p.qtiles && item < p.items; item += gridDim.x) {
+      int q0, head, b, ntiles, T;
+      item_geom(item, q0, head, b, ntiles, T);
+      if (t >= ntiles) continue;
       const int qrow = q0 + t * kBQ + r;
-      const uint32_t lane_off = static_cast<uint32_t>(qd * 32) << 16;
-      const uint32_t tS = tmem_base + (2 * t + wg) * 64 + lane_off;
-      const uint32_t tO0 = tmem_base + p.o_col + (2 * t) * p.o_stride + lane_off;  // even-tile accumulator
-      const uint32_t tO = tO0 + wg * p.o_stride;                                   // mine
-      const uint32_t sPt = sP + (2 * t + wg) * kQAtom + r * 128;
-      const uint32_t swz = static_cast<uint32_t>(r & 7) << 4;
-      const int pair_bar = 1 + t * 4 + qd;  // named barrier shared by the two warps that own the same 32 rows
       float mb = 0.f;     // my reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
-      float l_run = 0.f;  // my row sum (register-sum variant)
+      float l_run = 0.f;  // my row sum
       for (int j = wg; j < T; j += 2) {
+        const int gi = cw[wg] + (j >> 1);  // running index of this use of my S / P barriers
         const int col0 = j * kBKV;
         int limit = p.nk - col0;  // valid columns: [0, limit)
         if (p.causal) limit = min(limit, qrow - col0 + 1);
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
-        mbar_wait_spin((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), (j >> 1) & 1);
+        mbar_wait_spin((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), gi & 1);
         tc_fence_after();
         // the whole row of the tile goes to registers and the S buffer is handed straight back: Q K^T of my next
         // tile runs on the tensor pipe while I am still busy with this one
@@ -306,7 +366,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         const float xmax = fmaf(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)), p.scale_log2, -mb);  // -inf: row fully masked
         const bool exceed = (xmax > kTau) || (j == wg && xmax < -kTau && xmax != -INFINITY);
         const uint32_t pv_bar = bar0 + 8 * (kBarPVDone + 2 * t + wg);
-        const uint32_t pv_par = ((j >> 1) - 1) & 1;
+        const uint32_t pv_par = (gi - 1) & 1;  // my previous tile (always of this item where it is waited for)
         if (__any_sync(0xffffffffu, exceed)) {  // rare
           const float delta = exceed ? xmax : 0.f;
           const float alpha = ex2f(-delta);
@@ -349,7 +409,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           // the two warpgroups of the tile share - tile j may be written once P(j-1) V(j-1) (the other warpgroup's
           // tile) has been consumed.  No shared-memory store, and P V reads its A operand from TMEM: half of this
           // kernel's shared-memory traffic is gone.
-          if (j >= 1) mbar_wait_spin(bar0 + 8 * (kBarPVDone + 2 * t + (wg ^ 1)), ((j - 1) >> 1) & 1);
+          if (j >= 1) mbar_wait_spin(bar0 + 8 * (kBarPVDone + 2 * t + (wg ^ 1)), (cw[wg ^ 1] + ((j - 1) >> 1)) & 1);
           tmem_st32(tmem_base + p.p_col + 32 * t + lane_off, w);
           tmem_st_wait();
         } else {
@@ -369,7 +429,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       // with f_x = 2^(mb_x - max(mb_e, mb_o)); both accumulators live in my TMEM lanes, only mb / l travel through smem.
       const int mine = (T - wg + 1) >> 1;  // tiles I processed
       const bool has_odd = T >= 2;
-      if (mine > 0) mbar_wait((bar0 + 8 * (kBarPVDone + 2 * (t) + (wg))), (mine - 1) & 1);  // the last commit covers every earlier MMA
+      if (mine > 0) mbar_wait((bar0 + 8 * (kBarPVDone + 2 * (t) + (wg))), (cw[wg] + mine - 1) & 1);  // the last commit covers every earlier MMA
       const uint32_t xa = sX + ((t * 2 + wg) * 2 * kBQ + r) * 4, xb = sX + ((t * 2 + (wg ^ 1)) * 2 * kBQ + r) * 4;
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(xa), "f"(mb) : "memory");
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(xa + kBQ * 4), "f"(l_run) : "memory");
@@ -379,6 +439,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       float mb_o, l_o;
       asm volatile("ld.shared.f32 %0, [%1];" : "=f"(mb_o) : "r"(xb) : "memory");
       asm volatile("ld.shared.f32 %0, [%1];" : "=f"(l_o) : "r"(xb + kBQ * 4) : "memory");
+      named_bar_sync(pair_bar, 64);  // (my slots are rewritten at the end of the NEXT item: the partner has read them)
       // (e, o) = (even-tile warpgroup, odd-tile warpgroup) regardless of which one I am
       const float mb_e = wg ? mb_o : mb, mb_d = wg ? mb : mb_o;
       float l_e = wg ? l_o : l_run, l_d = wg ? l_run : l_o;
@@ -412,6 +473,11 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           }
         }
       }
+      // O has been read out: the issuer may overwrite the accumulators with the next item's first products
+      tc_fence_before();
+      mbar_arrive((bar0 + 8 * (kBarOFree + t)));
+      cw[0] += (T + 1) >> 1;
+      cw[1] += T >> 1;
     }
   }
 
@@ -458,7 +524,8 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
                  B200SD_ERR_BAD_SHAPE, "attention: row stride smaller than heads*d");
   B200SD_REQUIRE(aligned16(h.q) && aligned16(h.k) && aligned16(h.v) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
                  "attention: pointers must be 16-byte aligned");
-  B200SD_REQUIRE(h.heads <= 65535 && h.batch <= 65535, B200SD_ERR_TOO_LARGE, "attention: grid too large");
+  B200SD_REQUIRE(static_cast<long long>(h.heads) * h.batch * ceil_div(h.nq, kBQ) < (1ll << 30), B200SD_ERR_TOO_LARGE,
+                 "attention: too many work items");
   B200SD_REQUIRE(h.scale > 0.f, B200SD_ERR_BAD_ARGUMENT, "attention: scale must be positive");
   if (!h.causal && h.nk <= 128) {
     // the whole key set is one tile (cross-attention against the 77 text tokens): persistent short-KV kernel
@@ -516,7 +583,11 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   if (int e = enc(&d.tmV, h.v, h.nk, h.ldv, kBKV)) return e;
 
   const int smem_bytes = fixed + d.stages * per_stage;
-  dim3 grid(ceil_div(h.nq, kBQ * d.qtiles), h.heads, h.batch);
+  d.nqblk = ceil_div(h.nq, kBQ * d.qtiles);
+  d.items = h.batch * h.heads * d.nqblk;
+  dim3 grid(min(d.items, di.sm_count));  // persistent: one CTA per SM, items taken with stride gridDim.x
+  if (const char* sw = getenv("B200SD_ATT_PERSIST"))  // "0": one CTA per item (A/B measurements)
+    if (sw[0] == '0') grid = dim3(d.items);
   {
     AttnLaunch L;
     memset(&L, 0, sizeof(L));
