@@ -472,7 +472,7 @@ extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200s
   B200SD_CUDA_CHECK(cudaGetLastError());
   gn_apply_kernel<<<grid, kNormThreads, 0, s>>>(
       static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<const unsigned long long*>(h.stats),
-      h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.silu, h.eps);
+      h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, gn_silu_mode(h.silu), h.eps);
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }
