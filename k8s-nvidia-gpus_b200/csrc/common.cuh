@@ -561,6 +561,51 @@ __device__ __forceinline__ double fixed_value(const unsigned long long* slot2) {
          static_cast<double>(static_cast<long long>(slot2[1])) * 5.9604644775390625e-08;  // 2^-24
 }
 
+// ------------------------------------------------------------------ packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2)
+// One instruction for two lanes' worth of fp32 work: the epilogues are issue/latency-bound, not FMA-pipe-bound, so
+// halving the instruction count of their element-wise chains is what counts.
+__device__ __forceinline__ void ffma2(float a0, float a1, float b0, float b1, float c0, float c1, float& x0, float& x1) {
+  asm("{\n.reg .b64 va, vb, vc, vd;\nmov.b64 va, {%2, %3};\nmov.b64 vb, {%4, %5};\nmov.b64 vc, {%6, %7};\n"
+      "fma.rn.f32x2 vd, va, vb, vc;\nmov.b64 {%0, %1}, vd;\n}\n"
+      : "=f"(x0), "=f"(x1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void fmul2(float a0, float a1, float b0, float b1, float& x0, float& x1) {
+  asm("{\n.reg .b64 va, vb, vd;\nmov.b64 va, {%2, %3};\nmov.b64 vb, {%4, %5};\nmul.rn.f32x2 vd, va, vb;\n"
+      "mov.b64 {%0, %1}, vd;\n}\n"
+      : "=f"(x0), "=f"(x1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+__device__ __forceinline__ void fadd2(float a0, float a1, float b0, float b1, float& x0, float& x1) {
+  asm("{\n.reg .b64 va, vb, vd;\nmov.b64 va, {%2, %3};\nmov.b64 vb, {%4, %5};\nadd.rn.f32x2 vd, va, vb;\n"
+      "mov.b64 {%0, %1}, vd;\n}\n"
+      : "=f"(x0), "=f"(x1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+// (v0, v1) *= gelu_erf(g0), gelu_erf(g1): the pair form of gelu_erf_f (same formula, same constants)
+__device__ __forceinline__ void mul_gelu_erf2(float& v0, float& v1, float g0, float g1) {
+  float z0, z1, t0, t1, q0, q1, e0, e1, h0, h1;
+  fmul2(fabsf(g0), fabsf(g1), 0.70710678118654752f, 0.70710678118654752f, z0, z1);
+  ffma2(z0, z1, 0.3275911f, 0.3275911f, 1.f, 1.f, t0, t1);
+  t0 = rcp_approx(t0);
+  t1 = rcp_approx(t1);
+  ffma2(t0, t1, 1.061405429f, 1.061405429f, -1.453152027f, -1.453152027f, q0, q1);
+  ffma2(q0, q1, t0, t1, 1.421413741f, 1.421413741f, q0, q1);
+  ffma2(q0, q1, t0, t1, -0.284496736f, -0.284496736f, q0, q1);
+  ffma2(q0, q1, t0, t1, 0.254829592f, 0.254829592f, q0, q1);
+  fmul2(q0, q1, t0, t1, q0, q1);
+  fmul2(z0, z1, z0, z1, e0, e1);
+  e0 = ex2_approx(-1.4426950408889634f * e0);
+  e1 = ex2_approx(-1.4426950408889634f * e1);
+  fmul2(q0, q1, e0, e1, h0, h1);  // erfc(z) = q t exp(-z^2)
+  // x * Phi(x) = x * (x >= 0 ? 1 - erfc / 2 : erfc / 2) = 0.5 * (x + |x| * (1 - erfc))
+  float w0, w1;
+  ffma2(h0, h1, -1.f, -1.f, 1.f, 1.f, w0, w1);               // 1 - erfc
+  ffma2(fabsf(g0), fabsf(g1), w0, w1, g0, g1, w0, w1);        // x + |x| (1 - erfc)
+  fmul2(w0, w1, 0.5f, 0.5f, w0, w1);
+  fmul2(v0, v1, w0, w1, v0, v1);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -474,10 +474,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col) + k);
-              f[4 * k + 0] += b4.x;
-              f[4 * k + 1] += b4.y;
-              f[4 * k + 2] += b4.z;
-              f[4 * k + 3] += b4.w;
+              fadd2(f[4 * k + 0], f[4 * k + 1], b4.x, b4.y, f[4 * k + 0], f[4 * k + 1]);
+              fadd2(f[4 * k + 2], f[4 * k + 3], b4.z, b4.w, f[4 * k + 2], f[4 * k + 3]);
             }
           } else {
 #pragma unroll
@@ -519,15 +517,24 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             load_chunk(ac0 + hh * 64, f);
             load_chunk(ac0 + hh * 64 + 32, gt);
 #pragma unroll
-            for (int k = 0; k < 32; ++k) f[k] *= gelu_erf_f(gt[k]);
+            for (int k = 0; k < 32; k += 2) mul_gelu_erf2(f[k], f[k + 1], gt[k], gt[k + 1]);
           } else {
             const int ac = ac0 + hh * 32;
             load_chunk(ac, f);
             if (p.rowbias != nullptr) {
               const float* rb = p.rowbias + static_cast<long long>(img) * p.ld_rowbias + col0 + ac;
+              if (col0 + ac + 32 <= p.N && (reinterpret_cast<uintptr_t>(rb) & 15u) == 0) {
 #pragma unroll
-              for (int k = 0; k < 32; ++k)
-                if (col0 + ac + k < p.N) f[k] += __ldg(rb + k);
+                for (int k = 0; k < 8; ++k) {
+                  const float4 b4 = __ldg(reinterpret_cast<const float4*>(rb) + k);
+                  fadd2(f[4 * k + 0], f[4 * k + 1], b4.x, b4.y, f[4 * k + 0], f[4 * k + 1]);
+                  fadd2(f[4 * k + 2], f[4 * k + 3], b4.z, b4.w, f[4 * k + 2], f[4 * k + 3]);
+                }
+              } else {
+#pragma unroll
+                for (int k = 0; k < 32; ++k)
+                  if (col0 + ac + k < p.N) f[k] += __ldg(rb + k);
+              }
             }
             if (p.act == B200SD_ACT_SILU) {
 #pragma unroll
@@ -549,14 +556,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
                            : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w)
                            : "r"(my_row + (((hh * 4 + k) ^ sw) << 4)));
               const float2 a = unpack_act2(u.x), b = unpack_act2(u.y), cc = unpack_act2(u.z), d = unpack_act2(u.w);
-              f[8 * k + 0] += a.x;
-              f[8 * k + 1] += a.y;
-              f[8 * k + 2] += b.x;
-              f[8 * k + 3] += b.y;
-              f[8 * k + 4] += cc.x;
-              f[8 * k + 5] += cc.y;
-              f[8 * k + 6] += d.x;
-              f[8 * k + 7] += d.y;
+              fadd2(f[8 * k + 0], f[8 * k + 1], a.x, a.y, f[8 * k + 0], f[8 * k + 1]);
+              fadd2(f[8 * k + 2], f[8 * k + 3], b.x, b.y, f[8 * k + 2], f[8 * k + 3]);
+              fadd2(f[8 * k + 4], f[8 * k + 5], cc.x, cc.y, f[8 * k + 4], f[8 * k + 5]);
+              fadd2(f[8 * k + 6], f[8 * k + 7], d.x, d.y, f[8 * k + 6], f[8 * k + 7]);
             }
           }
           if (kOutF32) {

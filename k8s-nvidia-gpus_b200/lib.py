@@ -6,6 +6,7 @@ library is missing or a call fails, an exception is raised.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 _LIB_PATH = Path(__file__).resolve().parent / "libb200sd.so"
@@ -152,6 +153,8 @@ def load(variant: str | None = None):
     if variant in _libs:
         return _libs[variant]
     path = _LIB_PATHS[variant]
+    if variant == "fp16" and os.environ.get("B200SD_LIB"):
+        path = Path(os.environ["B200SD_LIB"]).resolve()  # A/B measurements against another build of the library
     if not path.exists():
         raise B200SDError(
             f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
