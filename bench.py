@@ -252,7 +252,7 @@ def algorithmic_bytes(call):
 def cupti_profile(plan, replays=3):
     """Per-kernel device durations of `replays` graph replays of `plan` from CUPTI activity records (torch.profiler:
     hardware start / end timestamps of every kernel, no serialisation between launches, no replay - unlike ncu), matched
-    to the plan's call list by launch order.  Returns {kind: {launches, ms, flops, bytes}} averaged per replay, plus
+    to the plan's call list by launch order; overlapped heads (programmatic dependent launch) are not counted twice.  Returns {kind: {launches, ms, flops, bytes}} averaged per replay, plus
     the busy / span totals, or None when the profiler is unavailable."""
     try:
         from torch.profiler import ProfilerActivity, profile
@@ -268,12 +268,18 @@ def cupti_profile(plan, replays=3):
     if len(evs) != replays * len(calls):
         return {"error": f"{len(evs)} kernel records for {replays} x {len(calls)} calls"}
     agg = {}
+    frontier = evs[0].time_range.start
     for i, e in enumerate(evs):
         c = calls[i % len(calls)]
         fl, kind = flops_of_call(c)
         a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
         a["launches"] += 1
-        a["ms"] += e.device_time_total * 1e-3
+        # A kernel launched with programmatic dependent launch becomes resident (and its record starts) while its
+        # predecessor is still running, and then waits for it: the overlapped head belongs to the predecessor.  A
+        # kernel's time is therefore counted from the end of everything launched before it (== its whole duration when
+        # nothing overlaps), so the per-kind times still add up to the busy time of the stream.
+        a["ms"] += max(0.0, e.time_range.end - max(e.time_range.start, frontier)) * 1e-3
+        frontier = max(frontier, e.time_range.end)
         a["flops"] += fl
         a["bytes"] += algorithmic_bytes(c)
     for a in agg.values():
@@ -415,7 +421,9 @@ def run_cuda(args):
     if cupti_ok:
         gemm_ms_in_step = cupti["kinds"]["gemm"]["ms"]
         method = (f"CUPTI activity records (torch.profiler) of {evals} graph replays of the denoise step, kernel "
-                  "durations matched to the plan's calls by launch order; achieved = sum 2MNK / sum of durations")
+                  "durations matched to the plan's calls by launch order, each counted from the end of the kernels launched "
+                  "before it (programmatic dependent launch lets a GEMM's set-up start under its predecessor's tail); "
+                  "achieved = sum 2MNK / sum of those durations")
     else:
         gemm_ms_in_step = gemm_ms_event_share
         method = ("share of the step from per-launch CUDA-event intervals (eager pass) x the CUDA-event-timed graph "

@@ -160,12 +160,14 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_s, 0);  // warp-uniform for the issue loops
+  pdl_launch();  // set-up done (common.cuh: programmatic dependent launch)
   // TMEM columns: S_t[buf] at (2t + buf) * 64; accumulator of (query tile t, tile parity w) at o_col + (2t + w) * o_stride
 
   if (warp < 4) {
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (whole warp converged, one
     // elected lane issues - see the "_w" note in common.cuh)
+    pdl_wait();  // q / k / v come from the previous kernels of the step
     const uint32_t leader = elect_one();
     int st = 0;
     uint32_t ph = 1;
@@ -308,6 +310,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
   }
   } else {
     // ------------------------------------------------------------------ softmax / correction / epilogue
+    pdl_wait();  // the output rows may still be read by an earlier kernel
     const int g = (warp - 4) >> 2;  // warpgroup 0..3
     const int t = g >> 1;           // query tile
     const int wg = g & 1;           // parity of the KV tiles this warpgroup owns (and its S / P buffer, O accumulator)
@@ -508,8 +511,8 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
   {
     AttnLaunch hit;  // identical parameter block seen before: tensor maps and geometry are cached
     if (launch_cache_get(1, hp, sizeof(*hp), &hit, sizeof(hit))) {
-      attention_kernel<<<hit.grid, kAttThreads, hit.smem_bytes, static_cast<cudaStream_t>(stream_)>>>(hit.d);
-      B200SD_CUDA_CHECK(cudaGetLastError());
+      B200SD_CUDA_CHECK(launch_pdl(kPdlAttention, attention_kernel, dim3(hit.grid), dim3(kAttThreads), hit.smem_bytes,
+                                   static_cast<cudaStream_t>(stream_), hit.d));
       return B200SD_OK;
     }
   }
@@ -596,7 +599,7 @@ extern "C" int b200sd_attention(const b200sd_attn_params* hp, b200sd_stream stre
     L.smem_bytes = smem_bytes;
     launch_cache_put(1, hp, sizeof(*hp), &L, sizeof(L));
   }
-  attention_kernel<<<grid, kAttThreads, smem_bytes, static_cast<cudaStream_t>(stream_)>>>(d);
-  B200SD_CUDA_CHECK(cudaGetLastError());
+  B200SD_CUDA_CHECK(launch_pdl(kPdlAttention, attention_kernel, dim3(grid), dim3(kAttThreads), smem_bytes,
+                               static_cast<cudaStream_t>(stream_), d));
   return B200SD_OK;
 }

@@ -122,9 +122,11 @@ __global__ void __launch_bounds__(128 + 128 * kPipes, 1) xattn_kernel(const __gr
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_s, 0);
+  pdl_launch();  // set-up done (common.cuh: programmatic dependent launch)
 
   if (warp == 0) {
     // ---------------------------------------------------------------- TMA producer
+    pdl_wait();  // q comes from the previous kernel of the step
     const uint32_t leader = elect_one();
     int run = -1, prev_bh = -1;
     for (int k = 0; k < nitems; ++k) {
@@ -227,6 +229,7 @@ __global__ void __launch_bounds__(128 + 128 * kPipes, 1) xattn_kernel(const __gr
     }
   } else if (warp >= 4 && (warp - 4) / 4 < p.np) {
     // ---------------------------------------------------------------- softmax warpgroup of pipeline `pipe`
+    pdl_wait();  // the output rows may still be read by an earlier kernel
     const int pipe = (warp - 4) >> 2;
     const int qd = warp & 3;
     const int r = qd * 32 + lane;  // query row in the tile == TMEM lane
@@ -333,10 +336,9 @@ int launch_cross_attention(const b200sd_attn_params& h, const DeviceInfo& di, cu
   if (int e = ensure_dyn_smem(reinterpret_cast<const void*>(&xattn_kernel<8, 2>), di.max_smem_optin - 512)) return e;
   auto launch = [&](const XAttnLaunch& X) -> int {
     if (X.d.KP <= 80)
-      xattn_kernel<5, 3><<<X.grid, X.threads, X.smem_bytes, stream>>>(X.d);
+      B200SD_CUDA_CHECK(launch_pdl(kPdlAttention, xattn_kernel<5, 3>, dim3(X.grid), dim3(X.threads), X.smem_bytes, stream, X.d));
     else
-      xattn_kernel<8, 2><<<X.grid, X.threads, X.smem_bytes, stream>>>(X.d);
-    B200SD_CUDA_CHECK(cudaGetLastError());
+      B200SD_CUDA_CHECK(launch_pdl(kPdlAttention, xattn_kernel<8, 2>, dim3(X.grid), dim3(X.threads), X.smem_bytes, stream, X.d));
     return B200SD_OK;
   };
   XAttnLaunch L;

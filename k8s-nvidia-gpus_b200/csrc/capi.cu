@@ -7,6 +7,7 @@
 #include <utility>
 #include <vector>
 
+#include <stdlib.h>
 #include <string.h>
 
 #include "host.cuh"
@@ -61,6 +62,14 @@ int ensure_dyn_smem(const void* kernel, int bytes) {
   B200SD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
   g_smem_set.insert(key);
   return B200SD_OK;
+}
+
+bool pdl_enabled(int family) {
+  static const int mask = [] {
+    const char* e = getenv("B200SD_PDL");
+    return e != nullptr ? atoi(e) : kPdlGemm;  // measured (profiles/README.md): the attribute pays on the GEMMs only
+  }();
+  return (mask & family) != 0;
 }
 
 static std::mutex g_cache_mu;

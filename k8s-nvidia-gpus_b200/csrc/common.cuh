@@ -105,6 +105,15 @@ __device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
   }
 }
 
+// ------------------------------------------------------------------ programmatic dependent launch
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start (on SMs the previous kernel has
+// left) before that kernel has finished: its set-up - barrier init, TMEM allocation, descriptor prefetch - then runs
+// under the previous kernel's tail.  pdl_wait() returns once every earlier kernel of the stream has completed and its
+// writes are visible: NOTHING produced inside the step may be read, and no global memory written, before it.
+// pdl_launch() lets the NEXT kernel's blocks be scheduled as soon as this grid's blocks have all issued it or exited.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // generic-proxy writes to shared memory -> visible to the async proxy (TMA / UMMA operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -189,8 +189,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, tmem_base_s, 0);  // warp-uniform for the issue loop
+  pdl_launch();  // set-up done: the next kernel's blocks may take the SMs this grid leaves (see common.cuh)
 
   if (warp == 0) {
+    pdl_wait();  // activations (and the weights' neighbours in memory) come from earlier kernels of the step
     // -------------------------------------------------------------- TMA producer: whole warp converged, one elected
     // lane issues (see the "_w" note in common.cuh); the k-block -> (tap, channel block) walk is incremental
     const uint32_t leader = elect_one();
@@ -305,6 +307,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     }
   } else if (warp >= 4) {
     // -------------------------------------------------------------- epilogue: 2 warpgroups x 4 warps
+    pdl_wait();  // row biases, residuals, statistics slots, split-K slices and the output all belong to the step
     const int q = warp & 3;            // TMEM lane quarter
     const int wg = (warp - 4) >> 2;    // warpgroup: alternate column groups
     const int r = q * 32 + lane;       // accumulator row == staging row
@@ -727,13 +730,18 @@ static int launch_one(const GemmDev& d, int grid, int smem_bytes, int max_smem, 
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = smem_bytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = P ? 2 : 1;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  if (pdl_enabled(kPdlGemm)) {  // programmatic dependent launch: set-up overlaps the previous kernel's tail
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.numAttrs = 2;
+  }
   B200SD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_conv_kernel<F, G, R, P>, d));
   return B200SD_OK;
 }

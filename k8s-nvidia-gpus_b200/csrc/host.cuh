@@ -60,6 +60,31 @@ void launch_cache_put(int family, const void* params, size_t params_bytes, const
 // shape does not fit that kernel (the caller falls through to the general flash kernel), < 0 on error.
 int launch_cross_attention(const b200sd_attn_params& h, const DeviceInfo& di, cudaStream_t stream);
 
+// Programmatic dependent launch per kernel family; B200SD_PDL is a bit mask (1 GEMM, 2 attention, 4 norms; 0 = off;
+// default 1), read once.  Every kernel family issues griddepcontrol.launch_dependents early either way, so a GEMM that
+// follows a norm or attention kernel starts its set-up on the SMs that kernel has already left.
+enum { kPdlGemm = 1, kPdlAttention = 2, kPdlNorm = 4 };
+bool pdl_enabled(int family);
+
+// kernel<<<grid, block, smem, stream>>>(args...) with programmatic dependent launch allowed: every kernel launched
+// through this calls pdl_wait() (common.cuh) before its first access to global memory.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(int family, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled(family) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int pow2_ceil(int v) {

@@ -50,8 +50,10 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
   const int cpg = C / groups;
   const int p_begin = blockIdx.x * pix_per_cta;
   const int p_end = min(hw, p_begin + pix_per_cta);
+  pdl_launch();
   for (int i = threadIdx.x; i < copies * groups * kGnSlotWords64; i += blockDim.x) gacc_all[i] = 0ull;
   __syncthreads();
+  pdl_wait();  // programmatic dependent launch (common.cuh): nothing of the step is touched before this
   auto add_run = [&](int g, float rs, float rq) {
     long long H, L;
     fixed_split(rs, H, L);
@@ -140,6 +142,8 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
                                                                 const float* __restrict__ beta, act_t* __restrict__ out,
                                                                 int hw, int c0, int c1, int groups, int pix_per_cta,
                                                                 int silu, float eps) {
+  pdl_launch();
+  pdl_wait();
   const int n = blockIdx.y;
   const int C = c0 + c1;
   const int octs = C >> 3;
@@ -224,6 +228,8 @@ __global__ void __launch_bounds__(kNormThreads, (kVecs <= 5 ? 4 : 1)) layernorm_
                                                                  const float* __restrict__ gamma,
                                                                  const float* __restrict__ beta, act_t* __restrict__ out,
                                                                  int rows, int c, float eps) {
+  pdl_launch();
+  pdl_wait();
   constexpr int kRowsPerWarp = 32 / kLPR;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int sub = lane / kLPR, l = lane % kLPR;
@@ -389,11 +395,10 @@ extern "C" int b200sd_groupnorm_stats(const b200sd_groupnorm_params* hp, b200sd_
   if (int e = gn_check(*hp, &ppc, &chunks)) return e;
   const b200sd_groupnorm_params& h = *hp;
   dim3 grid(chunks, h.nimg);
-  gn_stats_kernel<<<grid, kNormThreads, gn_stats_smem(h.groups),
-                    static_cast<cudaStream_t>(stream_)>>>(static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1),
-                                                          static_cast<unsigned long long*>(h.stats), h.hw, h.c0, h.c1,
-                                                          h.groups, ppc);
-  B200SD_CUDA_CHECK(cudaGetLastError());
+  B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, gn_stats_kernel, grid, dim3(kNormThreads), gn_stats_smem(h.groups),
+                               static_cast<cudaStream_t>(stream_), static_cast<const act_t*>(h.x0),
+                               static_cast<const act_t*>(h.x1), static_cast<unsigned long long*>(h.stats), h.hw, h.c0,
+                               h.c1, h.groups, ppc));
   return B200SD_OK;
 }
 
@@ -406,10 +411,11 @@ extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_
   const int C = h.c0 + h.c1;
   (void)C;
   dim3 grid(chunks, h.nimg);
-  gn_apply_kernel<<<grid, kNormThreads, 0, static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<const unsigned long long*>(h.stats),
-      h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, gn_silu_mode(h.silu), h.eps);
-  B200SD_CUDA_CHECK(cudaGetLastError());
+  B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, gn_apply_kernel, grid, dim3(kNormThreads), 0, static_cast<cudaStream_t>(stream_),
+                               static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1),
+                               static_cast<const unsigned long long*>(h.stats), h.gamma, h.beta,
+                               static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, gn_silu_mode(h.silu),
+                               h.eps));
   return B200SD_OK;
 }
 
@@ -491,13 +497,17 @@ extern "C" int b200sd_layernorm(const b200sd_layernorm_params* hp, b200sd_stream
   const int warps = kNormThreads / 32;
   B200SD_REQUIRE(aligned16(h.gamma) && aligned16(h.beta), B200SD_ERR_BAD_ALIGNMENT, "layernorm: gamma/beta alignment");
   if (octs <= 8 * 5)  // <= 320 channels: 8 lanes per row, 4 rows per warp
-    layernorm_kernel<8, 5><<<ceil_div(h.rows, warps * 4), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<8, 5>, dim3(ceil_div(h.rows, warps * 4)), dim3(kNormThreads), 0, s, x,
+                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
   else if (octs <= 16 * 5)  // <= 640
-    layernorm_kernel<16, 5><<<ceil_div(h.rows, warps * 2), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<16, 5>, dim3(ceil_div(h.rows, warps * 2)), dim3(kNormThreads), 0, s, x,
+                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
   else if (octs <= 32 * 5)  // <= 1280
-    layernorm_kernel<32, 5><<<ceil_div(h.rows, warps), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<32, 5>, dim3(ceil_div(h.rows, warps)), dim3(kNormThreads), 0, s, x,
+                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
   else
-    layernorm_kernel<32, 16><<<ceil_div(h.rows, warps), kNormThreads, 0, s>>>(x, h.gamma, h.beta, o, h.rows, h.c, h.eps);
+    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<32, 16>, dim3(ceil_div(h.rows, warps)), dim3(kNormThreads), 0, s, x,
+                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }

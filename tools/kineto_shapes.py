@@ -32,6 +32,7 @@ evs = sorted([e for e in prof.events() if e.device_type.name == "CUDA" and "emse
 calls = [c for c in job.step_plan.calls if c.name != "b200sd_memset_zero"]
 assert len(evs) == len(calls), (len(evs), len(calls))
 agg = collections.OrderedDict()
+frontier = evs[0].time_range.start  # kernels may become resident under their predecessor's tail: count each from the end of what ran before it
 for e, c in zip(evs, calls):
     p = c.params
     if c.name == "b200sd_gemm":
@@ -46,7 +47,8 @@ for e, c in zip(evs, calls):
         key, fl = c.name.replace("b200sd_", ""), 0.0
     a = agg.setdefault(key, [0, 0.0, 0.0])
     a[0] += 1
-    a[1] += e.device_time_total
+    a[1] += max(0.0, e.time_range.end - max(e.time_range.start, frontier))
+    frontier = max(frontier, e.time_range.end)
     a[2] += fl
 tot = sum(a[1] for a in agg.values())
 print(f"one denoise step: {tot / 1e3:.3f} ms kernel time")
