@@ -136,6 +136,13 @@ typedef struct {
   const void* ln_in_stats;
   const float* ln_colsum;
   float ln_eps;
+  /* Non-zero: the caller guarantees that nothing still in flight on the device writes `w` when this call is enqueued
+   * (model weights, as opposed to an activation used as the B operand).  The kernel is launched with programmatic
+   * stream serialisation: its blocks may become resident while the previous kernel of the stream is still running,
+   * and with this flag they fetch the first weight tiles (and prefetch the rest of their first tile's weights into
+   * L2) before waiting for that kernel; everything else (a0 / a1, residual, biases, statistics, the output) is only
+   * touched after it has completed.  0: weights are read after the wait as well. */
+  int32_t weights_static;
 } b200sd_gemm_params;
 int b200sd_gemm(const b200sd_gemm_params* p, b200sd_stream stream);
 /* bytes of split-K workspace these parameters need (0 when split_k <= 1 or the parameters are rejected) */

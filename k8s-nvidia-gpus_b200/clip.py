@@ -85,5 +85,5 @@ class CLIPTextEngine:
             bld.add(ops.layernorm(eos.t, ln.t, fin_w, fin_b, rows=nseq, c=c, eps=cfg["eps"]))
             pooled = bld.persistent((nseq, proj), zero=False)
             bld.add(ops.gemm(ln.t, W.cat_linear(["text_projection"]), pooled, nimg=1, h=1, w_=nseq, c0=c, n=proj,
-                             ksize=1))
+                             ksize=1, weights_static=True))
         return bld.finish(), out, pooled

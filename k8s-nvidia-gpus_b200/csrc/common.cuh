@@ -315,6 +315,17 @@ __device__ __forceinline__ void tma_load_2d_w(uint32_t leader, uint32_t dst, con
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1), "r"(leader)
       : "memory");
 }
+// L2 prefetch of one box of a 2-D tensor map (no shared-memory destination, no barrier)
+__device__ __forceinline__ void tma_prefetch_l2_2d_w(uint32_t leader, const CUtensorMap* tm, int c0, int c1) {
+  asm volatile(
+      "{\n"
+      ".reg .pred e;\n"
+      "setp.ne.b32 e, %3, 0;\n"
+      "@e cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];\n"
+      "}\n" ::"l"(reinterpret_cast<uint64_t>(tm)),
+      "r"(c0), "r"(c1), "r"(leader)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_2d_pair_w(uint32_t leader, uint32_t dst, const CUtensorMap* tm, uint32_t bar,
                                                     int c0, int c1) {
   asm volatile(

@@ -101,6 +101,7 @@ struct alignas(64) GemmDev {
   // last at the tile's counter adds the slices IN INDEX ORDER (so the result does not depend on who arrives when) and
   // runs the epilogue.  Counters are zero at rest (the finishing unit re-arms its tile).
   int split_k;
+  int b_static;  // weights are not written by anything in flight: they may be fetched before griddepcontrol.wait
   FastDiv div_split;
   float* ws;   // [tiles][split_k] fp32 slices of 128 x BN, each stored [BN / 32 chunks][8 pieces][128 rows][4]
   int* cnt;    // [tiles]
@@ -192,12 +193,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
   pdl_launch();  // set-up done: the next kernel's blocks may take the SMs this grid leaves (see common.cuh)
 
   if (warp == 0) {
-    pdl_wait();  // activations (and the weights' neighbours in memory) come from earlier kernels of the step
     // -------------------------------------------------------------- TMA producer: whole warp converged, one elected
     // lane issues (see the "_w" note in common.cuh); the k-block -> (tap, channel block) walk is incremental
     const uint32_t leader = elect_one();
     int stage = 0;
     uint32_t phase = 0;
+    // Programmatic dependent launch: this block may be resident while the previous kernel of the stream still runs.
+    // Static weights do not depend on it: the B tiles of the first ring pass are requested (and their barriers armed
+    // for the whole stage) before the wait, the A tiles follow after it.
+    int pre = 0;
+    if (p.b_static && tile0 < num_units) {
+      const int tile = static_cast<int>(fdiv(static_cast<uint32_t>(tile0), p.div_split));
+      const int split = tile0 - tile * p.split_k;
+      const int kb_begin = split * num_kb / p.split_k, kb_end = (split + 1) * num_kb / p.split_k;
+      int n0, h0, w0, col0;
+      decode_tile(p, tile, rank, n0, h0, w0, col0);
+      const int ntile = (min(p.BN, p.N - col0) + 15) & ~15;
+      const int bcol = kPair ? col0 + static_cast<int>(rank) * (ntile / 2) : col0;
+      pre = min(p.num_stages, kb_end - kb_begin);
+      for (int s = 0; s < pre; ++s) {
+        const uint32_t bar = bar0 + 8 * (kBarFull + s);
+        const uint32_t sb = tiles_base + s * stage_bytes + kABytes;
+        const int kcol = (kb_begin + s) * kBlockK;
+        if (kPair) {
+          if (rank == 0) mbar_arrive_expect_tx_w(leader, bar, 2 * stage_bytes);
+          tma_load_2d_pair_w(leader, sb, &p.tmB, bar, kcol, bcol);
+        } else {
+          mbar_arrive_expect_tx_w(leader, bar, stage_bytes);
+          tma_load_2d_w(leader, sb, &p.tmB, bar, kcol, bcol);
+          if (p.wide) tma_load_2d_w(leader, sb + b_bytes / 2, &p.tmB, bar, kcol, bcol + p.BN / 2);
+        }
+      }
+    }
+    pdl_wait();  // activations come from earlier kernels of the step
     for (int unit = tile0; unit < num_units; unit += tile_step) {
       const int tile = static_cast<int>(fdiv(static_cast<uint32_t>(unit), p.div_split));
       const int split = unit - tile * p.split_k;
@@ -211,6 +239,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       int cb = kb_begin - tap0 * cblk, kh = tap0 / p.kw_taps;
       int kw = tap0 - kh * p.kw_taps;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
+        const bool b_issued = pre > 0;  // first ring pass of the first unit: armed and B requested before the wait
+        pre -= b_issued ? 1 : 0;
         mbar_wait(bar0 + 8 * (kBarEmpty + stage), phase ^ 1u);
         const uint32_t bar = bar0 + 8 * (kBarFull + stage);
         const uint32_t sa = tiles_base + stage * stage_bytes;
@@ -218,9 +248,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         const CUtensorMap* tmA = first ? &p.tmA0 : &p.tmA1;
         const int ch = (first ? cb : cb - p.cblk0) * kBlockK;
         if (kPair) {
-          if (rank == 0) mbar_arrive_expect_tx_w(leader, bar, 2 * stage_bytes);  // both CTAs' loads land on the leader's barrier
+          if (rank == 0 && !b_issued) mbar_arrive_expect_tx_w(leader, bar, 2 * stage_bytes);  // both CTAs' loads land on the leader's barrier
           tma_load_4d_pair_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
-          tma_load_2d_pair_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+          if (!b_issued) tma_load_2d_pair_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+        } else if (b_issued) {
+          tma_load_4d_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
         } else {
           mbar_arrive_expect_tx_w(leader, bar, stage_bytes);
           tma_load_4d_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
@@ -302,6 +334,28 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         if (++acc == nacc) {
           acc = 0;
           acc_phase ^= 1u;
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // -------------------------------------------------------------- weight prefetch (static weights only): the block
+    // that owns M unit 0 of a column tile asks L2 for the rest of that tile's weight slab while the previous kernel of
+    // the stream is still running (at small batch the step streams 1.7 GB of weights through short kernels that
+    // would otherwise each start cold).  No dependence on earlier kernels, so no griddepcontrol.wait.
+    if (p.b_static && tile0 < num_units) {
+      const int tile = static_cast<int>(fdiv(static_cast<uint32_t>(tile0), p.div_split));
+      const int split = tile0 - tile * p.split_k;
+      const int m_units = static_cast<int>(p.div_munits.d);
+      const int nt = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits));
+      if (tile - nt * m_units == 0) {
+        const uint32_t leader = elect_one();
+        const int kb_begin = split * num_kb / p.split_k, kb_end = (split + 1) * num_kb / p.split_k;
+        const int col0 = nt * p.BN;
+        const int ntile = (min(p.BN, p.N - col0) + 15) & ~15;
+        const int bcol = kPair ? col0 + static_cast<int>(rank) * (ntile / 2) : col0;
+        for (int kb = kb_begin + p.num_stages; kb < kb_end; ++kb) {
+          tma_prefetch_l2_2d_w(leader, &p.tmB, kb * kBlockK, bcol);
+          if (!kPair && p.wide) tma_prefetch_l2_2d_w(leader, &p.tmB, kb * kBlockK, bcol + p.BN / 2);
         }
       }
     }
@@ -860,6 +914,7 @@ static int gemm_impl(const b200sd_gemm_params* hp, b200sd_stream stream_, size_t
   d.tiles_ncol = ceil_div(h.n, d.BN);
   d.div_munits = make_fastdiv(static_cast<uint32_t>(d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m));
   d.split_k = split;
+  d.b_static = h.weights_static != 0 ? 1 : 0;
   d.div_split = make_fastdiv(static_cast<uint32_t>(split));
   d.div_tw = make_fastdiv(static_cast<uint32_t>(d.tiles_w));
   d.div_twth = make_fastdiv(static_cast<uint32_t>(d.tiles_w * d.tiles_h));

@@ -280,7 +280,7 @@ class Builder:
                                a1=None if a1 is None else a1.t, c1=0 if a1 is None else a1.c, bias=b, rowbias=rowbias,
                                ld_rowbias=ld_rowbias, residual=None if residual is None else residual.t,
                                ldr=0 if residual is None else residual.c, ldc=ldc, act=act, gn_stats=st,
-                               gn_groups=gn_groups if st is not None else 0, split_k=sk,
+                               gn_groups=gn_groups if st is not None else 0, split_k=sk, weights_static=True,
                                ln_out_stats=(rs := self.stats_slice(a0.rows, 1) if rowstats else None)), sk)
         return Act(out, a0.nimg, a0.h, a0.w, cout if ldc is None else ldc,
                    stats=None if st is None else (st, gn_groups), rowstats=rs)
@@ -301,7 +301,7 @@ class Builder:
         self.add_gemm(ops.gemm(x.t, w, out, c0=x.c, n=n, ksize=1, bias=b,
                                residual=None if residual is None else residual.t,
                                ldr=0 if residual is None else residual.c, act=act, rowbias=rowbias,
-                               ld_rowbias=ld_rowbias, split_k=sk,
+                               ld_rowbias=ld_rowbias, split_k=sk, weights_static=True,
                                ln_out_stats=(rs := self.stats_slice(x.rows, 1) if rowstats else None),
                                ln_in_stats=x.rowstats if ln is not None else None, ln_colsum=ln, ln_eps=ln_eps,
                                **geo), sk)
@@ -358,7 +358,8 @@ class Builder:
             for px in (0, 1):
                 self.add(ops.gemm(x.t, w4[py * 2 + px], out[:, py::2, px::2, :], nimg=x.nimg, h=x.h, w_=x.w, c0=x.c,
                                   n=cout, ksize=1, kh=2, kw=2, off_h=py - 1, off_w=px - 1, bias=b, ldc=cout,
-                                  out_strides=strides, gn_stats=st, gn_groups=gn_groups if st is not None else 0))
+                                  out_strides=strides, gn_stats=st, gn_groups=gn_groups if st is not None else 0,
+                                  weights_static=True))
         return Act(out, x.nimg, 2 * x.h, 2 * x.w, cout, stats=None if st is None else (st, gn_groups))
 
     def conv_s2(self, W: DeviceWeights, name, x: Act, cout, gn_groups=None):
@@ -374,7 +375,7 @@ class Builder:
         sk = self.split_k_for(ho * wo, x.nimg * ho * wo, cout, 9 * -(-x.c // 64))
         self.add_gemm(ops.gemm(x.t, W.conv(name), out, nimg=x.nimg, h=ho, w_=wo, c0=x.c, n=cout, ksize=3, kh=3, kw=3,
                                off_h=-1, off_w=-1, stride=2, bias=W.vec(name + ".bias"), gn_stats=st,
-                               gn_groups=gn_groups if st is not None else 0, split_k=sk), sk)
+                               gn_groups=gn_groups if st is not None else 0, split_k=sk, weights_static=True), sk)
         return Act(out, x.nimg, ho, wo, cout, stats=None if st is None else (st, gn_groups))
 
     # ------------------------------------------------------------------ composite blocks (UNet + VAE)

@@ -34,7 +34,7 @@ class GemmParams(C.Structure):
                 ("gn_rows_per_img", i32), ("kh", i32), ("kw", i32), ("off_h", i32), ("off_w", i32), ("stride", i32),
                 ("out_pix_stride", i32), ("out_row_stride", i32), ("out_img_stride", i32), ("split_k", i32),
                 ("workspace", vp), ("workspace_bytes", i64), ("ln_out_stats", vp), ("ln_in_stats", vp),
-                ("ln_colsum", vp), ("ln_eps", f32)]
+                ("ln_colsum", vp), ("ln_eps", f32), ("weights_static", i32)]
 
 
 class AttnParams(C.Structure):

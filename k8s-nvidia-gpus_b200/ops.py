@@ -7,6 +7,8 @@ from __future__ import annotations
 
 import ctypes as C
 
+import os
+
 import torch
 
 from . import lib as L
@@ -77,11 +79,14 @@ def geglu_perm(n2: int) -> torch.Tensor:
 
 
 # ------------------------------------------------------------------------------------------------ call builders
+_WEIGHTS_STATIC = os.environ.get("B200SD_WEIGHTS_STATIC", "1") != "0"  # A/B switch: early weight fetch (b200sd.h)
 def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld1=None, bias=None, rowbias=None,
          ld_rowbias=0, residual=None, ldr=0, ldc=None, act=L.ACT_NONE, out_dtype=None, alpha=1.0, bn_hint=0,
          gn_stats=None, gn_groups=0, gn_rows_per_img=0, kh=0, kw=0, off_h=0, off_w=0, stride=0, out_strides=None,
-         split_k=0, workspace=None, ln_out_stats=None, ln_in_stats=None, ln_colsum=None, ln_eps=1e-5):
-    """out_strides: (pixel, row, image) strides of the output in elements when its pixels are interleaved into a larger
+         split_k=0, workspace=None, ln_out_stats=None, ln_in_stats=None, ln_colsum=None, ln_eps=1e-5,
+         weights_static=False):
+    """weights_static: `w` holds model weights (nothing in flight writes it) - see b200sd.h.
+    out_strides: (pixel, row, image) strides of the output in elements when its pixels are interleaved into a larger
     tensor (pass the strided VIEW as `out`: its data_ptr is the first pixel)."""
     p = L.GemmParams()
     p.a0, p.a1, p.w, p.out = _ptr(a0), _ptr(a1), _ptr(w), _ptr(out)
@@ -105,6 +110,7 @@ def gemm(a0, w, out, *, nimg, h, w_, c0, n, ksize=1, a1=None, c1=0, ld0=None, ld
     if out_strides is not None:
         p.out_pix_stride, p.out_row_stride, p.out_img_stride = out_strides
     p.split_k = split_k
+    p.weights_static = 1 if weights_static and _WEIGHTS_STATIC else 0
     p.ln_out_stats, p.ln_in_stats, p.ln_colsum, p.ln_eps = _ptr(ln_out_stats), _ptr(ln_in_stats), _ptr(ln_colsum), ln_eps
     if workspace is not None:
         p.workspace, p.workspace_bytes = _ptr(workspace), workspace.numel() * workspace.element_size()

@@ -91,7 +91,7 @@ class UNetEngine:
                 out = bld.persistent((nctx, 1, seq, 2 * c), zero=False)
                 bld.add(ops.gemm(ctxs[0], w, out, nimg=1, h=1, w_=nctx * seq, c0=dims[0],
                                  a1=ctxs[1] if len(ctxs) > 1 else None, c1=dims[1] if len(ctxs) > 1 else 0, n=2 * c,
-                                 ksize=1))
+                                 ksize=1, weights_static=True))
                 kv[b] = out
         aug = None
         if self.cfg.get("addition_embed_type") == "text_time":
@@ -104,10 +104,10 @@ class UNetEngine:
             h1 = bld.alloc((nctx, 1, 1, temb_dim))
             bld.add(ops.gemm(text_embeds, W.conv("add_embedding.linear_1", (c0, c1)), h1, nimg=1, h=1, w_=nctx, c0=c0,
                              a1=time_ids_emb, c1=c1, n=temb_dim, ksize=1, bias=W.vec("add_embedding.linear_1.bias"),
-                             act=L.ACT_SILU))
+                             act=L.ACT_SILU, weights_static=True))
             aug = bld.persistent((nctx, temb_dim), dtype=torch.float32, zero=False)
             bld.add(ops.gemm(h1, W.conv("add_embedding.linear_2"), aug, nimg=1, h=1, w_=nctx, c0=temb_dim, n=temb_dim,
-                             ksize=1, bias=W.vec("add_embedding.linear_2.bias")))
+                             ksize=1, bias=W.vec("add_embedding.linear_2.bias"), weights_static=True))
         return bld.finish(), kv, aug
 
     # ------------------------------------------------------------------ one denoise step
