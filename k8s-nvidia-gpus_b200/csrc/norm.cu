@@ -31,41 +31,29 @@ __device__ __forceinline__ void store8(act_t* p, const float (&f)[8]) {
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: stats
-// grid (chunks, nimg).  Each thread owns one 8-channel vector column ("octet") and walks pixels, keeping 8 sums and
-// 8 sums of squares in registers (fixed order: deterministic); the per-thread results are then added as 64-bit
-// fixed-point integers (common.cuh, fixed_split) - first into shared memory, then one global add per (group, CTA)
-// word - so the totals are bit-identical from run to run whatever the CTA / warp arrival order.
+// grid (chunks, nimg).  Each thread owns one 8-channel vector column ("octet") and a pixel stream, keeping 8 sums and
+// 8 sums of squares in registers.  The CTA's partial sums are combined in shared memory by a FIXED-order fp32 tree
+// (octet sums of every pixel stream -> one thread per (group, statistic)), converted once per (group, statistic, CTA)
+// to 64-bit fixed point (common.cuh, fixed_split) and added to the global slot as integers: the totals are
+// bit-identical from run to run whatever the CTA arrival order, and - pixels per CTA being a function of the
+// per-image shape only - whatever batch the image rides in.  (An earlier version converted per thread and used 64-bit
+// shared-memory atomics: 8.7 instructions per element, most of them in that tail.)
 __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __restrict__ x0,
                                                                 const act_t* __restrict__ x1,
                                                                 unsigned long long* __restrict__ stats, int hw, int c0,
                                                                 int c1, int groups, int pix_per_cta) {
-  extern __shared__ unsigned long long gacc_all[];  // [copies][groups][4]: {sum H, sum L, sumsq H, sumsq L}
-  // one private copy per warp (when it fits): 64-bit shared-memory atomics are compare-and-swap loops, and with a single
-  // copy the warps of a CTA spend their time retrying on each other's groups
-  const int copies = groups <= 64 ? kNormThreads / 32 : 1;
-  unsigned long long* gacc = gacc_all + ((threadIdx.x >> 5) % copies) * groups * kGnSlotWords64;
+  extern __shared__ float gred[];  // [streams][octs][16]: {8 sums, 8 sums of squares} of a (pixel stream, octet)
   const int n = blockIdx.y;
   const int C = c0 + c1;
   const int octs = C >> 3;
   const int cpg = C / groups;
   const int p_begin = blockIdx.x * pix_per_cta;
   const int p_end = min(hw, p_begin + pix_per_cta);
-  pdl_launch();
-  for (int i = threadIdx.x; i < copies * groups * kGnSlotWords64; i += blockDim.x) gacc_all[i] = 0ull;
-  __syncthreads();
-  pdl_wait();  // programmatic dependent launch (common.cuh): nothing of the step is touched before this
-  auto add_run = [&](int g, float rs, float rq) {
-    long long H, L;
-    fixed_split(rs, H, L);
-    atomicAdd(&gacc[4 * g], static_cast<unsigned long long>(H));
-    atomicAdd(&gacc[4 * g + 1], static_cast<unsigned long long>(L));
-    fixed_split(rq, H, L);
-    atomicAdd(&gacc[4 * g + 2], static_cast<unsigned long long>(H));
-    atomicAdd(&gacc[4 * g + 3], static_cast<unsigned long long>(L));
-  };
   const int Wd = min(octs, kNormThreads);
   const int S = kNormThreads / Wd;
   const int stream = threadIdx.x / Wd;
+  pdl_launch();
+  pdl_wait();  // programmatic dependent launch (common.cuh): nothing of the step is touched before this
   if (stream < S) {
     for (int oct = threadIdx.x % Wd; oct < octs; oct += Wd) {
       const int ch0 = oct * 8;
@@ -106,42 +94,45 @@ __global__ void __launch_bounds__(kNormThreads) gn_stats_kernel(const act_t* __r
           q[e] = fmaf(f[e], f[e], q[e]);
         }
       }
-      // merge runs of equal group before touching shared memory
-      int g_cur = ch0 / cpg;
-      float rs = 0.f, rq = 0.f;
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int g = (ch0 + e) / cpg;
-        if (g != g_cur) {
-          add_run(g_cur, rs, rq);
-          rs = rq = 0.f;
-          g_cur = g;
-        }
-        rs += s[e];
-        rq += q[e];
-      }
-      add_run(g_cur, rs, rq);
+      float4* dst = reinterpret_cast<float4*>(gred + (static_cast<size_t>(stream) * octs + oct) * 16);
+      dst[0] = make_float4(s[0], s[1], s[2], s[3]);
+      dst[1] = make_float4(s[4], s[5], s[6], s[7]);
+      dst[2] = make_float4(q[0], q[1], q[2], q[3]);
+      dst[3] = make_float4(q[4], q[5], q[6], q[7]);
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < groups * kGnSlotWords64; i += blockDim.x) {
-    unsigned long long v = 0ull;
-    for (int cpy = 0; cpy < copies; ++cpy) v += gacc_all[cpy * groups * kGnSlotWords64 + i];
-    if (v != 0ull) atomicAdd(&stats[static_cast<size_t>(n) * groups * kGnSlotWords64 + i], v);
+  // one thread per (group, statistic): the group's channels x the pixel streams, always in the same order
+  for (int i = threadIdx.x; i < 2 * groups; i += blockDim.x) {
+    const int g = i >> 1, which = i & 1;
+    float acc = 0.f;
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c) {
+      const float* col = gred + (c >> 3) * 16 + which * 8 + (c & 7);
+      for (int st = 0; st < S; ++st) acc += col[static_cast<size_t>(st) * octs * 16];
+    }
+    long long H, L;
+    fixed_split(acc, H, L);
+    unsigned long long* slot = stats + (static_cast<size_t>(n) * groups + g) * kGnSlotWords64 + which * 2;
+    atomicAdd(slot, static_cast<unsigned long long>(H));
+    atomicAdd(slot + 1, static_cast<unsigned long long>(L));
   }
 }
 
 // ---------------------------------------------------------------------------------------------- GroupNorm: apply
 // Same thread -> (octet, pixel stream) mapping as the statistics pass: a thread normalises ONE 8-channel column, so its
 // 8 scales and 8 shifts live in registers for the whole walk (no per-element shared-memory lookups) and the inner
-// loop is load16 -> 8 fma (+SiLU) -> store16 with four pixels in flight.
+// loop is load16 -> 8 fma (+SiLU) -> store16 with four pixels in flight.  The (mean, rstd) of the image's groups are
+// finalised once per CTA (one thread per group, in double from the integer totals) into shared memory.  kSilu is a
+// template parameter: as a run-time value the compiler evaluated both SiLU forms per element and selected.
+template <int kSilu>
 __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* __restrict__ x0,
                                                                 const act_t* __restrict__ x1,
                                                                 const unsigned long long* __restrict__ stats,
                                                                 const float* __restrict__ gamma,
                                                                 const float* __restrict__ beta, act_t* __restrict__ out,
                                                                 int hw, int c0, int c1, int groups, int pix_per_cta,
-                                                                int silu, float eps) {
+                                                                float eps) {
+  extern __shared__ float2 gmr[];  // [groups] (mean, rstd)
   pdl_launch();
   pdl_wait();
   const int n = blockIdx.y;
@@ -149,35 +140,32 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
   const int octs = C >> 3;
   const int cpg = C / groups;
   const double inv_cnt = 1.0 / (static_cast<double>(hw) * static_cast<double>(cpg));
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+    // exact integer totals -> mean / variance in double (no E[x^2] - mean^2 cancellation in fp32)
+    const unsigned long long* sl = stats + (static_cast<size_t>(n) * groups + g) * kGnSlotWords64;
+    const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(sl);
+    const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(sl + 2);
+    const unsigned long long sw[2] = {a.x, a.y}, qw[2] = {b.x, b.y};
+    const double m = fixed_value(sw) * inv_cnt;
+    const double var = fmax(fixed_value(qw) * inv_cnt - m * m, 0.0);
+    gmr[g] = make_float2(static_cast<float>(m), rsqrtf(static_cast<float>(var) + eps));
+  }
+  __syncthreads();
   const int p_begin = blockIdx.x * pix_per_cta;
   const int p_end = min(hw, p_begin + pix_per_cta);
   const int Wd = min(octs, kNormThreads);
   const int S = kNormThreads / Wd;
   const int stream = threadIdx.x / Wd;
   if (stream >= S) return;
+  auto act = [](float y) { return kSilu == 2 ? silu_tanh_f(y) : (kSilu == 1 ? silu_f(y) : y); };
   for (int oct = threadIdx.x % Wd; oct < octs; oct += Wd) {
     const int ch0 = oct * 8;
     float sc[8], sh[8];
-    int g_have = -1;
-    float mean = 0.f, rstd = 0.f;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int c = ch0 + e;
-      const int g = c / cpg;
-      if (g != g_have) {
-        // exact integer totals -> mean / variance in double (no E[x^2] - mean^2 cancellation in fp32)
-        const unsigned long long* sl = stats + (static_cast<size_t>(n) * groups + g) * kGnSlotWords64;
-        const ulonglong2 a = *reinterpret_cast<const ulonglong2*>(sl);
-        const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(sl + 2);
-        const unsigned long long sw[2] = {a.x, a.y}, qw[2] = {b.x, b.y};
-        const double m = fixed_value(sw) * inv_cnt;
-        const double var = fmax(fixed_value(qw) * inv_cnt - m * m, 0.0);
-        mean = static_cast<float>(m);
-        rstd = rsqrtf(static_cast<float>(var) + eps);
-        g_have = g;
-      }
-      sc[e] = __ldg(gamma + c) * rstd;
-      sh[e] = __ldg(beta + c) - mean * sc[e];
+      const float2 mr = gmr[(ch0 + e) / cpg];
+      sc[e] = __ldg(gamma + ch0 + e) * mr.y;
+      sh[e] = __ldg(beta + ch0 + e) - mr.x * sc[e];
     }
     const act_t* src;
     int ld;
@@ -199,10 +187,7 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
         float f[8];
         unpack8(raw[u], f);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float y = fmaf(f[e], sc[e], sh[e]);
-          f[e] = silu == 2 ? silu_tanh_f(y) : (silu ? silu_f(y) : y);
-        }
+        for (int e = 0; e < 8; ++e) f[e] = act(fmaf(f[e], sc[e], sh[e]));
         store8(dst + static_cast<size_t>(p + u * S) * C, f);
       }
     }
@@ -210,13 +195,24 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
       float f[8];
       load8(src + static_cast<size_t>(p) * ld, f);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float y = fmaf(f[e], sc[e], sh[e]);
-        f[e] = silu == 2 ? silu_tanh_f(y) : (silu ? silu_f(y) : y);
-      }
+      for (int e = 0; e < 8; ++e) f[e] = act(fmaf(f[e], sc[e], sh[e]));
       store8(dst + static_cast<size_t>(p) * C, f);
     }
   }
+}
+
+// the three activation modes of gn_apply_kernel (0 none, 1 SiLU with ex2 + rcp, 2 SiLU in tanh form)
+template <typename... Args>
+static cudaError_t launch_gn_apply(bool pdl, int mode, dim3 grid, int groups, cudaStream_t s, Args... args) {
+  const size_t smem = static_cast<size_t>(groups) * sizeof(float2);
+  auto go = [&](auto kernel) -> cudaError_t {
+    if (pdl) return launch_pdl(kPdlNorm, kernel, grid, dim3(kNormThreads), smem, s, args...);
+    kernel<<<grid, kNormThreads, smem, s>>>(args...);
+    return cudaGetLastError();
+  };
+  if (mode == 2) return go(gn_apply_kernel<2>);
+  if (mode == 1) return go(gn_apply_kernel<1>);
+  return go(gn_apply_kernel<0>);
 }
 
 // ---------------------------------------------------------------------------------------------- LayerNorm
@@ -224,7 +220,7 @@ __global__ void __launch_bounds__(kNormThreads, 4) gn_apply_kernel(const act_t* 
 // several rows' loads are in flight per warp and the two reductions take log2(kLPR) shuffles.  Two-pass mean /
 // variance like the fp32 reference.
 template <int kLPR, int kVecs>
-__global__ void __launch_bounds__(kNormThreads, (kVecs <= 5 ? 4 : 1)) layernorm_kernel(const act_t* __restrict__ x,
+__global__ void __launch_bounds__(kNormThreads, (kVecs <= 3 ? 6 : kVecs <= 5 ? 4 : 1)) layernorm_kernel(const act_t* __restrict__ x,
                                                                  const float* __restrict__ gamma,
                                                                  const float* __restrict__ beta, act_t* __restrict__ out,
                                                                  int rows, int c, float eps) {
@@ -350,8 +346,11 @@ __global__ void __launch_bounds__(kNormThreads) softmax_rows_kernel(const float*
   }
 }
 
-static size_t gn_stats_smem(int groups) {
-  return static_cast<size_t>(groups <= 64 ? kNormThreads / 32 : 1) * groups * kGnSlotWords64 * sizeof(unsigned long long);
+// shared memory of gn_stats_kernel: 16 floats per (pixel stream, octet)
+static size_t gn_stats_smem(int C) {
+  const int octs = C / 8;
+  const int Wd = octs < kNormThreads ? octs : kNormThreads;
+  return static_cast<size_t>(kNormThreads / Wd) * octs * 16 * sizeof(float);
 }
 
 // SiLU after GroupNorm takes ONE MUFU op (tanh form, common.cuh silu_tanh_f) instead of two (ex2 + rcp): with two, the
@@ -370,7 +369,7 @@ static int gn_check(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chu
   B200SD_REQUIRE((h.c0 % 8) == 0 && (h.c1 % 8) == 0, B200SD_ERR_BAD_SHAPE, "groupnorm: channels must be multiples of 8");
   B200SD_REQUIRE((C % h.groups) == 0, B200SD_ERR_BAD_SHAPE, "groupnorm: %d channels not divisible by %d groups", C,
                  h.groups);
-  B200SD_REQUIRE(h.groups <= 1024 && C <= 8192, B200SD_ERR_TOO_LARGE, "groupnorm: too many groups/channels");
+  B200SD_REQUIRE(h.groups <= 1024 && C <= 6144, B200SD_ERR_TOO_LARGE, "groupnorm: too many groups/channels");
   B200SD_REQUIRE((h.c1 == 0) == (h.x1 == nullptr), B200SD_ERR_BAD_ARGUMENT, "groupnorm: x1 and c1 must agree");
   B200SD_REQUIRE(aligned16(h.x0) && aligned16(h.x1) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
                  "groupnorm: pointers must be 16-byte aligned");
@@ -379,6 +378,23 @@ static int gn_check(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chu
   // invariance).
   int ppc = (64 << 10) / (2 * C);
   if (ppc < 8) ppc = 8;
+  if (ppc > h.hw) ppc = h.hw;
+  *pix_per_cta = ppc;
+  *chunks = (h.hw + ppc - 1) / ppc;
+  return B200SD_OK;
+}
+
+// The apply pass is elementwise, so its split is free of the invariance rule above: pixels per CTA are chosen so that
+// the whole grid is resident at once (4 CTAs per SM) with equal shares - no second, mostly empty wave (the
+// statistics split gave 656 CTAs for 592 places on the 64x64 level at batch 8), and a full machine at small batch.
+static int gn_apply_split(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chunks) {
+  DeviceInfo di;
+  if (int e = get_device_info(&di)) return e;
+  const int octs = (h.c0 + h.c1) / 8;
+  const int streams = kNormThreads / (octs < kNormThreads ? octs : kNormThreads);
+  const int per_img = di.sm_count * 4 / h.nimg > 0 ? di.sm_count * 4 / h.nimg : 1;
+  int ppc = (h.hw + per_img - 1) / per_img;
+  if (ppc < 4 * streams) ppc = 4 * streams;  // at least one full round of loads per thread
   if (ppc > h.hw) ppc = h.hw;
   *pix_per_cta = ppc;
   *chunks = (h.hw + ppc - 1) / ppc;
@@ -395,7 +411,7 @@ extern "C" int b200sd_groupnorm_stats(const b200sd_groupnorm_params* hp, b200sd_
   if (int e = gn_check(*hp, &ppc, &chunks)) return e;
   const b200sd_groupnorm_params& h = *hp;
   dim3 grid(chunks, h.nimg);
-  B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, gn_stats_kernel, grid, dim3(kNormThreads), gn_stats_smem(h.groups),
+  B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, gn_stats_kernel, grid, dim3(kNormThreads), gn_stats_smem(h.c0 + h.c1),
                                static_cast<cudaStream_t>(stream_), static_cast<const act_t*>(h.x0),
                                static_cast<const act_t*>(h.x1), static_cast<unsigned long long*>(h.stats), h.hw, h.c0,
                                h.c1, h.groups, ppc));
@@ -408,14 +424,12 @@ extern "C" int b200sd_groupnorm_apply(const b200sd_groupnorm_params* hp, b200sd_
   if (int e = gn_check(*hp, &ppc, &chunks)) return e;
   const b200sd_groupnorm_params& h = *hp;
   B200SD_REQUIRE(h.out && h.gamma && h.beta, B200SD_ERR_BAD_ARGUMENT, "groupnorm_apply: out/gamma/beta required");
-  const int C = h.c0 + h.c1;
-  (void)C;
+  if (int e = gn_apply_split(h, &ppc, &chunks)) return e;
   dim3 grid(chunks, h.nimg);
-  B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, gn_apply_kernel, grid, dim3(kNormThreads), 0, static_cast<cudaStream_t>(stream_),
-                               static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1),
-                               static_cast<const unsigned long long*>(h.stats), h.gamma, h.beta,
-                               static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, gn_silu_mode(h.silu),
-                               h.eps));
+  B200SD_CUDA_CHECK(launch_gn_apply(true, gn_silu_mode(h.silu), grid, h.groups, static_cast<cudaStream_t>(stream_),
+                                    static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1),
+                                    static_cast<const unsigned long long*>(h.stats), h.gamma, h.beta,
+                                    static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, h.eps));
   return B200SD_OK;
 }
 
@@ -472,14 +486,16 @@ extern "C" int b200sd_groupnorm_noalloc(const b200sd_groupnorm_params* hp, b200s
   // the scratch still holds the previous call's sums: the accumulators of this call must start from zero
   B200SD_CUDA_CHECK(cudaMemsetAsync(h.stats, 0, static_cast<size_t>(need) * sizeof(float), s));
   dim3 grid(chunks, h.nimg);
-  gn_stats_kernel<<<grid, kNormThreads, gn_stats_smem(h.groups), s>>>(
+  gn_stats_kernel<<<grid, kNormThreads, gn_stats_smem(h.c0 + h.c1), s>>>(
       static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<unsigned long long*>(h.stats), h.hw,
       h.c0, h.c1, h.groups, ppc);
   B200SD_CUDA_CHECK(cudaGetLastError());
-  gn_apply_kernel<<<grid, kNormThreads, 0, s>>>(
-      static_cast<const act_t*>(h.x0), static_cast<const act_t*>(h.x1), static_cast<const unsigned long long*>(h.stats),
-      h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc, gn_silu_mode(h.silu), h.eps);
-  B200SD_CUDA_CHECK(cudaGetLastError());
+  if (int e = gn_apply_split(h, &ppc, &chunks)) return e;
+  grid = dim3(chunks, h.nimg);
+  B200SD_CUDA_CHECK(launch_gn_apply(false, gn_silu_mode(h.silu), grid, h.groups, s, static_cast<const act_t*>(h.x0),
+                                    static_cast<const act_t*>(h.x1), static_cast<const unsigned long long*>(h.stats),
+                                    h.gamma, h.beta, static_cast<act_t*>(h.out), h.hw, h.c0, h.c1, h.groups, ppc,
+                                    h.eps));
   return B200SD_OK;
 }
 
@@ -496,18 +512,26 @@ extern "C" int b200sd_layernorm(const b200sd_layernorm_params* hp, b200sd_stream
   const int octs = h.c / 8;
   const int warps = kNormThreads / 32;
   B200SD_REQUIRE(aligned16(h.gamma) && aligned16(h.beta), B200SD_ERR_BAD_ALIGNMENT, "layernorm: gamma/beta alignment");
-  if (octs <= 8 * 5)  // <= 320 channels: 8 lanes per row, 4 rows per warp
-    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<8, 5>, dim3(ceil_div(h.rows, warps * 4)), dim3(kNormThreads), 0, s, x,
-                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
+  static const bool narrow = [] {  // A/B switch: fewer row vectors per lane -> fewer registers, 6 CTAs per SM
+    const char* e = getenv("B200SD_LN_NARROW");
+    return !(e != nullptr && e[0] == '0');
+  }();
+  auto go = [&](auto kernel, int rows_per_cta) -> cudaError_t {
+    return launch_pdl(kPdlNorm, kernel, dim3(ceil_div(h.rows, rows_per_cta)), dim3(kNormThreads), 0, s, x, h.gamma,
+                      h.beta, o, h.rows, h.c, h.eps);
+  };
+  if (octs <= 16 * 3 && narrow)  // <= 384 channels: 16 lanes per row, 2 rows per warp
+    B200SD_CUDA_CHECK(go(layernorm_kernel<16, 3>, warps * 2));
+  else if (octs <= 8 * 5)  // <= 320 channels: 8 lanes per row, 4 rows per warp
+    B200SD_CUDA_CHECK(go(layernorm_kernel<8, 5>, warps * 4));
+  else if (octs <= 32 * 3 && narrow)  // <= 768
+    B200SD_CUDA_CHECK(go(layernorm_kernel<32, 3>, warps));
   else if (octs <= 16 * 5)  // <= 640
-    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<16, 5>, dim3(ceil_div(h.rows, warps * 2)), dim3(kNormThreads), 0, s, x,
-                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
+    B200SD_CUDA_CHECK(go(layernorm_kernel<16, 5>, warps * 2));
   else if (octs <= 32 * 5)  // <= 1280
-    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<32, 5>, dim3(ceil_div(h.rows, warps)), dim3(kNormThreads), 0, s, x,
-                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
+    B200SD_CUDA_CHECK(go(layernorm_kernel<32, 5>, warps));
   else
-    B200SD_CUDA_CHECK(launch_pdl(kPdlNorm, layernorm_kernel<32, 16>, dim3(ceil_div(h.rows, warps)), dim3(kNormThreads), 0, s, x,
-                                 h.gamma, h.beta, o, h.rows, h.c, h.eps));
+    B200SD_CUDA_CHECK(go(layernorm_kernel<32, 16>, warps));
   B200SD_CUDA_CHECK(cudaGetLastError());
   return B200SD_OK;
 }

@@ -328,3 +328,50 @@ def mode_split():
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "split":
     mode_split()
+
+
+def mode_norms():
+    """GroupNorm statistics / apply and LayerNorm on the step's main shapes, cold (L2 flushed by a 512 MB write) and
+    warm (second launch on the same input): quick timing and the ncu target for the bandwidth-bound kernels."""
+    import b200sd
+    ops = b200sd.ops
+    dt = b200sd.lib.act_dtype()
+    s = ops.current_stream()
+    n = 16
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
+
+    def run(name, call, byt):
+        res = []
+        for cold in (True, False):
+            if cold:
+                flush.fill_(1)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            call(s)
+            e1.record()
+            torch.cuda.synchronize()
+            res.append(e0.elapsed_time(e1))
+        print(f"{name:40s} cold {res[0] * 1e3:7.1f} us {byt / res[0] / 1e6:7.0f} GB/s   warm {res[1] * 1e3:7.1f} us "
+              f"{byt / res[1] / 1e6:7.0f} GB/s")
+
+    for hw, c0, c1 in [(4096, 320, 0), (4096, 320, 320), (1024, 640, 0), (1024, 640, 640), (256, 1280, 0),
+                       (256, 1280, 1280), (64, 1280, 1280)]:
+        x0 = torch.randn(n, hw, c0, device="cuda").to(dt)
+        x1 = torch.randn(n, hw, c1, device="cuda").to(dt) if c1 else None
+        C = c0 + c1
+        o = torch.empty(n, hw, C, device="cuda", dtype=dt)
+        g, b = torch.ones(C, device="cuda"), torch.zeros(C, device="cuda")
+        st = ops.groupnorm_stats_buffer(n, 32)
+        sc, ac = ops.groupnorm(x0, o, st, g, b, nimg=n, hw=hw, c0=c0, groups=32, eps=1e-5, silu=True, x1=x1, c1=c1)
+        run(f"groupnorm stats {c0}+{c1} @{hw} px", sc, 2.0 * n * hw * C)
+        run(f"groupnorm apply {c0}+{c1} @{hw} px", ac, 4.0 * n * hw * C)
+    for rows, c in [(n * 4096, 320), (n * 1024, 640), (n * 256, 1280)]:
+        x = torch.randn(rows, c, device="cuda").to(dt)
+        o = torch.empty_like(x)
+        g, b = torch.ones(c, device="cuda"), torch.zeros(c, device="cuda")
+        run(f"layernorm {rows}x{c}", ops.layernorm(x, o, g, b, rows=rows, c=c, eps=1e-5), 4.0 * rows * c)
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "norms":
+    mode_norms()
