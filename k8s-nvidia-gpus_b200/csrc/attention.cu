@@ -339,28 +339,28 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
         const bool need_mask = __any_sync(0xffffffffu, limit < kBKV);
         mbar_wait_spin((bar0 + 8 * (kBarSFull + 2 * (t) + (wg))), gi & 1);
         tc_fence_after();
-        // the whole row of the tile goes to registers and the S buffer is handed straight back: Q K^T of my next
-        // tile runs on the tensor pipe while I am still busy with this one
-        uint32_t sa[32], sb[32];
-        tmem_ld32(tS, sa);
-        tmem_ld32(tS + 32, sb);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive((bar0 + 8 * (kBarSFree + 2 * (t) + (wg))));
-        if (need_mask) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            if (i >= limit) sa[i] = __float_as_uint(-INFINITY);
-            if (i + 32 >= limit) sb[i] = __float_as_uint(-INFINITY);
-          }
-        }
+        // Two passes over the 64 scores in TMEM, 32 at a time through ONE register array: the row maximum first, the
+        // exponentials after the reference is settled.  Holding all 64 scores (as an earlier version did, to release S
+        // before the exponentials) left no room for the packed row-sum adds and cost a register move per pair; the
+        // second read of S is cheap, and S is handed back as soon as its last columns are in registers.
+        uint32_t sc[32];
         float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          m0 = fmaxf(m0, __uint_as_float(sa[i]));
-          m1 = fmaxf(m1, __uint_as_float(sa[i + 1]));
-          m2 = fmaxf(m2, __uint_as_float(sb[i]));
-          m3 = fmaxf(m3, __uint_as_float(sb[i + 1]));
+        for (int half = 0; half < 2; ++half) {
+          tmem_ld32(tS + 32 * half, sc);
+          tmem_ld_wait();
+          if (need_mask) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (i + 32 * half >= limit) sc[i] = __float_as_uint(-INFINITY);
+          }
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            m0 = fmaxf(m0, __uint_as_float(sc[i]));
+            m1 = fmaxf(m1, __uint_as_float(sc[i + 1]));
+            m2 = fmaxf(m2, __uint_as_float(sc[i + 2]));
+            m3 = fmaxf(m3, __uint_as_float(sc[i + 3]));
+          }
         }
         // Lazily updated reference (0 at the start): it only moves - with a rescale of O / l - when the tile max
         // overshoots it by more than 2^kTau (or, on my first tile, undershoots it by as much); p <= 2^kTau stays far
@@ -389,24 +389,33 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
             tmem_st_wait();
           }
         }
-        // 64 scores -> exp2 -> 16-bit P (registers)
-        float psum = 0.f;
+        // 64 scores -> exp2 -> 16-bit P (registers); row sum by packed fp32x2 adds into two pair accumulators
+        float ps[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
         uint32_t w[32];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
+        for (int half = 0; half < 2; ++half) {
+          tmem_ld32(tS + 32 * half, sc);
+          tmem_ld_wait();
+          if (half == 1) {  // S is in registers: Q K^T of my next tile may overwrite it
+            tc_fence_before();
+            mbar_arrive((bar0 + 8 * (kBarSFree + 2 * (t) + (wg))));
+          }
+          if (need_mask) {
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int i = (q & 3) * 8 + 2 * e;
+            for (int i = 0; i < 32; ++i)
+              if (i + 32 * half >= limit) sc[i] = __float_as_uint(-INFINITY);
+          }
+#pragma unroll
+          for (int k = 0; k < 16; ++k) {
             // both scores of the pair through one packed fp32x2 FMA (half the FMA-pipe issue slots)
             float x0, x1;
-            fma2(__uint_as_float(q < 4 ? sa[i] : sb[i]), __uint_as_float(q < 4 ? sa[i + 1] : sb[i + 1]), p.scale_log2,
-                 -mb, x0, x1);
+            fma2(__uint_as_float(sc[2 * k]), __uint_as_float(sc[2 * k + 1]), p.scale_log2, -mb, x0, x1);
             const float p0 = ex2f(x0), p1 = ex2f(x1);
-            psum += p0 + p1;
-            w[q * 4 + e] = pack_act2(p0, p1);
+            fadd2(ps[k & 1][0], ps[k & 1][1], p0, p1, ps[k & 1][0], ps[k & 1][1]);
+            w[16 * half + k] = pack_act2(p0, p1);
           }
         }
-        l_run += psum;
+        l_run += (ps[0][0] + ps[1][0]) + (ps[0][1] + ps[1][1]);
         if (p.p_col >= 0) {
           // P through tensor memory: my row's 64 probabilities as 32 packed columns of the query tile's P buffer, which
           // the two warpgroups of the tile share - tile j may be written once P(j-1) V(j-1) (the other warpgroup's
