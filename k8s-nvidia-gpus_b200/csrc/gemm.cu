@@ -74,6 +74,14 @@ struct alignas(64) GemmDev {
   int bw, bh, bn;
   int tiles_w, tiles_h, tiles_n, tiles_m, tiles_ncol;
   FastDiv div_munits, div_tw, div_twth;  // tile -> column tile; M tile -> (tw, th, tn)
+  // Tile order.  0: M fastest (all M tiles of column tile 0, then column tile 1, ...), CTAs striding over the list.
+  // 1: column fastest AND every CTA takes a contiguous run of the list - the column tiles of one M tile run back to
+  // back on the same CTA, so an A operand larger than L2 is read from HBM once instead of once per column tile
+  // (65536 x 1280 -> 320: 168 MB of activations, two column tiles), and every CTA still sees the same mix of wide
+  // and narrow column tiles.  The loops keep their strided index; split_tile() maps it to the run.
+  int col_fast;
+  FastDiv div_ncol, div_ctas;  // column tiles; CTAs (pairs) of the grid
+  int run_q, run_rem;          // tiles / CTAs: quotient and remainder (CTA b owns q + (b < rem) consecutive tiles)
   int kw_taps, taps;     // filter taps along w; total taps (kh * kw)
   int off_h, off_w;      // input pixel of tap (0, 0) relative to output pixel * stride (-pad for a centred filter)
   int stride;            // 1, or 2: the A tensor map then walks every other input pixel (element strides)
@@ -110,10 +118,27 @@ struct alignas(64) GemmDev {
 // tile -> (M tile, column tile), M fastest: with a persistent grid-stride loop every CTA then sees the same mix of
 // full-width and (narrower) last-column tiles instead of always the same column.  In pair mode `tile` counts PAIR
 // tiles (two consecutive M tiles, one per CTA).
+// tile -> (M unit, column tile) in the launch's tile order
+__device__ __forceinline__ void split_tile(const GemmDev& p, int tile, int& mt, int& nt) {
+  if (p.col_fast) {
+    const int k = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_ctas));  // my k-th tile
+    const int b = tile - k * static_cast<int>(p.div_ctas.d);                        // my CTA (pair)
+    const int t = b * p.run_q + min(b, p.run_rem) + k;
+    mt = static_cast<int>(fdiv(static_cast<uint32_t>(t), p.div_ncol));
+    nt = t - mt * p.tiles_ncol;
+  } else {
+    nt = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits));
+    mt = tile - nt * static_cast<int>(p.div_munits.d);
+  }
+}
+__device__ __forceinline__ int tile_col0(const GemmDev& p, int tile) {
+  int mt, nt;
+  split_tile(p, tile, mt, nt);
+  return nt * p.BN;
+}
 __device__ __forceinline__ void decode_tile(const GemmDev& p, int tile, int rank, int& n0, int& h0, int& w0, int& col0) {
-  const int m_units = static_cast<int>(p.div_munits.d);
-  const int nt = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits));
-  int mt = tile - nt * m_units;
+  int mt, nt;
+  split_tile(p, tile, mt, nt);
   if (p.pair) mt = 2 * mt + rank;  // an M tile past the end is all out of bounds: TMA zero-fills / clips it
   const int tn = static_cast<int>(fdiv(static_cast<uint32_t>(mt), p.div_twth));
   const int rem = mt - tn * static_cast<int>(p.div_twth.d);
@@ -292,7 +317,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         const int tile = static_cast<int>(fdiv(static_cast<uint32_t>(unit), p.div_split));
         const int split = unit - tile * p.split_k;
         const int kb_begin = split * num_kb / p.split_k, kb_end = (split + 1) * num_kb / p.split_k;
-        const int col0 = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits)) * p.BN;
+        const int col0 = tile_col0(p, tile);
         const int ncols = min(p.BN, p.N - col0);
         // no MMA work on padding columns; pair mode: one M = 256 instruction spans both CTAs
         const int ncols16 = (ncols + 15) & ~15;
@@ -345,9 +370,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
     if (p.b_static && tile0 < num_units) {
       const int tile = static_cast<int>(fdiv(static_cast<uint32_t>(tile0), p.div_split));
       const int split = tile0 - tile * p.split_k;
-      const int m_units = static_cast<int>(p.div_munits.d);
-      const int nt = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits));
-      if (tile - nt * m_units == 0) {
+      int mt, nt;
+      split_tile(p, tile, mt, nt);
+      if (mt == 0) {
         const uint32_t leader = elect_one();
         const int kb_begin = split * num_kb / p.split_k, kb_end = (split + 1) * num_kb / p.split_k;
         const int col0 = nt * p.BN;
@@ -385,7 +410,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       g += 2;
       for (;;) {
         if (tile >= num_tiles) return;
-        const int c0 = static_cast<int>(fdiv(static_cast<uint32_t>(tile), p.div_munits)) * p.BN;
+        const int c0 = tile_col0(p, tile);
         const int ng = (min(p.BN, p.N - c0) + acols - 1) / acols;
         if (g < ng) return;
         tile += tile_step;
@@ -1051,6 +1076,18 @@ static int gemm_impl(const b200sd_gemm_params* hp, b200sd_stream stream_, size_t
   const int smem_bytes = d.num_stages * stage_bytes + d.res_bufs * kEpiStageBytes + 1024;
   const int num_tiles = (d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m) * d.tiles_ncol * split;  // work units
   const int grid = d.pair ? 2 * min(num_tiles, di.sm_count / 2) : min(num_tiles, di.sm_count);
+  {
+    // column-fastest runs whenever there are several column tiles (see GemmDev::col_fast).  Measured inside the SD1.5
+    // step at batch 8: 65536 x 1280 -> 320 (168 MB of activations) 83 -> 73 us, 16384 x 2560 -> 640 -6 %,
+    // 65536 x 320 -> 960 -7 %, the 64x64-level convs -1..2 %, GEGLU 320 -> 2560 +1 %; all GEMMs 10.36 -> 10.23 ms.
+    const char* sw = getenv("B200SD_GEMM_COLFAST");  // "0": M-fastest strided order everywhere (A/B measurements)
+    d.col_fast = (d.tiles_ncol > 1 && split == 1 && !(sw != nullptr && sw[0] == '0')) ? 1 : 0;
+    const int ctas = d.pair ? grid / 2 : grid;
+    d.div_ncol = make_fastdiv(static_cast<uint32_t>(d.tiles_ncol));
+    d.div_ctas = make_fastdiv(static_cast<uint32_t>(ctas));
+    d.run_q = num_tiles / ctas;
+    d.run_rem = num_tiles % ctas;
+  }
   GemmLaunch L;
   memset(&L, 0, sizeof(L));
   L.d = d;
