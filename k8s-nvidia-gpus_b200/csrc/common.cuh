@@ -538,19 +538,24 @@ __device__ __forceinline__ float silu_tanh_f(float x) {
 __device__ __forceinline__ float quick_gelu_f(float x) {
   return x * rcp_approx(1.f + ex2_approx(-1.702f * 1.4426950408889634f * x));
 }
-// exact (erf) GELU = x * Phi(x) with erfc from Abramowitz & Stegun 7.1.26 (|error| < 1.5e-7 in erf, i.e. < 1e-7 in
-// Phi - far below the 16-bit output rounding): erfc(z) = t (a1 + t (a2 + t (a3 + t (a4 + t a5)))) exp(-z^2),
-// t = 1 / (1 + p z), z = |x| / sqrt(2).
+// exact (erf) GELU = x * Phi(x) with ONE MUFU op per element: log2 Phi(-a), a = |x|, is a smooth function that a
+// degree-6 polynomial through (0, -1) fits on [0, 6] to 2.4e-7 of a * erfc (weighted minimax; beyond 6, Phi(-a) < 1e-9),
+// so  h = Phi(-a) = 2^q(a)  costs six FMAs and an ex2, and  x Phi(x) = 0.5 x + a (0.5 - h)  for either sign.  |error| of
+// the result < 5e-7 over [-10, 10] evaluated in fp32 - the same as the Abramowitz & Stegun 7.1.26 form it replaces
+// (which needed a reciprocal and an exponential per element: the GEGLU epilogues were bound by the MUFU pipe).
+static constexpr float kGeluQ1 = -1.1511470079421997f, kGeluQ2 = -0.458916038274765f, kGeluQ3 = -0.05323765426874161f,
+                       kGeluQ4 = 0.007977096363902092f, kGeluQ5 = -0.0007397594163194299f,
+                       kGeluQ6 = 2.9910861485404894e-05f;
 __device__ __forceinline__ float gelu_erf_f(float x) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  const float t = rcp_approx(fmaf(0.3275911f, z, 1.f));
-  float q = fmaf(1.061405429f, t, -1.453152027f);
-  q = fmaf(q, t, 1.421413741f);
-  q = fmaf(q, t, -0.284496736f);
-  q = fmaf(q, t, 0.254829592f);
-  const float half_erfc = 0.5f * q * t * ex2_approx(-1.4426950408889634f * z * z);
-  const float phi = x >= 0.f ? 1.f - half_erfc : half_erfc;
-  return x * phi;
+  const float a = fabsf(x), c = fminf(a, 6.f);
+  float q = fmaf(kGeluQ6, c, kGeluQ5);
+  q = fmaf(q, c, kGeluQ4);
+  q = fmaf(q, c, kGeluQ3);
+  q = fmaf(q, c, kGeluQ2);
+  q = fmaf(q, c, kGeluQ1);
+  q = fmaf(q, c, -1.f);
+  const float h = ex2_approx(q);  // Phi(-|x|)
+  return fmaf(a, 0.5f - h, 0.5f * x);
 }
 
 // ------------------------------------------------------------------ order-independent statistics accumulation
@@ -604,25 +609,19 @@ __device__ __forceinline__ void fadd2(float a0, float a1, float b0, float b1, fl
 }
 // (v0, v1) *= gelu_erf(g0), gelu_erf(g1): the pair form of gelu_erf_f (same formula, same constants)
 __device__ __forceinline__ void mul_gelu_erf2(float& v0, float& v1, float g0, float g1) {
-  float z0, z1, t0, t1, q0, q1, e0, e1, h0, h1;
-  fmul2(fabsf(g0), fabsf(g1), 0.70710678118654752f, 0.70710678118654752f, z0, z1);
-  ffma2(z0, z1, 0.3275911f, 0.3275911f, 1.f, 1.f, t0, t1);
-  t0 = rcp_approx(t0);
-  t1 = rcp_approx(t1);
-  ffma2(t0, t1, 1.061405429f, 1.061405429f, -1.453152027f, -1.453152027f, q0, q1);
-  ffma2(q0, q1, t0, t1, 1.421413741f, 1.421413741f, q0, q1);
-  ffma2(q0, q1, t0, t1, -0.284496736f, -0.284496736f, q0, q1);
-  ffma2(q0, q1, t0, t1, 0.254829592f, 0.254829592f, q0, q1);
-  fmul2(q0, q1, t0, t1, q0, q1);
-  fmul2(z0, z1, z0, z1, e0, e1);
-  e0 = ex2_approx(-1.4426950408889634f * e0);
-  e1 = ex2_approx(-1.4426950408889634f * e1);
-  fmul2(q0, q1, e0, e1, h0, h1);  // erfc(z) = q t exp(-z^2)
-  // x * Phi(x) = x * (x >= 0 ? 1 - erfc / 2 : erfc / 2) = 0.5 * (x + |x| * (1 - erfc))
-  float w0, w1;
-  ffma2(h0, h1, -1.f, -1.f, 1.f, 1.f, w0, w1);               // 1 - erfc
-  ffma2(fabsf(g0), fabsf(g1), w0, w1, g0, g1, w0, w1);        // x + |x| (1 - erfc)
-  fmul2(w0, w1, 0.5f, 0.5f, w0, w1);
+  const float a0 = fabsf(g0), a1 = fabsf(g1);
+  const float c0 = fminf(a0, 6.f), c1 = fminf(a1, 6.f);
+  float q0, q1, s0, s1, w0, w1;
+  ffma2(c0, c1, kGeluQ6, kGeluQ6, kGeluQ5, kGeluQ5, q0, q1);
+  ffma2(q0, q1, c0, c1, kGeluQ4, kGeluQ4, q0, q1);
+  ffma2(q0, q1, c0, c1, kGeluQ3, kGeluQ3, q0, q1);
+  ffma2(q0, q1, c0, c1, kGeluQ2, kGeluQ2, q0, q1);
+  ffma2(q0, q1, c0, c1, kGeluQ1, kGeluQ1, q0, q1);
+  ffma2(q0, q1, c0, c1, -1.f, -1.f, q0, q1);
+  const float h0 = ex2_approx(q0), h1 = ex2_approx(q1);  // Phi(-|g|)
+  ffma2(h0, h1, -1.f, -1.f, 0.5f, 0.5f, s0, s1);         // 0.5 - h
+  fmul2(g0, g1, 0.5f, 0.5f, w0, w1);
+  ffma2(a0, a1, s0, s1, w0, w1, w0, w1);                 // g Phi(g) = 0.5 g + |g| (0.5 - h)
   fmul2(v0, v1, w0, w1, v0, v1);
 }
 

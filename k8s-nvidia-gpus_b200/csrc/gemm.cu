@@ -82,6 +82,9 @@ struct alignas(64) GemmDev {
   int col_fast;
   FastDiv div_ncol, div_ctas;  // column tiles; CTAs (pairs) of the grid
   int run_q, run_rem;          // tiles / CTAs: quotient and remainder (CTA b owns q + (b < rem) consecutive tiles)
+#ifdef B200SD_DIAG
+  int diag;  // timing experiments only (results are wrong): 1 no epilogue work, 2 no B loads, 4 no A loads, 8 no output store, 16 epilogue math only
+#endif
   int kw_taps, taps;     // filter taps along w; total taps (kh * kw)
   int off_h, off_w;      // input pixel of tap (0, 0) relative to output pixel * stride (-pad for a centred filter)
   int stride;            // 1, or 2: the A tensor map then walks every other input pixel (element strides)
@@ -278,6 +281,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           if (!b_issued) tma_load_2d_pair_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
         } else if (b_issued) {
           tma_load_4d_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
+#ifdef B200SD_DIAG
+        } else if (p.diag & 6) {
+          mbar_arrive_expect_tx_w(leader, bar, (p.diag & 4) ? b_bytes : kABytes);
+          if (!(p.diag & 4))
+            tma_load_4d_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
+          if (!(p.diag & 2)) tma_load_2d_w(leader, sa + kABytes, &p.tmB, bar, kb * kBlockK, bcol);
+#endif
         } else {
           mbar_arrive_expect_tx_w(leader, bar, stage_bytes);
           tma_load_4d_w(leader, sa, tmA, bar, ch, w0 * p.stride + kw + p.off_w, h0 * p.stride + kh + p.off_h, n0);
@@ -445,7 +455,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * 256 + (static_cast<uint32_t>(q * 32) << 16);
       const int ncols = min(p.BN, p.N - col0);  // valid accumulator columns in this tile
+#ifdef B200SD_DIAG
+      const int ngroups = (p.diag & 1) ? 0 : (ncols + acols - 1) / acols;
+#else
       const int ngroups = (ncols + acols - 1) / acols;
+#endif
 
       // ---- split-K: park this unit's raw accumulator tile, count it, and go on unless it was the last slice
       const float* ws_tile = nullptr;
@@ -673,6 +687,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
             }
           }
         }
+#ifdef B200SD_DIAG
+        if (p.diag & 16) {  // compute only: no staging, no store (keep the packed words alive)
+          if (w[0] == 0x7fc07fc0u && w[31] == 0x12345678u) p.cnt[0] = 1;
+          ++gk;
+          continue;
+        }
+#endif
         // staging tile free: residual consumed by everyone (kRes) / previous store has finished reading it
         if (!kRes && issuer) bulk_wait_read0();
         named_bar_sync(bar_id, 128);
@@ -727,7 +748,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           }
         }
         named_bar_sync(bar_id, 128);
+#ifdef B200SD_DIAG
+        if (issuer && !(p.diag & 8)) {
+#else
         if (issuer) {
+#endif
           tma_store_4d(&p.tmO, stg, ocol0, w0, h0, n0);
           bulk_commit();
         }
@@ -1076,6 +1101,9 @@ static int gemm_impl(const b200sd_gemm_params* hp, b200sd_stream stream_, size_t
   const int smem_bytes = d.num_stages * stage_bytes + d.res_bufs * kEpiStageBytes + 1024;
   const int num_tiles = (d.pair ? (d.tiles_m + 1) / 2 : d.tiles_m) * d.tiles_ncol * split;  // work units
   const int grid = d.pair ? 2 * min(num_tiles, di.sm_count / 2) : min(num_tiles, di.sm_count);
+#ifdef B200SD_DIAG
+  d.diag = getenv("B200SD_GEMM_DIAG") ? atoi(getenv("B200SD_GEMM_DIAG")) : 0;
+#endif
   {
     // column-fastest runs whenever there are several column tiles (see GemmDev::col_fast).  Measured inside the SD1.5
     // step at batch 8: 65536 x 1280 -> 320 (168 MB of activations) 83 -> 73 us, 16384 x 2560 -> 640 -6 %,
