@@ -163,7 +163,11 @@ enum : int {
   kNumBars = kBarRes + 4              // [epilogue warpgroup][staging buffer]
 };
 
-template <bool kOutF32, bool kGeglu, bool kRes, bool kPair>
+// kSimple: the epilogue of a plain linear / 1x1 layer (bias, GEGLU or residual only) - no split-K reduction, no alpha, no
+// row bias, no SiLU / GELU, no folded LayerNorm, no fused GroupNorm statistics.  Those features are uniform run-time
+// branches otherwise; compiled out they free registers and instructions in the epilogue that bounds the
+// short-reduction layers.
+template <bool kOutF32, bool kGeglu, bool kRes, bool kPair, bool kSimple>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid_constant__ GemmDev p) {
   extern __shared__ uint8_t smem_raw[];
   // all mbarriers in one block: one base address, every barrier a constant byte offset from it
@@ -463,7 +467,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
 
       // ---- split-K: park this unit's raw accumulator tile, count it, and go on unless it was the last slice
       const float* ws_tile = nullptr;
-      if (p.split_k > 1) {
+      if (!kSimple && p.split_k > 1) {
         // slice layout [32-column chunk][16-byte piece k][row] : the 32 lanes of a warp (consecutive rows) write 512
         // contiguous bytes per store (row-major rows would make every lane's 16 bytes a request of its own: measured,
         // the reduction then costs more than the split saves)
@@ -503,7 +507,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       const long long grow = (static_cast<long long>(n0 + in) * p.H + (h0 + ih)) * p.W + (w0 + iw);
       // folded LayerNorm, consumer side: my row's mean and 1/std from the producer's integer sums
       float ln_a = 1.f, ln_b = 0.f;
-      if (p.ln_in != nullptr && gn_row_ok) {
+      if (!kSimple && p.ln_in != nullptr && gn_row_ok) {
         const unsigned long long* sl = p.ln_in + grow * kGnSlotWords64;
         const ulonglong2 a2 = __ldcg(reinterpret_cast<const ulonglong2*>(sl));
         const ulonglong2 b2 = __ldcg(reinterpret_cast<const ulonglong2*>(sl + 2));
@@ -517,7 +521,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
       // accumulator columns [ac, ac+32) -> f[] = alpha * acc + bias
       auto load_chunk = [&](int ac, float(&f)[32]) {
         uint32_t v[32];
-        if (ws_tile != nullptr) {
+        if (!kSimple && ws_tile != nullptr) {
           // the slices of this tile, added in index order (deterministic whatever the arrival order was)
 #pragma unroll
           for (int k = 0; k < 32; ++k) v[k] = 0u;
@@ -537,14 +541,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           tmem_ld32(taddr + ac, v);
           tmem_ld_wait();
         }
-        if (p.alpha != 1.f) {
+        if (!kSimple && p.alpha != 1.f) {
 #pragma unroll
           for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(v[k]) * p.alpha;
         } else {
 #pragma unroll
           for (int k = 0; k < 32; ++k) f[k] = __uint_as_float(v[k]);
         }
-        if (p.ln_in != nullptr) {
+        if (!kSimple && p.ln_in != nullptr) {
           // LN(x) W^T = rstd * (x (gamma W)^T) - rstd * mean * colsum(gamma W)   (+ W beta + b, folded into bias)
           const int col = col0 + ac;
           if (col + 32 <= p.N) {
@@ -617,7 +621,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           } else {
             const int ac = ac0 + hh * 32;
             load_chunk(ac, f);
-            if (p.rowbias != nullptr) {
+            if (!kSimple && p.rowbias != nullptr) {
               const float* rb = p.rowbias + static_cast<long long>(img) * p.ld_rowbias + col0 + ac;
               if (col0 + ac + 32 <= p.N && (reinterpret_cast<uintptr_t>(rb) & 15u) == 0) {
 #pragma unroll
@@ -632,7 +636,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
                   if (col0 + ac + k < p.N) f[k] += __ldg(rb + k);
               }
             }
-            if (p.act == B200SD_ACT_SILU) {
+            if (kSimple) {
+            } else if (p.act == B200SD_ACT_SILU) {
 #pragma unroll
               for (int k = 0; k < 32; ++k) f[k] = silu_f(f[k]);
             } else if (p.act == B200SD_ACT_QUICK_GELU) {
@@ -667,7 +672,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
           }
         }
         if (!kOutF32) {
-          if (p.ln_out != nullptr) {
+          if (!kSimple && p.ln_out != nullptr) {
             // folded LayerNorm, producer side: sum / sum of squares of my row's 64 (rounded) outputs of this group,
             // added as integers to the row's slot (order-independent across column groups and tiles)
             const int n_valid = (kGeglu ? p.N / 2 : p.N) - ocol0;
@@ -704,7 +709,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
                        : "memory");
         fence_proxy_async_smem();
         if (!kOutF32 && !kGeglu) {
-          if (p.gn_stats != nullptr) {
+          if (!kSimple && p.gn_stats != nullptr) {
             // Fused GroupNorm statistics of this 128 x 64 output group, read back TRANSPOSED from the staging tile:
             // lane = one column pair, walking the 32 rows my own warp has just written (one image, see b200sd.h) -
             // conflict-free 4-byte loads, a rolled loop.  Lanes of the same channel group are then combined by a
@@ -758,7 +763,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_conv_kernel(const __grid
         }
         ++gk;
       }
-      if (p.split_k > 1) continue;  // (the accumulator was released right after its slice was parked)
+      if (!kSimple && p.split_k > 1) continue;  // (the accumulator was released right after its slice was parked)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -825,9 +830,9 @@ static TilePlan pick_tiles(int M_tiles, int N, int sm_count, int gran, int num_k
   return best;
 }
 
-template <bool F, bool G, bool R, bool P>
+template <bool F, bool G, bool R, bool P, bool S>
 static int launch_one(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
-  if (int e = ensure_dyn_smem(reinterpret_cast<const void*>(&gemm_conv_kernel<F, G, R, P>), max_smem - 512)) return e;
+  if (int e = ensure_dyn_smem(reinterpret_cast<const void*>(&gemm_conv_kernel<F, G, R, P, S>), max_smem - 512)) return e;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
@@ -846,28 +851,32 @@ static int launch_one(const GemmDev& d, int grid, int smem_bytes, int max_smem, 
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.numAttrs = 2;
   }
-  B200SD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_conv_kernel<F, G, R, P>, d));
+  B200SD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemm_conv_kernel<F, G, R, P, S>, d));
   return B200SD_OK;
 }
 
 template <bool F, bool G, bool R>
-static int launch_variant(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream) {
-  return d.pair ? launch_one<F, G, R, true>(d, grid, smem_bytes, max_smem, stream)
-                : launch_one<F, G, R, false>(d, grid, smem_bytes, max_smem, stream);
+static int launch_variant(const GemmDev& d, int grid, int smem_bytes, int max_smem, cudaStream_t stream, bool simple) {
+  if (!F && simple)
+    return d.pair ? launch_one<false, G, R, true, true>(d, grid, smem_bytes, max_smem, stream)
+                  : launch_one<false, G, R, false, true>(d, grid, smem_bytes, max_smem, stream);
+  return d.pair ? launch_one<F, G, R, true, false>(d, grid, smem_bytes, max_smem, stream)
+                : launch_one<F, G, R, false, false>(d, grid, smem_bytes, max_smem, stream);
 }
 
 // what a finished launch needs: the device-side descriptor block + launch geometry (kept in the launch cache)
 struct GemmLaunch {
   GemmDev d;
   int grid, smem_bytes, variant;  // variant: 0 plain, 1 residual, 2 fp32 out, 3 GEGLU
+  int simple;                     // the kSimple instantiation (see the kernel)
 };
 
 static int launch_cached(const GemmLaunch& L, int max_smem, cudaStream_t stream) {
   switch (L.variant) {
-    case 3: return launch_variant<false, true, false>(L.d, L.grid, L.smem_bytes, max_smem, stream);
-    case 2: return launch_variant<true, false, false>(L.d, L.grid, L.smem_bytes, max_smem, stream);
-    case 1: return launch_variant<false, false, true>(L.d, L.grid, L.smem_bytes, max_smem, stream);
-    default: return launch_variant<false, false, false>(L.d, L.grid, L.smem_bytes, max_smem, stream);
+    case 3: return launch_variant<false, true, false>(L.d, L.grid, L.smem_bytes, max_smem, stream, L.simple != 0);
+    case 2: return launch_variant<true, false, false>(L.d, L.grid, L.smem_bytes, max_smem, stream, L.simple != 0);
+    case 1: return launch_variant<false, false, true>(L.d, L.grid, L.smem_bytes, max_smem, stream, L.simple != 0);
+    default: return launch_variant<false, false, false>(L.d, L.grid, L.smem_bytes, max_smem, stream, L.simple != 0);
   }
 }
 
@@ -1122,6 +1131,14 @@ static int gemm_impl(const b200sd_gemm_params* hp, b200sd_stream stream_, size_t
   L.grid = grid;
   L.smem_bytes = smem_bytes;
   L.variant = geglu ? 3 : (f32 ? 2 : (res ? 1 : 0));
+  {
+    const char* sw = getenv("B200SD_GEMM_SIMPLE");  // "0": always the general epilogue (A/B measurements)
+    L.simple = (!(sw != nullptr && sw[0] == '0') && !f32 && split == 1 && h.alpha == 1.f && h.rowbias == nullptr &&
+                h.ln_in_stats == nullptr && h.ln_out_stats == nullptr && h.gn_stats == nullptr &&
+                (h.act == B200SD_ACT_NONE || h.act == B200SD_ACT_GEGLU))
+                   ? 1
+                   : 0;
+  }
   launch_cache_put(0, hp, sizeof(*hp), &L, sizeof(L));
   return launch_cached(L, di.max_smem_optin, stream);
 }
