@@ -217,7 +217,8 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
     const uint32_t tOt = tmem_base + p.o_col + 2 * t * p.o_stride;
     int kst = 0, vst = 0;
     uint32_t kph = 0, vph = 0;
-    int cw[2] = {0, 0};  // completions so far of this tile's per-parity barriers (S full / free, P full, PV done)
+    int cw0 = 0, cw1 = 0;  // completions so far of this tile's per-parity barriers (S full / free, P full, PV done);
+                           // two scalars, not an array: a dynamically indexed array lives in local memory
     int n = 0, n_act = 0;  // items seen / items in which this query tile existed
     // S_t into buffer bfs from the current K stage (MMAs only; the commits follow separately)
     auto issue_s = [&](int bfs) {
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
     // S of tile jj of the current item: its buffer's previous use (this item or the one before) must have been read
     auto s_tile = [&](int jj) {
       const int bfs = jj & 1;
-      const int gi = cw[bfs] + (jj >> 1);  // how many times this buffer has been used before
+      const int gi = (bfs ? cw1 : cw0) + (jj >> 1);  // how many times this buffer has been used before
       if (gi > 0) mbar_wait_spin((bar0 + 8 * (kBarSFree + 2 * (t) + (bfs))), (gi - 1) & 1);
       mbar_wait_spin((bar0 + 8 * (kBarKFull + (kst))), kph);
       tc_fence_after();
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       if (T <= 2) umma_commit_w(leader, (bar0 + 8 * kBarQFree));  // every S of the item has been issued
       for (int j = 0; j < T; ++j) {
         const int bf = j & 1;
-        const int gi = cw[bf] + (j >> 1);
+        const int gi = (bf ? cw1 : cw0) + (j >> 1);
         if (j + 2 < T) {
           s_tile(j + 2);
           if (j + 3 >= T) umma_commit_w(leader, (bar0 + 8 * kBarQFree));  // that was the item's last S
@@ -303,8 +304,8 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           vph ^= 1u;
         }
       }
-      cw[0] += (T + 1) >> 1;
-      cw[1] += T >> 1;
+      cw0 += (T + 1) >> 1;
+      cw1 += T >> 1;
       ++n_act;
     }
   }
@@ -323,7 +324,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
     const uint32_t sPt = sP + (2 * t + wg) * kQAtom + r * 128;
     const uint32_t swz = static_cast<uint32_t>(r & 7) << 4;
     const int pair_bar = 1 + t * 4 + qd;  // named barrier shared by the two warps that own the same 32 rows
-    int cw[2] = {0, 0};  // completions so far of this tile's per-parity barriers (as in the issuer)
+    int cw0 = 0, cw1 = 0;  // completions so far of this tile's per-parity barriers (as in the issuer)
     for (int item = blockIdx.x; t < p.qtiles && item < p.items; item += gridDim.x) {
       int q0, head, b, ntiles, T;
       item_geom(item, q0, head, b, ntiles, T);
@@ -332,7 +333,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       float mb = 0.f;     // my reference exponent (log2 domain): p = 2^(s * scale_log2 - mb)
       float l_run = 0.f;  // my row sum
       for (int j = wg; j < T; j += 2) {
-        const int gi = cw[wg] + (j >> 1);  // running index of this use of my S / P barriers
+        const int gi = (wg ? cw1 : cw0) + (j >> 1);  // running index of this use of my S / P barriers
         const int col0 = j * kBKV;
         int limit = p.nk - col0;  // valid columns: [0, limit)
         if (p.causal) limit = min(limit, qrow - col0 + 1);
@@ -421,7 +422,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
           // the two warpgroups of the tile share - tile j may be written once P(j-1) V(j-1) (the other warpgroup's
           // tile) has been consumed.  No shared-memory store, and P V reads its A operand from TMEM: half of this
           // kernel's shared-memory traffic is gone.
-          if (j >= 1) mbar_wait_spin(bar0 + 8 * (kBarPVDone + 2 * t + (wg ^ 1)), (cw[wg ^ 1] + ((j - 1) >> 1)) & 1);
+          if (j >= 1) mbar_wait_spin(bar0 + 8 * (kBarPVDone + 2 * t + (wg ^ 1)), ((wg ? cw0 : cw1) + ((j - 1) >> 1)) & 1);
           tmem_st32(tmem_base + p.p_col + 32 * t + lane_off, w);
           tmem_st_wait();
         } else {
@@ -441,7 +442,7 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       // with f_x = 2^(mb_x - max(mb_e, mb_o)); both accumulators live in my TMEM lanes, only mb / l travel through smem.
       const int mine = (T - wg + 1) >> 1;  // tiles I processed
       const bool has_odd = T >= 2;
-      if (mine > 0) mbar_wait((bar0 + 8 * (kBarPVDone + 2 * (t) + (wg))), (cw[wg] + mine - 1) & 1);  // the last commit covers every earlier MMA
+      if (mine > 0) mbar_wait((bar0 + 8 * (kBarPVDone + 2 * (t) + (wg))), ((wg ? cw1 : cw0) + mine - 1) & 1);  // the last commit covers every earlier MMA
       const uint32_t xa = sX + ((t * 2 + wg) * 2 * kBQ + r) * 4, xb = sX + ((t * 2 + (wg ^ 1)) * 2 * kBQ + r) * 4;
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(xa), "f"(mb) : "memory");
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(xa + kBQ * 4), "f"(l_run) : "memory");
@@ -488,8 +489,8 @@ __global__ void __launch_bounds__(kAttThreads, 1) attention_kernel(const __grid_
       // O has been read out: the issuer may overwrite the accumulators with the next item's first products
       tc_fence_before();
       mbar_arrive((bar0 + 8 * (kBarOFree + t)));
-      cw[0] += (T + 1) >> 1;
-      cw[1] += T >> 1;
+      cw0 += (T + 1) >> 1;
+      cw1 += T >> 1;
     }
   }
 
