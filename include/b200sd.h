@@ -175,6 +175,8 @@ int b200sd_attention(const b200sd_attn_params* p, b200sd_stream stream);
  * (image, group), 16-byte aligned); b200sd_groupnorm_stats ACCUMULATES into it (the caller zeroes it first).
  * The sums are kept as 64-bit fixed-point integers, so the totals - and therefore the images - are bit-identical from
  * run to run and do not depend on the order in which thread blocks finish (fp32 atomics would).
+ * Limits: c0, c1 multiples of 8, (c0 + c1) divisible by groups and <= 6144, groups <= 1024 (B200SD_ERR_BAD_SHAPE /
+ * B200SD_ERR_TOO_LARGE otherwise); nimg <= 65535 (one grid row per image).
  */
 #define B200SD_GN_STATS_WORDS 8
 typedef struct {

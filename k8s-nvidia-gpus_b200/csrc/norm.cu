@@ -370,6 +370,7 @@ static int gn_check(const b200sd_groupnorm_params& h, int* pix_per_cta, int* chu
   B200SD_REQUIRE((C % h.groups) == 0, B200SD_ERR_BAD_SHAPE, "groupnorm: %d channels not divisible by %d groups", C,
                  h.groups);
   B200SD_REQUIRE(h.groups <= 1024 && C <= 6144, B200SD_ERR_TOO_LARGE, "groupnorm: too many groups/channels");
+  B200SD_REQUIRE(h.nimg <= 65535, B200SD_ERR_TOO_LARGE, "groupnorm: at most 65535 images per call (got %d)", h.nimg);
   B200SD_REQUIRE((h.c1 == 0) == (h.x1 == nullptr), B200SD_ERR_BAD_ARGUMENT, "groupnorm: x1 and c1 must agree");
   B200SD_REQUIRE(aligned16(h.x0) && aligned16(h.x1) && aligned16(h.out), B200SD_ERR_BAD_ALIGNMENT,
                  "groupnorm: pointers must be 16-byte aligned");
