@@ -249,6 +249,20 @@ def algorithmic_bytes(call):
     return 0.0
 
 
+def exclusive_us(spans):
+    """spans: (start, end) of kernels sorted by start.  Returns each kernel's time counted from the end of everything
+    launched before it: a kernel launched with programmatic dependent launch becomes resident (and its record starts)
+    while its predecessor is still running and then waits for it, so the overlapped head belongs to the predecessor.
+    Equals end - start when nothing overlaps; the values add up to the busy time of the stream."""
+    out, frontier = [], None
+    for start, end in spans:
+        if frontier is None:
+            frontier = start
+        out.append(max(0.0, end - max(start, frontier)))
+        frontier = max(frontier, end)
+    return out
+
+
 def cupti_profile(plan, replays=3):
     """Per-kernel device durations of `replays` graph replays of `plan` from CUPTI activity records (torch.profiler:
     hardware start / end timestamps of every kernel, no serialisation between launches, no replay - unlike ncu), matched
@@ -268,18 +282,13 @@ def cupti_profile(plan, replays=3):
     if len(evs) != replays * len(calls):
         return {"error": f"{len(evs)} kernel records for {replays} x {len(calls)} calls"}
     agg = {}
-    frontier = evs[0].time_range.start
+    excl = exclusive_us([(e.time_range.start, e.time_range.end) for e in evs])
     for i, e in enumerate(evs):
         c = calls[i % len(calls)]
         fl, kind = flops_of_call(c)
         a = agg.setdefault(kind, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
         a["launches"] += 1
-        # A kernel launched with programmatic dependent launch becomes resident (and its record starts) while its
-        # predecessor is still running, and then waits for it: the overlapped head belongs to the predecessor.  A
-        # kernel's time is therefore counted from the end of everything launched before it (== its whole duration when
-        # nothing overlaps), so the per-kind times still add up to the busy time of the stream.
-        a["ms"] += max(0.0, e.time_range.end - max(e.time_range.start, frontier)) * 1e-3
-        frontier = max(frontier, e.time_range.end)
+        a["ms"] += excl[i] * 1e-3  # see exclusive_us
         a["flops"] += fl
         a["bytes"] += algorithmic_bytes(c)
     for a in agg.values():

@@ -478,3 +478,19 @@ def test_integration_md_ctypes_stub_runs(b200sd):
     finally:
         os.chdir(cwd)
     assert ns["ctypes"].sizeof(ns["GemmParams"]) == b200sd.lib.struct_sizes()[0]
+
+
+def test_bench_exclusive_kernel_times():
+    """bench.py's CUPTI pass: a kernel that became resident under its predecessor's tail (programmatic dependent launch)
+    is counted from the predecessor's end; without overlap every kernel keeps its whole duration; times add up to the
+    busy time of the stream."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert bench.exclusive_us([(0.0, 10.0), (12.0, 20.0), (20.0, 21.0)]) == [10.0, 8.0, 1.0]
+    # second kernel resident from t = 6 but waiting until 10; third entirely inside the second (cannot happen, but
+    # must not go negative)
+    assert bench.exclusive_us([(0.0, 10.0), (6.0, 18.0), (7.0, 17.0)]) == [10.0, 8.0, 0.0]
+    spans = [(0.0, 5.0), (4.0, 9.0), (8.5, 30.0), (31.0, 32.0)]
+    assert sum(bench.exclusive_us(spans)) == 5.0 + 4.0 + 21.0 + 1.0
